@@ -1,0 +1,885 @@
+// C ABI of libmsckf_b200.so (see include/msckf_b200.h): context life cycle, pinned staging,
+// stage sequencing on one CUDA stream, state import / export.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "kernels.h"
+
+using namespace msckf;
+
+namespace {
+thread_local std::string g_create_error;
+
+struct Staging {          // one pinned + one device arena; reused round-robin
+  char* h = nullptr;
+  char* d = nullptr;
+  size_t cap = 0;
+  cudaEvent_t done = nullptr;
+};
+}  // namespace
+
+struct msckf_ctx {
+  msckf_config cfg;
+  Dev d;
+  Params hp;
+  int device = 0;
+  cudaStream_t st = nullptr;
+  std::vector<void*> dev_allocs;
+  Staging stg[2];
+  int stg_next = 0;
+  double* h_pub = nullptr;          // pinned [F][IMU_STRIDE]
+  unsigned char* h_reset = nullptr; // pinned [F]
+  unsigned* h_err = nullptr;        // pinned [1]
+  std::string err;
+  bool timing = false;
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  float last_ms[5] = {0, 0, 0, 0, 0};
+  bool frame_pending = false;
+};
+
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      char buf_[512];                                                                              \
+      snprintf(buf_, sizeof buf_, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+      ctx->err = buf_;                                                                             \
+      return MSCKF_ERR_CUDA;                                                                       \
+    }                                                                                              \
+  } while (0)
+
+#define ARG(cond, msg)                  \
+  do {                                  \
+    if (!(cond)) {                      \
+      ctx->err = std::string("bad argument: ") + msg; \
+      return MSCKF_ERR_ARG;             \
+    }                                   \
+  } while (0)
+
+template <class T>
+static int dalloc(msckf_ctx* ctx, T** p, size_t count) {
+  void* q = nullptr;
+  CK(cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T)));
+  CK(cudaMemsetAsync(q, 0, std::max<size_t>(count, 1) * sizeof(T), ctx->st));
+  ctx->dev_allocs.push_back(q);
+  *p = (T*)q;
+  return 0;
+}
+
+static int check_device_errors(msckf_ctx* ctx) {
+  // caller has synchronised the stream after copying d.err to h_err
+  const unsigned e = *ctx->h_err;
+  if (!e) return MSCKF_OK;
+  cudaMemsetAsync(ctx->d.err, 0, sizeof(unsigned), ctx->st);
+  *ctx->h_err = 0;
+  std::string s = "device reported:";
+  int rc = MSCKF_ERR_CAPACITY;
+  if (e & ERRBIT_FEATURE_CAP) s += " feature_capacity exceeded;";
+  if (e & ERRBIT_POOL) s += " jacobian pool exhausted (raise jacobian_pool_bytes);";
+  if (e & ERRBIT_ROWS) s += " stacked-Jacobian rows exceed max_rows;";
+  if (e & ERRBIT_CAM_CAP) s += " camera-state window full (augment without prune);";
+  if (e & ERRBIT_NOT_SPD) { s += " innovation covariance not positive definite;"; rc = MSCKF_ERR_NUMERIC; }
+  ctx->err = s;
+  return rc;
+}
+
+static int sync_and_check(msckf_ctx* ctx) {
+  CK(cudaMemcpyAsync(ctx->h_err, ctx->d.err, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->st));
+  CK(cudaStreamSynchronize(ctx->st));
+  CK(cudaGetLastError());
+  return check_device_errors(ctx);
+}
+
+// ---- staging: pack several host arrays into one pinned arena, one H2D copy
+struct Packer {
+  msckf_ctx* ctx;
+  Staging* s;
+  size_t off = 0;
+  std::vector<std::pair<size_t, std::pair<const void*, size_t>>> parts;
+  size_t add(const void* src, size_t bytes) {
+    const size_t o = off;
+    parts.push_back({o, {src, bytes}});
+    off += (bytes + 255) & ~size_t(255);
+    return o;
+  }
+};
+
+static int stage_begin(msckf_ctx* ctx, Packer& p) {
+  p.ctx = ctx;
+  p.s = &ctx->stg[ctx->stg_next];
+  ctx->stg_next ^= 1;
+  return 0;
+}
+
+static int stage_commit(msckf_ctx* ctx, Packer& p) {
+  Staging* s = p.s;
+  CK(cudaEventSynchronize(s->done));       // previous user of this arena has finished
+  if (p.off > s->cap) {
+    if (s->h) cudaFreeHost(s->h);
+    if (s->d) cudaFree(s->d);
+    s->cap = std::max<size_t>(p.off * 2, 1 << 20);
+    CK(cudaMallocHost((void**)&s->h, s->cap));
+    CK(cudaMalloc((void**)&s->d, s->cap));
+  }
+  for (auto& part : p.parts)
+    if (part.second.second) memcpy(s->h + part.first, part.second.first, part.second.second);
+  if (p.off) CK(cudaMemcpyAsync(s->d, s->h, p.off, cudaMemcpyHostToDevice, ctx->st));
+  return 0;
+}
+static int stage_end(msckf_ctx* ctx, Packer& p) {
+  CK(cudaEventRecord(p.s->done, ctx->st));
+  return 0;
+}
+
+extern "C" {
+
+const char* msckf_version(void) { return "msckf_b200 sm_100a cuda " "12.9"; }
+
+const char* msckf_last_error(const msckf_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
+  if (!cfg || !out) { g_create_error = "null argument"; return MSCKF_ERR_ARG; }
+  *out = nullptr;
+  if (cfg->n_filters < 1 || cfg->max_cam_states < 5 || cfg->max_cam_states > 64 || cfg->feature_capacity < 8) {
+    g_create_error = "bad argument: n_filters >= 1, 5 <= max_cam_states <= 64, feature_capacity >= 8";
+    return MSCKF_ERR_ARG;
+  }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0 || cfg->device < 0 || cfg->device >= ndev) {
+    g_create_error = std::string("no usable CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device ordinal out of range");
+    return MSCKF_ERR_CUDA;
+  }
+  cudaDeviceProp prop;
+  cudaGetDeviceProperties(&prop, cfg->device);
+  if (prop.major < 10) {
+    g_create_error = std::string("device is not sm_100-class: ") + prop.name + " (this library ships sm_100a code only, no fallback)";
+    return MSCKF_ERR_CUDA;
+  }
+  msckf_ctx* ctx = new msckf_ctx();
+  ctx->cfg = *cfg;
+  ctx->device = cfg->device;
+  auto fail = [&](int rc) {
+    g_create_error = ctx->err;
+    msckf_destroy(ctx);
+    return rc;
+  };
+#define CKC(call) do { int rc_ = [&]() -> int { CK(call); return 0; }(); if (rc_) return fail(rc_); } while (0)
+  CKC(cudaSetDevice(cfg->device));
+  CKC(cudaStreamCreateWithFlags(&ctx->st, cudaStreamNonBlocking));
+  for (auto& s : ctx->stg) CKC(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+  for (auto& evn : ctx->ev) CKC(cudaEventCreate(&evn));
+
+  Dev& d = ctx->d;
+  memset(&d, 0, sizeof d);
+  d.F = cfg->n_filters;
+  d.Nmax = cfg->max_cam_states;
+  d.nmax = NI + 6 * d.Nmax;
+  d.ld = (d.nmax + 7) & ~7;
+  d.Fcap = cfg->feature_capacity;
+  int hs = 16;
+  while (hs < 2 * d.Fcap) hs <<= 1;
+  d.Hs = hs;
+  const int row_cap = cfg->row_cap;
+  d.max_rows = cfg->max_rows > 0 ? cfg->max_rows : ((row_cap > 0 ? row_cap : 1500) + 4 * d.Nmax + 8);
+  d.Tk = d.nmax;
+  {
+    const long long mr = ((long long)d.max_rows + 3) / 4 * 4;
+    const long long a1 = mr * (d.nmax + 1);
+    const long long a2 = ((long long)5 * d.Fcap + 4) * 13;
+    d.A_elems = std::max(a1, a2);
+  }
+  auto need = [](long long M) { return 4 * M * (6 * M + 4) + (4 * M - 3) * 6 * M + (4 * M - 3) * (4 * M - 3); };
+  long long pool = cfg->jacobian_pool_bytes > 0 ? cfg->jacobian_pool_bytes / 8
+                                                : (long long)d.F * ((long long)d.Fcap * 256 + 32 * need(d.Nmax));
+  d.pool_cap = pool;
+
+  Params& hp = ctx->hp;
+  memset(&hp, 0, sizeof hp);
+  hp.Qc[0] = cfg->gyro_noise; hp.Qc[1] = cfg->gyro_bias_noise; hp.Qc[2] = cfg->acc_noise; hp.Qc[3] = cfg->acc_bias_noise;
+  hp.obs_noise = cfg->observation_noise;
+  hp.P0[0] = cfg->gyro_bias_cov; hp.P0[1] = cfg->velocity_cov; hp.P0[2] = cfg->acc_bias_cov;
+  hp.P0[3] = cfg->extrinsic_rotation_cov; hp.P0[4] = cfg->extrinsic_translation_cov;
+  hp.pos_std_thr = cfg->position_std_threshold;
+  hp.tri_translation_thr = cfg->translation_threshold; hp.huber_eps = cfg->huber_epsilon;
+  hp.est_precision = cfg->estimation_precision; hp.init_damping = cfg->initial_damping;
+  hp.outer_max = cfg->outer_loop_max_iteration; hp.inner_max = cfg->inner_loop_max_iteration;
+  hp.prune_rot_thr = cfg->prune_rotation_threshold; hp.prune_trans_thr = cfg->prune_translation_threshold;
+  hp.prune_track_thr = cfg->prune_tracking_rate_threshold;
+  memcpy(hp.R01, cfg->R_cam0_cam1, sizeof hp.R01);
+  memcpy(hp.t01, cfg->t_cam0_cam1, sizeof hp.t01);
+  memcpy(hp.chi2, cfg->chi2_table, sizeof hp.chi2);
+  hp.max_cam = d.Nmax;
+  hp.row_cap = row_cap;
+
+  const size_t F = d.F, Fc = d.Fcap, Nm = d.Nmax;
+  Params* dprm = nullptr;
+#define DA(ptr, count) do { int rc_ = dalloc(ctx, &(ptr), (count)); if (rc_) return fail(rc_); } while (0)
+  DA(dprm, 1);
+  CKC(cudaMemcpyAsync(dprm, &hp, sizeof hp, cudaMemcpyHostToDevice, ctx->st));
+  d.prm = dprm;
+  DA(d.imu, F * IMU_STRIDE);
+  DA(d.cam_id, F * Nm); DA(d.cam_phys, F * Nm); DA(d.cam, F * Nm * CAM_STRIDE); DA(d.ncam, F); DA(d.phys_used, F);
+  DA(d.P, F * (size_t)d.ld * d.ld);
+  DA(d.f_id, F * Fc); DA(d.f_mask, F * Fc); DA(d.f_flags, F * Fc); DA(d.f_pos, F * Fc * 3); DA(d.f_obs, F * Fc * Nm * 4);
+  DA(d.ord, F * Fc); DA(d.ord_tmp, F * Fc); DA(d.nlive, F); DA(d.free_stack, F * Fc); DA(d.nfree, F);
+  DA(d.h_key, F * (size_t)d.Hs); DA(d.h_val, F * (size_t)d.Hs);
+  DA(d.cand, F * Fc); DA(d.cand_status, F * Fc); DA(d.ncand, F);
+  DA(d.item_cand, F * Fc); DA(d.item_mask, F * Fc); DA(d.item_rows, F * Fc); DA(d.item_off, F * Fc); DA(d.item_rowoff, F * Fc);
+  DA(d.item_dof, F * Fc); DA(d.item_gamma, F * Fc); DA(d.item_pass, F * Fc); DA(d.nitem, F);
+  DA(d.rm_mask, F); DA(d.rm_idx, F * 2);
+  DA(d.pool, (size_t)d.pool_cap); DA(d.pool_used, 1);
+  DA(d.A, F * (size_t)d.A_elems); DA(d.m_rows, F); DA(d.m_pad, F); DA(d.n_act, F); DA(d.k_rows, F); DA(d.colmap, F * (size_t)d.nmax);
+  DA(d.T, F * (size_t)d.Tk * Tld(d)); DA(d.S, F * (size_t)d.Tk * d.Tk); DA(d.dx, F * (size_t)d.nmax);
+  DA(d.log_id, 2 * F * Fc); DA(d.log_status, 2 * F * Fc); DA(d.log_gamma, 2 * F * Fc); DA(d.log_dof, 2 * F * Fc);
+  DA(d.log_n, 2 * F); DA(d.log_upd, 2 * F * 2); DA(d.log_rm, F * 2);
+  DA(d.counters, F * 4); DA(d.err, 1); DA(d.did_reset, F); DA(d.imu_pub, F * IMU_STRIDE);
+#undef DA
+  CKC(cudaMallocHost((void**)&ctx->h_pub, F * IMU_STRIDE * sizeof(double)));
+  CKC(cudaMallocHost((void**)&ctx->h_reset, F));
+  CKC(cudaMallocHost((void**)&ctx->h_err, sizeof(unsigned)));
+  *ctx->h_err = 0;
+  // initial state: identity orientation, gravity from the caller later (set_imu_state), reset covariance
+  {
+    std::vector<double> imu0(F * IMU_STRIDE, 0.0);
+    for (size_t f = 0; f < F; ++f) {
+      imu0[f * IMU_STRIDE + MSCKF_IMU_Q + 3] = 1.0;
+      imu0[f * IMU_STRIDE + MSCKF_IMU_Q_NULL + 3] = 1.0;
+      for (int i = 0; i < 3; ++i) imu0[f * IMU_STRIDE + MSCKF_IMU_R_IC + 4 * i] = 1.0;
+      imu0[f * IMU_STRIDE + MSCKF_IMU_GRAVITY + 2] = -9.81;
+    }
+    CKC(cudaMemcpyAsync(d.imu, imu0.data(), imu0.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->st));
+    CKC(cudaStreamSynchronize(ctx->st));
+  }
+  launch_reset(d, -1, 0, ctx->st);
+  CKC(cudaStreamSynchronize(ctx->st));
+  CKC(cudaGetLastError());
+#undef CKC
+  *out = ctx;
+  return MSCKF_OK;
+}
+
+void msckf_destroy(msckf_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  if (ctx->st) cudaStreamSynchronize(ctx->st);
+  for (void* p : ctx->dev_allocs) cudaFree(p);
+  for (auto& s : ctx->stg) {
+    if (s.h) cudaFreeHost(s.h);
+    if (s.d) cudaFree(s.d);
+    if (s.done) cudaEventDestroy(s.done);
+  }
+  for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
+  if (ctx->h_pub) cudaFreeHost(ctx->h_pub);
+  if (ctx->h_reset) cudaFreeHost(ctx->h_reset);
+  if (ctx->h_err) cudaFreeHost(ctx->h_err);
+  if (ctx->st) cudaStreamDestroy(ctx->st);
+  delete ctx;
+}
+
+int msckf_sync(msckf_ctx* ctx) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  CK(cudaSetDevice(ctx->device));
+  return sync_and_check(ctx);
+}
+
+// ------------------------------------------------------------------ state I/O
+int msckf_set_imu_state(msckf_ctx* ctx, int32_t f, const double* imu) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  ARG(f >= 0 && f < ctx->d.F && imu, "filter index / pointer");
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaStreamSynchronize(ctx->st));
+  CK(cudaMemcpy(ctx->d.imu + (size_t)f * IMU_STRIDE, imu, IMU_STRIDE * sizeof(double), cudaMemcpyHostToDevice));
+  return MSCKF_OK;
+}
+int msckf_get_imu_state(msckf_ctx* ctx, int32_t f, double* imu) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  ARG(f >= 0 && f < ctx->d.F && imu, "filter index / pointer");
+  CK(cudaSetDevice(ctx->device));
+  int rc = sync_and_check(ctx);
+  if (rc) return rc;
+  CK(cudaMemcpy(imu, ctx->d.imu + (size_t)f * IMU_STRIDE, IMU_STRIDE * sizeof(double), cudaMemcpyDeviceToHost));
+  return MSCKF_OK;
+}
+int msckf_get_imu_states(msckf_ctx* ctx, double* imu) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  ARG(imu, "pointer");
+  CK(cudaSetDevice(ctx->device));
+  int rc = sync_and_check(ctx);
+  if (rc) return rc;
+  CK(cudaMemcpy(imu, ctx->d.imu, (size_t)ctx->d.F * IMU_STRIDE * sizeof(double), cudaMemcpyDeviceToHost));
+  return MSCKF_OK;
+}
+int msckf_get_cam_states(msckf_ctx* ctx, int32_t f, int32_t* n_cam, int64_t* ids, double* cams) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  ARG(f >= 0 && f < ctx->d.F && n_cam, "filter index / pointer");
+  CK(cudaSetDevice(ctx->device));
+  int rc = sync_and_check(ctx);
+  if (rc) return rc;
+  const Dev& d = ctx->d;
+  int n = 0;
+  CK(cudaMemcpy(&n, d.ncam + f, sizeof(int), cudaMemcpyDeviceToHost));
+  *n_cam = n;
+  if (ids && n) CK(cudaMemcpy(ids, d.cam_id + (size_t)f * d.Nmax, n * sizeof(int64_t), cudaMemcpyDeviceToHost));
+  if (cams && n) CK(cudaMemcpy(cams, d.cam + (size_t)f * d.Nmax * CAM_STRIDE, (size_t)n * CAM_STRIDE * sizeof(double), cudaMemcpyDeviceToHost));
+  return MSCKF_OK;
+}
+int msckf_set_cam_states(msckf_ctx* ctx, int32_t f, int32_t n, const int64_t* ids, const double* cams) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  const Dev& d = ctx->d;
+  ARG(f >= 0 && f < d.F && n >= 0 && n <= d.Nmax && (n == 0 || (ids && cams)), "filter index / count / pointers");
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaStreamSynchronize(ctx->st));
+  // keeps the physical slots of ids that are already present (their observations stay valid)
+  int n_old = 0;
+  CK(cudaMemcpy(&n_old, d.ncam + f, sizeof(int), cudaMemcpyDeviceToHost));
+  std::vector<long long> old_ids(d.Nmax);
+  std::vector<int> old_phys(d.Nmax), phys(d.Nmax);
+  if (n_old) {
+    CK(cudaMemcpy(old_ids.data(), d.cam_id + (size_t)f * d.Nmax, n_old * sizeof(long long), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(old_phys.data(), d.cam_phys + (size_t)f * d.Nmax, n_old * sizeof(int), cudaMemcpyDeviceToHost));
+  }
+  unsigned long long used = 0;
+  std::vector<char> have(n, 0);
+  for (int i = 0; i < n; ++i)
+    for (int j = 0; j < n_old; ++j)
+      if (old_ids[j] == ids[i]) { phys[i] = old_phys[j]; used |= 1ull << phys[i]; have[i] = 1; }
+  for (int i = 0; i < n; ++i)
+    if (!have[i]) {
+      int s = 0;
+      while ((used >> s) & 1ull) ++s;
+      phys[i] = s;
+      used |= 1ull << s;
+    }
+  if (n) {
+    CK(cudaMemcpy(d.cam_id + (size_t)f * d.Nmax, ids, n * sizeof(int64_t), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d.cam_phys + (size_t)f * d.Nmax, phys.data(), n * sizeof(int), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d.cam + (size_t)f * d.Nmax * CAM_STRIDE, cams, (size_t)n * CAM_STRIDE * sizeof(double), cudaMemcpyHostToDevice));
+  }
+  CK(cudaMemcpy(d.ncam + f, &n, sizeof(int), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d.phys_used + f, &used, sizeof(used), cudaMemcpyHostToDevice));
+  return MSCKF_OK;
+}
+int msckf_get_cov(msckf_ctx* ctx, int32_t f, double* P, int32_t n) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  const Dev& d = ctx->d;
+  ARG(f >= 0 && f < d.F && P && n >= NI && n <= d.nmax, "filter index / size");
+  CK(cudaSetDevice(ctx->device));
+  int rc = sync_and_check(ctx);
+  if (rc) return rc;
+  CK(cudaMemcpy2D(P, (size_t)n * sizeof(double), d.P + (size_t)f * d.ld * d.ld, (size_t)d.ld * sizeof(double),
+                  (size_t)n * sizeof(double), n, cudaMemcpyDeviceToHost));
+  return MSCKF_OK;
+}
+int msckf_set_cov(msckf_ctx* ctx, int32_t f, const double* P, int32_t n) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  const Dev& d = ctx->d;
+  ARG(f >= 0 && f < d.F && P && n >= NI && n <= d.nmax, "filter index / size");
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaStreamSynchronize(ctx->st));
+  CK(cudaMemcpy2D(d.P + (size_t)f * d.ld * d.ld, (size_t)d.ld * sizeof(double), P, (size_t)n * sizeof(double),
+                  (size_t)n * sizeof(double), n, cudaMemcpyHostToDevice));
+  return MSCKF_OK;
+}
+
+// host copy of one filter's landmark tables
+struct StoreDump {
+  int nlive = 0, ncam = 0;
+  std::vector<int> ord, flags, phys;
+  std::vector<long long> ids;
+  std::vector<unsigned long long> mask;
+};
+static int dump_store(msckf_ctx* ctx, int f, StoreDump& s) {
+  const Dev& d = ctx->d;
+  int rc = sync_and_check(ctx);
+  if (rc) return rc;
+  CK(cudaMemcpy(&s.nlive, d.nlive + f, sizeof(int), cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(&s.ncam, d.ncam + f, sizeof(int), cudaMemcpyDeviceToHost));
+  s.ord.resize(d.Fcap); s.flags.resize(d.Fcap); s.ids.resize(d.Fcap); s.mask.resize(d.Fcap); s.phys.resize(d.Nmax);
+  CK(cudaMemcpy(s.ord.data(), d.ord + (size_t)f * d.Fcap, d.Fcap * sizeof(int), cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(s.flags.data(), d.f_flags + (size_t)f * d.Fcap, d.Fcap * sizeof(int), cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(s.ids.data(), d.f_id + (size_t)f * d.Fcap, d.Fcap * sizeof(long long), cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(s.mask.data(), d.f_mask + (size_t)f * d.Fcap, d.Fcap * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(s.phys.data(), d.cam_phys + (size_t)f * d.Nmax, d.Nmax * sizeof(int), cudaMemcpyDeviceToHost));
+  return 0;
+}
+static int find_slot(const StoreDump& s, long long id) {
+  for (int j = 0; j < s.nlive; ++j)
+    if (s.ids[s.ord[j]] == id) return s.ord[j];
+  return -1;
+}
+
+int msckf_get_features(msckf_ctx* ctx, int32_t f, int32_t* n_features, int64_t* ids, uint64_t* obs_mask, uint8_t* is_init,
+                       double* position, double* obs) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  const Dev& d = ctx->d;
+  ARG(f >= 0 && f < d.F && n_features, "filter index / pointer");
+  CK(cudaSetDevice(ctx->device));
+  StoreDump s;
+  int rc = dump_store(ctx, f, s);
+  if (rc) return rc;
+  *n_features = s.nlive;
+  std::vector<double> pos, ob;
+  if (position) { pos.resize((size_t)d.Fcap * 3); CK(cudaMemcpy(pos.data(), d.f_pos + (size_t)f * d.Fcap * 3, pos.size() * 8, cudaMemcpyDeviceToHost)); }
+  if (obs) { ob.resize((size_t)d.Fcap * d.Nmax * 4); CK(cudaMemcpy(ob.data(), d.f_obs + (size_t)f * d.Fcap * d.Nmax * 4, ob.size() * 8, cudaMemcpyDeviceToHost)); }
+  for (int j = 0; j < s.nlive; ++j) {
+    const int slot = s.ord[j];
+    if (ids) ids[j] = s.ids[slot];
+    if (is_init) is_init[j] = (s.flags[slot] & FF_INIT) ? 1 : 0;
+    if (obs_mask) {
+      uint64_t lm = 0;
+      for (int c = 0; c < s.ncam; ++c)
+        if ((s.mask[slot] >> s.phys[c]) & 1ull) lm |= 1ull << c;
+      obs_mask[j] = lm;
+    }
+    if (position) for (int k = 0; k < 3; ++k) position[3 * j + k] = pos[(size_t)slot * 3 + k];
+    if (obs)
+      for (int c = 0; c < d.Nmax; ++c)
+        for (int k = 0; k < 4; ++k)
+          obs[((size_t)j * d.Nmax + c) * 4 + k] = (c < s.ncam) ? ob[((size_t)slot * d.Nmax + s.phys[c]) * 4 + k] : 0.0;
+  }
+  return MSCKF_OK;
+}
+
+int msckf_set_feature_position(msckf_ctx* ctx, int32_t f, int64_t id, const double* position, int32_t is_initialized) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  const Dev& d = ctx->d;
+  ARG(f >= 0 && f < d.F && position, "filter index / pointer");
+  CK(cudaSetDevice(ctx->device));
+  StoreDump s;
+  int rc = dump_store(ctx, f, s);
+  if (rc) return rc;
+  const int slot = find_slot(s, id);
+  ARG(slot >= 0, "unknown feature id");
+  CK(cudaMemcpy(d.f_pos + ((size_t)f * d.Fcap + slot) * 3, position, 3 * sizeof(double), cudaMemcpyHostToDevice));
+  int fl = (s.flags[slot] & ~FF_INIT) | (is_initialized ? FF_INIT : 0);
+  CK(cudaMemcpy(d.f_flags + (size_t)f * d.Fcap + slot, &fl, sizeof(int), cudaMemcpyHostToDevice));
+  return MSCKF_OK;
+}
+
+// ------------------------------------------------------------------ stage enqueue helpers
+static void enqueue_lost_stage(msckf_ctx* ctx) {
+  const Dev& d = ctx->d;
+  cudaMemsetAsync(d.pool_used, 0, sizeof(unsigned long long), ctx->st);
+  launch_classify_lost(d, ctx->st);
+  launch_triangulate_store(d, ctx->st);
+  launch_plan_items(d, 0, ctx->st);
+  launch_jacobian_gate(d, ctx->st);
+  launch_plan_stack(d, 0, ctx->st);
+  launch_stack(d, ctx->st);
+  launch_qr(d, ctx->st);
+  launch_update(d, 0, ctx->st);
+}
+static void enqueue_prune_stage(msckf_ctx* ctx) {
+  const Dev& d = ctx->d;
+  cudaMemsetAsync(d.pool_used, 0, sizeof(unsigned long long), ctx->st);
+  launch_prune_select(d, ctx->st);
+  launch_triangulate_store(d, ctx->st);
+  launch_plan_items(d, 1, ctx->st);
+  launch_jacobian_gate(d, ctx->st);
+  launch_plan_stack(d, 1, ctx->st);
+  launch_stack(d, ctx->st);
+  launch_qr(d, ctx->st);
+  launch_update(d, 1, ctx->st);
+  launch_remove_cams(d, ctx->st);
+}
+
+int msckf_propagate(msckf_ctx* ctx, const int32_t* imu_off, const double* ts, const double* gyro, const double* acc) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  ARG(imu_off, "imu_off");
+  CK(cudaSetDevice(ctx->device));
+  const int F = ctx->d.F, n = imu_off[F];
+  ARG(n == 0 || (ts && gyro && acc), "sample pointers");
+  Packer p;
+  stage_begin(ctx, p);
+  const size_t o0 = p.add(imu_off, (F + 1) * sizeof(int)), o1 = p.add(ts, n * sizeof(double));
+  const size_t o2 = p.add(gyro, n * 3 * sizeof(double)), o3 = p.add(acc, n * 3 * sizeof(double));
+  int rc = stage_commit(ctx, p);
+  if (rc) return rc;
+  char* b = p.s->d;
+  launch_propagate(ctx->d, (const int*)(b + o0), (const double*)(b + o1), (const double*)(b + o2), (const double*)(b + o3), ctx->st);
+  stage_end(ctx, p);
+  CK(cudaGetLastError());
+  return MSCKF_OK;
+}
+
+int msckf_augment(msckf_ctx* ctx, const int64_t* cam_ids) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  ARG(cam_ids, "cam_ids");
+  CK(cudaSetDevice(ctx->device));
+  Packer p;
+  stage_begin(ctx, p);
+  const size_t o0 = p.add(cam_ids, ctx->d.F * sizeof(int64_t));
+  int rc = stage_commit(ctx, p);
+  if (rc) return rc;
+  launch_augment(ctx->d, (const long long*)(p.s->d + o0), ctx->st);
+  stage_end(ctx, p);
+  CK(cudaGetLastError());
+  return MSCKF_OK;
+}
+
+int msckf_add_observations(msckf_ctx* ctx, const int32_t* feat_off, const int64_t* ids, const double* uv) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  ARG(feat_off, "feat_off");
+  CK(cudaSetDevice(ctx->device));
+  const int F = ctx->d.F, n = feat_off[F];
+  ARG(n == 0 || (ids && uv), "feature pointers");
+  Packer p;
+  stage_begin(ctx, p);
+  const size_t o0 = p.add(feat_off, (F + 1) * sizeof(int)), o1 = p.add(ids, n * sizeof(int64_t)), o2 = p.add(uv, (size_t)n * 4 * sizeof(double));
+  int rc = stage_commit(ctx, p);
+  if (rc) return rc;
+  char* b = p.s->d;
+  launch_observe(ctx->d, (const int*)(b + o0), (const long long*)(b + o1), (const double*)(b + o2), ctx->st);
+  stage_end(ctx, p);
+  CK(cudaGetLastError());
+  return MSCKF_OK;
+}
+
+int msckf_remove_lost_features(msckf_ctx* ctx) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  CK(cudaSetDevice(ctx->device));
+  enqueue_lost_stage(ctx);
+  CK(cudaGetLastError());
+  return MSCKF_OK;
+}
+
+int msckf_prune_cam_states(msckf_ctx* ctx) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  CK(cudaSetDevice(ctx->device));
+  enqueue_prune_stage(ctx);
+  CK(cudaGetLastError());
+  return MSCKF_OK;
+}
+
+int msckf_online_reset(msckf_ctx* ctx, uint8_t* did_reset) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  CK(cudaSetDevice(ctx->device));
+  launch_finish_frame(ctx->d, 1, ctx->st);
+  CK(cudaMemcpyAsync(ctx->h_reset, ctx->d.did_reset, ctx->d.F, cudaMemcpyDeviceToHost, ctx->st));
+  int rc = sync_and_check(ctx);
+  if (rc) return rc;
+  if (did_reset) memcpy(did_reset, ctx->h_reset, ctx->d.F);
+  return MSCKF_OK;
+}
+
+int msckf_reset(msckf_ctx* ctx, int32_t f) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  ARG(f >= 0 && f < ctx->d.F, "filter index");
+  CK(cudaSetDevice(ctx->device));
+  launch_reset(ctx->d, f, 1, ctx->st);
+  CK(cudaGetLastError());
+  return MSCKF_OK;
+}
+
+int msckf_feature_callback_async(msckf_ctx* ctx, const int32_t* imu_off, const double* ts, const double* gyro, const double* acc,
+                                 const int64_t* cam_ids, const int32_t* feat_off, const int64_t* ids, const double* uv) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  ARG(imu_off && cam_ids && feat_off, "offset / id pointers");
+  ARG(!ctx->frame_pending, "previous frame not collected");
+  CK(cudaSetDevice(ctx->device));
+  const Dev& d = ctx->d;
+  const int F = d.F, ni = imu_off[F], nf = feat_off[F];
+  ARG((ni == 0 || (ts && gyro && acc)) && (nf == 0 || (ids && uv)), "sample / feature pointers");
+  Packer p;
+  stage_begin(ctx, p);
+  const size_t o0 = p.add(imu_off, (F + 1) * sizeof(int)), o1 = p.add(ts, ni * sizeof(double));
+  const size_t o2 = p.add(gyro, (size_t)ni * 3 * sizeof(double)), o3 = p.add(acc, (size_t)ni * 3 * sizeof(double));
+  const size_t o4 = p.add(cam_ids, F * sizeof(int64_t)), o5 = p.add(feat_off, (F + 1) * sizeof(int));
+  const size_t o6 = p.add(ids, nf * sizeof(int64_t)), o7 = p.add(uv, (size_t)nf * 4 * sizeof(double));
+  int rc = stage_commit(ctx, p);
+  if (rc) return rc;
+  char* b = p.s->d;
+  const bool tm = ctx->timing;
+  if (tm) cudaEventRecord(ctx->ev[0], ctx->st);
+  launch_propagate(d, (const int*)(b + o0), (const double*)(b + o1), (const double*)(b + o2), (const double*)(b + o3), ctx->st);
+  launch_augment(d, (const long long*)(b + o4), ctx->st);
+  if (tm) cudaEventRecord(ctx->ev[1], ctx->st);
+  launch_observe(d, (const int*)(b + o5), (const long long*)(b + o6), (const double*)(b + o7), ctx->st);
+  if (tm) cudaEventRecord(ctx->ev[2], ctx->st);
+  enqueue_lost_stage(ctx);
+  if (tm) cudaEventRecord(ctx->ev[3], ctx->st);
+  enqueue_prune_stage(ctx);
+  if (tm) cudaEventRecord(ctx->ev[4], ctx->st);
+  launch_finish_frame(d, 1, ctx->st);
+  if (tm) cudaEventRecord(ctx->ev[5], ctx->st);
+  stage_end(ctx, p);
+  CK(cudaMemcpyAsync(ctx->h_pub, d.imu_pub, (size_t)F * IMU_STRIDE * sizeof(double), cudaMemcpyDeviceToHost, ctx->st));
+  CK(cudaMemcpyAsync(ctx->h_reset, d.did_reset, F, cudaMemcpyDeviceToHost, ctx->st));
+  CK(cudaMemcpyAsync(ctx->h_err, d.err, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->st));
+  CK(cudaGetLastError());
+  ctx->frame_pending = true;
+  return MSCKF_OK;
+}
+
+int msckf_collect(msckf_ctx* ctx, double* imu_out, uint8_t* did_reset) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  ARG(ctx->frame_pending, "no frame in flight");
+  CK(cudaSetDevice(ctx->device));
+  ctx->frame_pending = false;
+  CK(cudaStreamSynchronize(ctx->st));
+  CK(cudaGetLastError());
+  int rc = check_device_errors(ctx);
+  if (rc) return rc;
+  if (imu_out) memcpy(imu_out, ctx->h_pub, (size_t)ctx->d.F * IMU_STRIDE * sizeof(double));
+  if (did_reset) memcpy(did_reset, ctx->h_reset, ctx->d.F);
+  if (ctx->timing) {
+    for (int i = 0; i < 4; ++i) cudaEventElapsedTime(&ctx->last_ms[i], ctx->ev[i], ctx->ev[i + 1]);
+    float fin = 0;
+    cudaEventElapsedTime(&fin, ctx->ev[4], ctx->ev[5]);
+    cudaEventElapsedTime(&ctx->last_ms[4], ctx->ev[0], ctx->ev[5]);
+    ctx->last_ms[3] += fin;
+  }
+  return MSCKF_OK;
+}
+
+int msckf_feature_callback(msckf_ctx* ctx, const int32_t* imu_off, const double* ts, const double* gyro, const double* acc,
+                           const int64_t* cam_ids, const int32_t* feat_off, const int64_t* ids, const double* uv,
+                           double* imu_out, uint8_t* did_reset) {
+  int rc = msckf_feature_callback_async(ctx, imu_off, ts, gyro, acc, cam_ids, feat_off, ids, uv);
+  if (rc) return rc;
+  return msckf_collect(ctx, imu_out, did_reset);
+}
+
+int msckf_set_timing(msckf_ctx* ctx, int32_t enabled) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  ctx->timing = enabled != 0;
+  return MSCKF_OK;
+}
+int msckf_last_timing(msckf_ctx* ctx, float* ms) {
+  if (!ctx || !ms) return MSCKF_ERR_ARG;
+  memcpy(ms, ctx->last_ms, sizeof ctx->last_ms);
+  return MSCKF_OK;
+}
+
+// ------------------------------------------------------------------ logs / counters
+int msckf_get_stage_log(msckf_ctx* ctx, int32_t f, int32_t stage, int32_t* n_entries, int64_t* feature_ids, int32_t* status,
+                        double* gamma, int32_t* dof, int32_t* update_rows, int32_t* update_cols, int64_t* removed_cam_ids) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  const Dev& d = ctx->d;
+  ARG(f >= 0 && f < d.F && (stage == 0 || stage == 1) && n_entries, "filter / stage / pointer");
+  CK(cudaSetDevice(ctx->device));
+  int rc = sync_and_check(ctx);
+  if (rc) return rc;
+  int n = 0;
+  CK(cudaMemcpy(&n, d.log_n + stage * d.F + f, sizeof(int), cudaMemcpyDeviceToHost));
+  *n_entries = n;
+  const size_t base = ((size_t)stage * d.F + f) * d.Fcap;
+  if (n && feature_ids) CK(cudaMemcpy(feature_ids, d.log_id + base, n * sizeof(int64_t), cudaMemcpyDeviceToHost));
+  if (n && status) CK(cudaMemcpy(status, d.log_status + base, n * sizeof(int), cudaMemcpyDeviceToHost));
+  if (n && gamma) CK(cudaMemcpy(gamma, d.log_gamma + base, n * sizeof(double), cudaMemcpyDeviceToHost));
+  if (n && dof) CK(cudaMemcpy(dof, d.log_dof + base, n * sizeof(int), cudaMemcpyDeviceToHost));
+  int upd[2] = {0, 0};
+  CK(cudaMemcpy(upd, d.log_upd + ((size_t)stage * d.F + f) * 2, sizeof upd, cudaMemcpyDeviceToHost));
+  if (update_rows) *update_rows = upd[0];
+  if (update_cols) *update_cols = upd[1];
+  if (removed_cam_ids && stage == 1) CK(cudaMemcpy(removed_cam_ids, d.log_rm + 2 * (size_t)f, 2 * sizeof(int64_t), cudaMemcpyDeviceToHost));
+  return MSCKF_OK;
+}
+
+int msckf_get_counters(msckf_ctx* ctx, int64_t* counters) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  ARG(counters, "pointer");
+  CK(cudaSetDevice(ctx->device));
+  int rc = sync_and_check(ctx);
+  if (rc) return rc;
+  CK(cudaMemcpy(counters, ctx->d.counters, (size_t)ctx->d.F * 4 * sizeof(int64_t), cudaMemcpyDeviceToHost));
+  return MSCKF_OK;
+}
+
+// ------------------------------------------------------------------ directly callable pieces
+int msckf_triangulate(msckf_ctx* ctx, int32_t n, const int32_t* obs_off, const double* uv, const double* cam_q, const double* cam_p,
+                      double* position, uint8_t* valid, int32_t* lm_solves) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  ARG(n >= 0 && obs_off && position && valid, "count / pointers");
+  if (n == 0) return MSCKF_OK;
+  CK(cudaSetDevice(ctx->device));
+  const int total = obs_off[n];
+  ARG(total > 0 && uv && cam_q && cam_p, "observation pointers");
+  int max_obs = 0;
+  for (int i = 0; i < n; ++i) {
+    const int M = obs_off[i + 1] - obs_off[i];
+    ARG(M >= 1, "every landmark needs at least one observation");
+    max_obs = std::max(max_obs, M);
+  }
+  ARG(max_obs <= 200, "at most 200 observations per landmark");
+  Packer p;
+  stage_begin(ctx, p);
+  const size_t o0 = p.add(obs_off, (n + 1) * sizeof(int)), o1 = p.add(uv, (size_t)total * 4 * sizeof(double));
+  const size_t o2 = p.add(cam_q, (size_t)total * 4 * sizeof(double)), o3 = p.add(cam_p, (size_t)total * 3 * sizeof(double));
+  int rc = stage_commit(ctx, p);
+  if (rc) return rc;
+  double* dpos = nullptr;
+  unsigned char* dval = nullptr;
+  int* dsol = nullptr;
+  CK(cudaMalloc((void**)&dpos, (size_t)n * 3 * sizeof(double)));
+  CK(cudaMalloc((void**)&dval, n));
+  CK(cudaMalloc((void**)&dsol, n * sizeof(int)));
+  char* b = p.s->d;
+  launch_triangulate_raw(ctx->d, n, (const int*)(b + o0), (const double*)(b + o1), (const double*)(b + o2), (const double*)(b + o3), dpos,
+                         dval, dsol, max_obs, ctx->st);
+  stage_end(ctx, p);
+  rc = sync_and_check(ctx);
+  if (!rc) {
+    cudaMemcpy(position, dpos, (size_t)n * 3 * sizeof(double), cudaMemcpyDeviceToHost);
+    cudaMemcpy(valid, dval, n, cudaMemcpyDeviceToHost);
+    if (lm_solves) cudaMemcpy(lm_solves, dsol, n * sizeof(int), cudaMemcpyDeviceToHost);
+  }
+  cudaFree(dpos); cudaFree(dval); cudaFree(dsol);
+  return rc;
+}
+
+int msckf_feature_jacobian(msckf_ctx* ctx, int32_t f, int64_t feature_id, int32_t n_cam_ids, const int64_t* cam_ids, int32_t* rows_out,
+                           double* H, double* r, int32_t n_state) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  const Dev& d = ctx->d;
+  ARG(f >= 0 && f < d.F && cam_ids && rows_out && H && r && n_cam_ids > 0, "filter / pointers");
+  CK(cudaSetDevice(ctx->device));
+  StoreDump s;
+  int rc = dump_store(ctx, f, s);
+  if (rc) return rc;
+  ARG(n_state == NI + 6 * s.ncam, "n_state must be 21 + 6 * (number of camera states)");
+  const int slot = find_slot(s, feature_id);
+  ARG(slot >= 0, "unknown feature id");
+  std::vector<long long> ids(d.Nmax);
+  if (s.ncam) CK(cudaMemcpy(ids.data(), d.cam_id + (size_t)f * d.Nmax, s.ncam * sizeof(long long), cudaMemcpyDeviceToHost));
+  unsigned long long im = 0;
+  for (int k = 0; k < n_cam_ids; ++k)
+    for (int c = 0; c < s.ncam; ++c)
+      if (ids[c] == cam_ids[k] && ((s.mask[slot] >> s.phys[c]) & 1ull)) im |= 1ull << s.phys[c];
+  const int M = __builtin_popcountll(im);
+  ARG(M >= 1, "landmark not observed by any of the given camera states");
+  const int rows = 4 * M - 3;
+  const long long need = (long long)4 * M * (6 * M + 4) + (long long)rows * 6 * M + (long long)rows * rows;
+  ARG(need <= d.pool_cap, "jacobian pool too small");
+  // a one-item work list for filter f
+  CK(cudaMemsetAsync(d.nitem, 0, d.F * sizeof(int), ctx->st));
+  CK(cudaMemsetAsync(d.ncand, 0, d.F * sizeof(int), ctx->st));
+  const size_t b = (size_t)f * d.Fcap;
+  const int one = 1, zero = 0, dof = std::min(M, 99);
+  const long long off0 = 0;
+  CK(cudaMemcpyAsync(d.cand + b, &slot, sizeof(int), cudaMemcpyHostToDevice, ctx->st));
+  CK(cudaMemcpyAsync(d.item_cand + b, &zero, sizeof(int), cudaMemcpyHostToDevice, ctx->st));
+  CK(cudaMemcpyAsync(d.item_mask + b, &im, sizeof(im), cudaMemcpyHostToDevice, ctx->st));
+  CK(cudaMemcpyAsync(d.item_rows + b, &rows, sizeof(int), cudaMemcpyHostToDevice, ctx->st));
+  CK(cudaMemcpyAsync(d.item_dof + b, &dof, sizeof(int), cudaMemcpyHostToDevice, ctx->st));
+  CK(cudaMemcpyAsync(d.item_off + b, &off0, sizeof(off0), cudaMemcpyHostToDevice, ctx->st));
+  CK(cudaMemcpyAsync(d.nitem + f, &one, sizeof(int), cudaMemcpyHostToDevice, ctx->st));
+  CK(cudaStreamSynchronize(ctx->st));      // the small host sources above live on this stack frame
+  launch_jacobian_gate(d, ctx->st);
+  double* dH = nullptr;
+  CK(cudaMalloc((void**)&dH, ((size_t)rows * n_state + rows) * sizeof(double)));
+  launch_export_item_dense(d, f, dH, dH + (size_t)rows * n_state, n_state, ctx->st);
+  rc = sync_and_check(ctx);
+  if (!rc) {
+    cudaMemcpy(H, dH, (size_t)rows * n_state * sizeof(double), cudaMemcpyDeviceToHost);
+    cudaMemcpy(r, dH + (size_t)rows * n_state, rows * sizeof(double), cudaMemcpyDeviceToHost);
+    *rows_out = rows;
+  }
+  cudaFree(dH);
+  cudaMemsetAsync(d.nitem, 0, d.F * sizeof(int), ctx->st);
+  return rc;
+}
+
+int msckf_measurement_jacobian(msckf_ctx* ctx, int32_t f, int64_t cam_id, int64_t feature_id, double* H_x, double* H_f, double* r) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  const Dev& d = ctx->d;
+  ARG(f >= 0 && f < d.F && H_x && H_f && r, "filter / pointers");
+  CK(cudaSetDevice(ctx->device));
+  StoreDump s;
+  int rc = dump_store(ctx, f, s);
+  if (rc) return rc;
+  const int slot = find_slot(s, feature_id);
+  ARG(slot >= 0, "unknown feature id");
+  std::vector<long long> ids(d.Nmax);
+  if (s.ncam) CK(cudaMemcpy(ids.data(), d.cam_id + (size_t)f * d.Nmax, s.ncam * sizeof(long long), cudaMemcpyDeviceToHost));
+  int c = -1;
+  for (int k = 0; k < s.ncam; ++k)
+    if (ids[k] == cam_id) c = k;
+  ARG(c >= 0 && ((s.mask[slot] >> s.phys[c]) & 1ull), "camera state unknown or does not observe the landmark");
+  double* dout = nullptr;
+  CK(cudaMalloc((void**)&dout, 40 * sizeof(double)));
+  launch_measurement_jacobian(d, f, c, slot, dout, ctx->st);
+  rc = sync_and_check(ctx);
+  double out[40];
+  if (!rc) {
+    cudaMemcpy(out, dout, sizeof out, cudaMemcpyDeviceToHost);
+    memcpy(H_x, out, 24 * sizeof(double));
+    memcpy(H_f, out + 24, 12 * sizeof(double));
+    memcpy(r, out + 36, 4 * sizeof(double));
+  }
+  cudaFree(dout);
+  return rc;
+}
+
+int msckf_gating_test(msckf_ctx* ctx, int32_t f, const double* H, const double* r, int32_t m, int32_t n_state, int32_t dof,
+                      double* gamma, int32_t* pass) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  const Dev& d = ctx->d;
+  ARG(f >= 0 && f < d.F && H && r && m > 0 && dof >= 1 && dof <= 99 && n_state >= NI && n_state <= d.nmax, "filter / sizes / dof");
+  CK(cudaSetDevice(ctx->device));
+  double* buf = nullptr;
+  const size_t nH = (size_t)m * n_state, nscr = nH + (size_t)m * m + m;
+  CK(cudaMalloc((void**)&buf, (nH + m + nscr + 2) * sizeof(double)));
+  CK(cudaMemcpy(buf, H, nH * sizeof(double), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(buf + nH, r, m * sizeof(double), cudaMemcpyHostToDevice));
+  double* dg = buf + nH + m + nscr;
+  int* dp = (int*)(dg + 1);
+  launch_gate_dense(d, f, buf, buf + nH, m, n_state, dof, buf + nH + m, dg, dp, ctx->st);
+  int rc = sync_and_check(ctx);
+  if (!rc || rc == MSCKF_ERR_NUMERIC) {
+    double g;
+    int pz;
+    cudaMemcpy(&g, dg, sizeof g, cudaMemcpyDeviceToHost);
+    cudaMemcpy(&pz, dp, sizeof pz, cudaMemcpyDeviceToHost);
+    if (gamma) *gamma = g;
+    if (pass) *pass = pz;
+  }
+  cudaFree(buf);
+  return rc;
+}
+
+int msckf_measurement_update(msckf_ctx* ctx, int32_t f, const double* H, const double* r, int32_t m, int32_t n_state) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  const Dev& d = ctx->d;
+  ARG(f >= 0 && f < d.F && n_state >= NI && n_state <= d.nmax, "filter / size");
+  if (m <= 0) return MSCKF_OK;                       // msckf.py:544-545
+  ARG(H && r, "pointers");
+  CK(cudaSetDevice(ctx->device));
+  const long long mp = std::max(4, (m + 3) / 4 * 4);
+  ARG(mp * (n_state + 1) <= d.A_elems, "H has more rows than max_rows allows");
+  int ncam = 0;
+  int rc = sync_and_check(ctx);
+  if (rc) return rc;
+  CK(cudaMemcpy(&ncam, d.ncam + f, sizeof(int), cudaMemcpyDeviceToHost));
+  ARG(n_state == NI + 6 * ncam, "n_state must be 21 + 6 * (number of camera states)");
+  double* buf = nullptr;
+  const size_t nH = (size_t)m * n_state;
+  CK(cudaMalloc((void**)&buf, (nH + m) * sizeof(double)));
+  CK(cudaMemcpy(buf, H, nH * sizeof(double), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(buf + nH, r, m * sizeof(double), cudaMemcpyHostToDevice));
+  launch_load_dense_H(d, f, buf, buf + nH, m, n_state, ctx->st);
+  launch_qr(d, ctx->st);
+  launch_update(d, 0, ctx->st);
+  rc = sync_and_check(ctx);
+  cudaFree(buf);
+  return rc;
+}
+
+int msckf_find_redundant_cam_states(msckf_ctx* ctx, int32_t f, int64_t* cam_ids) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  ARG(f >= 0 && f < ctx->d.F && cam_ids, "filter / pointer");
+  CK(cudaSetDevice(ctx->device));
+  long long* dout = nullptr;
+  CK(cudaMalloc((void**)&dout, 2 * sizeof(long long)));
+  launch_find_redundant(ctx->d, f, dout, ctx->st);
+  int rc = sync_and_check(ctx);
+  if (!rc) cudaMemcpy(cam_ids, dout, 2 * sizeof(long long), cudaMemcpyDeviceToHost);
+  cudaFree(dout);
+  return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,478 @@
+// IMU propagation (process_model / predict_new_state, msckf.py:291-380, jit_utils.py:6-135),
+// state augmentation (msckf.py:385-407, jit_utils.py:137-167), camera-state removal
+// (msckf.py:803-818) and online reset (msckf.py:820-886).  One CTA per filter.
+#include "msckf_dev.cuh"
+#include "kernels.h"
+
+namespace msckf {
+
+constexpr int PT = 256;   // threads per CTA for the per-filter kernels in this file
+
+// ------------------------------------------------------------------ RK4 state prediction (thread 0)
+// jit_utils.py:46-128, including the stale-skew quirk: the skew matrix built from the
+// normalised dq(dt) (lines 80-84) is re-used for R(dq(dt/2)) (line 94) and R(q) (line 104).
+__device__ void predict_new_state(double dt, const double* gyro, const double* acc, const double* g,
+                                  double* q, double* v, double* p) {
+  const double gn = norm3(gyro);
+  const double Om[16] = {0, gyro[2], -gyro[1], gyro[0],
+                         -gyro[2], 0, gyro[0], gyro[1],
+                         gyro[1], -gyro[0], 0, gyro[2],
+                         -gyro[0], -gyro[1], -gyro[2], 0};
+  double dq[4], dq2[4];
+  if (gn > 1e-5) {
+    const double c1 = cos(gn * dt * 0.5), s1 = sin(gn * dt * 0.5) / gn;
+    const double c2 = cos(gn * dt * 0.25), s2 = sin(gn * dt * 0.25) / gn;
+    for (int i = 0; i < 4; ++i) {
+      double a = 0, b = 0;
+      for (int j = 0; j < 4; ++j) {
+        const double e = (i == j) ? 1.0 : 0.0;
+        a += (c1 * e + s1 * Om[4 * i + j]) * q[j];
+        b += (c2 * e + s2 * Om[4 * i + j]) * q[j];
+      }
+      dq[i] = a; dq2[i] = b;
+    }
+  } else {
+    const double c1 = cos(gn * dt * 0.5), c2 = cos(gn * dt * 0.25);
+    for (int i = 0; i < 4; ++i) {
+      double a = 0, b = 0;
+      for (int j = 0; j < 4; ++j) {
+        const double e = (i == j) ? 1.0 : 0.0;
+        a += (c1 * (e + Om[4 * i + j] * dt * 0.5)) * q[j];
+        b += (c2 * (e + Om[4 * i + j] * dt * 0.25)) * q[j];
+      }
+      dq[i] = a; dq2[i] = b;
+    }
+  }
+  double n = norm4(dq);
+  for (int i = 0; i < 4; ++i) dq[i] /= n;
+  const double stale[3] = {dq[0], dq[1], dq[2]};
+  double RdT[9], Rd2T[9], R[9];
+  rot_from_parts(dq, dq[3], stale, RdT);            // dR_dt (transposed when applied)
+  n = norm4(dq2);
+  for (int i = 0; i < 4; ++i) dq2[i] /= n;
+  rot_from_parts(dq2, dq2[3], stale, Rd2T);
+  n = norm4(q);
+  const double qn[4] = {q[0] / n, q[1] / n, q[2] / n, q[3] / n};
+  rot_from_parts(qn, qn[3], stale, R);
+
+  double k1v[3], k2v[3], k4v[3], tmp[3];
+  mat3t_vec(R, acc, tmp);                            // R^T acc  (R.T @ acc)
+  for (int i = 0; i < 3; ++i) k1v[i] = tmp[i] + g[i];
+  // dR_dt2_transpose @ acc with dR_dt2_transpose = (...)^T  ->  (Rd2T)^T acc
+  mat3t_vec(Rd2T, acc, tmp);
+  for (int i = 0; i < 3; ++i) k2v[i] = tmp[i] + g[i];   // k3_v_dot is the same expression
+  mat3t_vec(RdT, acc, tmp);
+  for (int i = 0; i < 3; ++i) k4v[i] = tmp[i] + g[i];
+  double k1p[3], k2p[3], k3p[3], k4p[3];
+  for (int i = 0; i < 3; ++i) {
+    k1p[i] = v[i];
+    k2p[i] = v[i] + k1v[i] * dt / 2.;
+    k3p[i] = v[i] + k2v[i] * dt / 2;
+    k4p[i] = v[i] + k2v[i] * dt;
+  }
+  n = norm4(dq);
+  for (int i = 0; i < 4; ++i) q[i] = dq[i] / n;
+  for (int i = 0; i < 3; ++i) {
+    const double vi = v[i];
+    v[i] = vi + (k1v[i] + 2 * k2v[i] + 2 * k2v[i] + k4v[i]) * dt / 6.;
+    p[i] = p[i] + (k1p[i] + 2 * k2p[i] + 2 * k3p[i] + k4p[i]) * dt / 6.;
+  }
+}
+
+__device__ __forceinline__ void mm21(const double* A, const double* B, double* C, int tid) {   // C = A B (21x21)
+  for (int e = tid; e < 441; e += PT) {
+    const int i = e / 21, j = e - 21 * i;
+    double s = 0;
+#pragma unroll
+    for (int k = 0; k < 21; ++k) s += A[21 * i + k] * B[21 * k + j];
+    C[e] = s;
+  }
+}
+
+// One CTA per filter: integrates the filter's IMU samples of this frame.  The 21x21 IMU block of P
+// is advanced per sample; the IMU-camera cross covariance only needs the product of the Phis,
+// applied once at the end (identical algebra: P_IC <- Phi_k ... Phi_1 P_IC; symmetrising it is exact).
+__global__ void __launch_bounds__(PT) k_propagate(Dev d, const int* __restrict__ imu_off, const double* __restrict__ ts,
+                                                   const double* __restrict__ gyro_m, const double* __restrict__ acc_m) {
+  const int f = blockIdx.x, tid = threadIdx.x;
+  const int k0 = imu_off[f], k1 = imu_off[f + 1];
+  if (k1 <= k0) return;
+  __shared__ double sPhi[441], sA[441], sB[441], sC[441], sPII[441], sU[441], sT1[441], sAcc[441];
+  __shared__ double sx[IMU_STRIDE];
+  __shared__ double sM[9];       // sigma_a^2 R^T R block of G Qc G^T
+  __shared__ double sdt;
+  const Params& prm = *d.prm;
+  double* imu = d.imu + (size_t)f * IMU_STRIDE;
+  double* P = d.P + (size_t)f * d.ld * d.ld;
+  const int ld = d.ld;
+  const int ncam = d.ncam[f];
+  const int n = NI + 6 * ncam;
+
+  for (int e = tid; e < IMU_STRIDE; e += PT) sx[e] = imu[e];
+  for (int e = tid; e < 441; e += PT) {
+    const int i = e / 21, j = e - 21 * i;
+    sPII[e] = P[(size_t)i * ld + j];
+    sAcc[e] = (i == j) ? 1.0 : 0.0;
+  }
+  __syncthreads();
+
+  for (int k = k0; k < k1; ++k) {
+    // ---- F*dt (jit_utils.py:10-38)
+    for (int e = tid; e < 441; e += PT) sA[e] = 0.0;
+    __syncthreads();
+    if (tid == 0) {
+      const double dt = ts[k] - sx[MSCKF_IMU_TIME];
+      sdt = dt;
+      double w[3], a[3], R[9], Sa[9], RtS[9];
+      for (int i = 0; i < 3; ++i) {
+        w[i] = gyro_m[3 * k + i] - sx[MSCKF_IMU_BG + i];
+        a[i] = acc_m[3 * k + i] - sx[MSCKF_IMU_BA + i];
+      }
+      to_rotation(sx + MSCKF_IMU_Q, R);
+      skew3(a, Sa);
+      mat3_mul_tn(R, Sa, RtS);
+      double Sw[9];
+      skew3(w, Sw);
+      for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) {
+          sA[21 * i + j] = -Sw[3 * i + j] * dt;
+          sA[21 * (6 + i) + j] = -RtS[3 * i + j] * dt;
+          sA[21 * (6 + i) + 9 + j] = -R[3 * j + i] * dt;
+        }
+      for (int i = 0; i < 3; ++i) {
+        sA[21 * i + 3 + i] = -1.0 * dt;
+        sA[21 * (12 + i) + 6 + i] = 1.0 * dt;
+      }
+      // G Qc G^T, block (6:9,6:9) = (-R^T) sigma_a^2 (-R^T)^T
+      double nR[9], nRq[9];
+      for (int i = 0; i < 9; ++i) nR[i] = -R[i];                  // (-R^T) stored transposed
+      for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) nRq[3 * i + j] = nR[3 * j + i] * prm.Qc[2];   // (-R^T) Qc_a
+      for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j)
+          sM[3 * i + j] = nRq[3 * i] * nR[3 * 0 + j] + nRq[3 * i + 1] * nR[3 * 1 + j] + nRq[3 * i + 2] * nR[3 * 2 + j];
+      // state prediction (RK4) on registers of thread 0
+      double q[4], v[3], p[3];
+      for (int i = 0; i < 4; ++i) q[i] = sx[MSCKF_IMU_Q + i];
+      for (int i = 0; i < 3; ++i) { v[i] = sx[MSCKF_IMU_V + i]; p[i] = sx[MSCKF_IMU_P + i]; }
+      predict_new_state(dt, w, a, sx + MSCKF_IMU_GRAVITY, q, v, p);
+      for (int i = 0; i < 4; ++i) sx[MSCKF_IMU_Q + i] = q[i];
+      for (int i = 0; i < 3; ++i) { sx[MSCKF_IMU_V + i] = v[i]; sx[MSCKF_IMU_P + i] = p[i]; }
+    }
+    __syncthreads();
+    mm21(sA, sA, sB, tid);
+    __syncthreads();
+    mm21(sB, sA, sC, tid);
+    __syncthreads();
+    for (int e = tid; e < 441; e += PT) {
+      const int i = e / 21, j = e - 21 * i;
+      sPhi[e] = ((i == j ? 1.0 : 0.0) + sA[e]) + sB[e] / 2. + sC[e] / 6.;
+    }
+    __syncthreads();
+    // ---- observability-constrained blocks of Phi (msckf.py:328-344)
+    if (tid == 0) {
+      const double dt = sdt;
+      const double* g = sx + MSCKF_IMU_GRAVITY;
+      double Rk[9], Rn[9], B[9];
+      to_rotation(sx + MSCKF_IMU_Q_NULL, Rk);
+      to_rotation(sx + MSCKF_IMU_Q, Rn);
+      mat3_mul_nt(Rn, Rk, B);
+      for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) sPhi[21 * i + j] = B[3 * i + j];
+      double u[3], s[3];
+      mat3_vec(Rk, g, u);
+      const double uu = u[0] * u[0] + u[1] * u[1] + u[2] * u[2];
+      for (int i = 0; i < 3; ++i) s[i] = u[i] / uu;
+      double dv[3], dp[3], w1[3], w2[3];
+      for (int i = 0; i < 3; ++i) {
+        dv[i] = sx[MSCKF_IMU_V_NULL + i] - sx[MSCKF_IMU_V + i];
+        dp[i] = dt * sx[MSCKF_IMU_V_NULL + i] + sx[MSCKF_IMU_P_NULL + i] - sx[MSCKF_IMU_P + i];
+      }
+      cross3(dv, g, w1);
+      cross3(dp, g, w2);
+      for (int blk = 0; blk < 2; ++blk) {
+        const int r0 = blk == 0 ? 6 : 12;
+        const double* ww = blk == 0 ? w1 : w2;
+        for (int i = 0; i < 3; ++i) {
+          double* row = sPhi + 21 * (r0 + i);
+          const double au = row[0] * u[0] + row[1] * u[1] + row[2] * u[2];
+          const double c = au - ww[i];
+          for (int j = 0; j < 3; ++j) row[j] = row[j] - c * s[j];
+        }
+      }
+      // null states <- current (msckf.py:366-368), time
+      for (int i = 0; i < 4; ++i) sx[MSCKF_IMU_Q_NULL + i] = sx[MSCKF_IMU_Q + i];
+      for (int i = 0; i < 3; ++i) {
+        sx[MSCKF_IMU_V_NULL + i] = sx[MSCKF_IMU_V + i];
+        sx[MSCKF_IMU_P_NULL + i] = sx[MSCKF_IMU_P + i];
+      }
+      sx[MSCKF_IMU_TIME] = ts[k];
+      sx[MSCKF_IMU_NULL_ALIASED] = 1.0;
+    }
+    __syncthreads();
+    // ---- T1 = Phi P_II ; U = Phi (G Qc G^T)   (jit_utils.py:132-134)
+    for (int e = tid; e < 441; e += PT) {
+      const int i = e / 21, j = e - 21 * i;
+      double s = 0;
+#pragma unroll
+      for (int kk = 0; kk < 21; ++kk) s += sPhi[21 * i + kk] * sPII[21 * kk + j];
+      sT1[e] = s;
+      double u = 0;
+      if (j < 3) u = sPhi[21 * i + j] * prm.Qc[0];
+      else if (j < 6) u = sPhi[21 * i + j] * prm.Qc[1];
+      else if (j < 9) u = sPhi[21 * i + 6] * sM[j - 6] + sPhi[21 * i + 7] * sM[3 + j - 6] + sPhi[21 * i + 8] * sM[6 + j - 6];
+      else if (j < 12) u = sPhi[21 * i + j] * prm.Qc[3];
+      sU[e] = u;
+    }
+    __syncthreads();
+    {
+      const double dt = sdt;
+      for (int e = tid; e < 441; e += PT) {
+        const int i = e / 21, j = e - 21 * i;
+        double s = 0, qq = 0;
+#pragma unroll
+        for (int kk = 0; kk < 21; ++kk) s += sT1[21 * i + kk] * sPhi[21 * j + kk];
+#pragma unroll
+        for (int kk = 0; kk < 12; ++kk) qq += sU[21 * i + kk] * sPhi[21 * j + kk];
+        sC[e] = s + qq * dt;
+      }
+    }
+    // Phi_acc <- Phi Phi_acc
+    mm21(sPhi, sAcc, sB, tid);
+    __syncthreads();
+    for (int e = tid; e < 441; e += PT) {
+      const int i = e / 21, j = e - 21 * i;
+      sPII[e] = (sC[e] + sC[21 * j + i]) / 2.;
+      sAcc[e] = sB[e];
+    }
+    __syncthreads();
+  }
+
+  // ---- write back: IMU state, P_II, P_IC = Phi_acc P_IC and its mirror
+  for (int e = tid; e < IMU_STRIDE; e += PT) imu[e] = sx[e];
+  for (int e = tid; e < 441; e += PT) {
+    const int i = e / 21, j = e - 21 * i;
+    P[(size_t)i * ld + j] = sPII[e];
+  }
+  for (int j = NI + tid; j < n; j += PT) {
+    double col[21];
+#pragma unroll
+    for (int i = 0; i < 21; ++i) col[i] = P[(size_t)i * ld + j];
+#pragma unroll
+    for (int i = 0; i < 21; ++i) {
+      double s = 0;
+#pragma unroll
+      for (int kk = 0; kk < 21; ++kk) s += sAcc[21 * i + kk] * col[kk];
+      P[(size_t)i * ld + j] = s;
+      P[(size_t)j * ld + i] = s;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ state augmentation
+// msckf.py:385-407 + jit_utils.py:137-167.  One CTA per filter.
+__global__ void __launch_bounds__(PT) k_augment(Dev d, const long long* __restrict__ new_ids) {
+  const int f = blockIdx.x, tid = threadIdx.x;
+  const int N = d.ncam[f];
+  if (N >= d.Nmax) {
+    if (tid == 0) atomicOr(d.err, ERRBIT_CAM_CAP);
+    return;
+  }
+  __shared__ double sJ[6 * 21];
+  __shared__ double sB[6 * 21];   // J P[:21,:21]
+  const double* imu = d.imu + (size_t)f * IMU_STRIDE;
+  double* P = d.P + (size_t)f * d.ld * d.ld;
+  const int ld = d.ld, n = NI + 6 * N;
+  if (tid == 0) {
+    double Rwi[9], Rwc[9], tw[3], q[4];
+    const double* Ric = imu + MSCKF_IMU_R_IC;
+    const double* tci = imu + MSCKF_IMU_T_CI;
+    to_rotation(imu + MSCKF_IMU_Q, Rwi);
+    mat3_mul(Ric, Rwi, Rwc);
+    mat3t_vec(Rwi, tci, tw);                      // R_w_i^T t_c_i
+    to_quaternion(Rwc, q);
+    double* c = d.cam + ((size_t)f * d.Nmax + N) * CAM_STRIDE;
+    for (int i = 0; i < 4; ++i) { c[i] = q[i]; c[7 + i] = q[i]; }
+    for (int i = 0; i < 3; ++i) { const double pi = imu[MSCKF_IMU_P + i] + tw[i]; c[4 + i] = pi; c[11 + i] = pi; }
+    d.cam_id[(size_t)f * d.Nmax + N] = new_ids[f];
+    // physical observation slot: lowest free bit
+    const unsigned long long used = d.phys_used[f];
+    const int slot = __ffsll((long long)~used) - 1;
+    d.cam_phys[(size_t)f * d.Nmax + N] = slot;
+    d.phys_used[f] = used | (1ull << slot);
+    for (int e = 0; e < 126; ++e) sJ[e] = 0.0;
+    double St[9];
+    skew3(tw, St);
+    for (int i = 0; i < 3; ++i) {
+      for (int j = 0; j < 3; ++j) { sJ[21 * i + j] = Ric[3 * i + j]; sJ[21 * (3 + i) + j] = St[3 * i + j]; }
+      sJ[21 * i + 15 + i] = 1.0;
+      sJ[21 * (3 + i) + 12 + i] = 1.0;
+      sJ[21 * (3 + i) + 18 + i] = 1.0;
+    }
+  }
+  __syncthreads();
+  // new rows: J P[:21, :n]; mirrored into the new columns
+  for (int e = tid; e < 6 * n; e += PT) {
+    const int i = e / n, j = e - i * n;
+    double s = 0;
+#pragma unroll
+    for (int k = 0; k < 21; ++k) s += sJ[21 * i + k] * P[(size_t)k * ld + j];
+    if (j < 21) sB[21 * i + j] = s;
+    P[(size_t)(n + i) * ld + j] = s;
+    P[(size_t)j * ld + n + i] = s;
+  }
+  __syncthreads();
+  if (tid < 36) {
+    const int i = tid / 6, j = tid - 6 * i;
+    double a = 0, b = 0;
+    for (int k = 0; k < 21; ++k) { a += sB[21 * i + k] * sJ[21 * j + k]; b += sB[21 * j + k] * sJ[21 * i + k]; }
+    P[(size_t)(n + i) * ld + n + j] = (a + b) / 2.;
+  }
+  if (tid == 0) d.ncam[f] = N + 1;
+}
+
+// ------------------------------------------------------------------ reset of P (msckf.py:820-830)
+__device__ void reset_cov(const Dev& d, int f, int tid, int nthreads) {
+  double* P = d.P + (size_t)f * d.ld * d.ld;
+  const Params& prm = *d.prm;
+  for (int e = tid; e < 21 * d.ld; e += nthreads) {
+    const int i = e / d.ld, j = e - i * d.ld;
+    double v = 0;
+    if (i == j) {
+      if (i >= 3 && i < 6) v = prm.P0[0];
+      else if (i >= 6 && i < 9) v = prm.P0[1];
+      else if (i >= 9 && i < 12) v = prm.P0[2];
+      else if (i >= 15 && i < 18) v = prm.P0[3];
+      else if (i >= 18 && i < 21) v = prm.P0[4];
+    }
+    P[e] = v;
+  }
+}
+
+__device__ void clear_window_and_map(const Dev& d, int f, int tid, int nthreads) {
+  for (int s = tid; s < d.Fcap; s += nthreads) {
+    d.f_flags[(size_t)f * d.Fcap + s] = 0;
+    d.f_mask[(size_t)f * d.Fcap + s] = 0ull;
+    d.free_stack[(size_t)f * d.Fcap + s] = d.Fcap - 1 - s;   // pop order: slot 0 first
+  }
+  if (tid == 0) {
+    d.nlive[f] = 0;
+    d.nfree[f] = d.Fcap;
+    d.ncam[f] = 0;
+    d.phys_used[f] = 0ull;
+  }
+}
+
+// online_reset (msckf.py:859-886).  Also snapshots the IMU block for publish() BEFORE resetting.
+__global__ void __launch_bounds__(PT) k_finish_frame(Dev d, int do_reset_check) {
+  const int f = blockIdx.x, tid = threadIdx.x;
+  const double* imu = d.imu + (size_t)f * IMU_STRIDE;
+  for (int e = tid; e < IMU_STRIDE; e += PT) d.imu_pub[(size_t)f * IMU_STRIDE + e] = imu[e];
+  if (tid == 0) d.counters[4 * f + 3] += 1;
+  if (!do_reset_check) return;
+  __shared__ int s_reset;
+  if (tid == 0) {
+    const double thr = d.prm->pos_std_thr;
+    int r = 0;
+    if (thr > 0) {
+      const double* P = d.P + (size_t)f * d.ld * d.ld;
+      const double sx = sqrt(P[(size_t)12 * d.ld + 12]), sy = sqrt(P[(size_t)13 * d.ld + 13]), sz = sqrt(P[(size_t)14 * d.ld + 14]);
+      const double m = fmax(fmax(sx, sy), sz);
+      r = !(m < thr);
+    }
+    s_reset = r;
+    d.did_reset[f] = (unsigned char)r;
+  }
+  __syncthreads();
+  if (s_reset) {
+    clear_window_and_map(d, f, tid, PT);
+    reset_cov(d, f, tid, PT);
+  }
+}
+
+// full reset of one filter (msckf.py:832-857) or of all filters (f < 0) at creation
+__global__ void __launch_bounds__(PT) k_reset(Dev d, int only_filter, int reset_imu) {
+  const int f = only_filter >= 0 ? only_filter : blockIdx.x;
+  const int tid = threadIdx.x;
+  clear_window_and_map(d, f, tid, PT);
+  reset_cov(d, f, tid, PT);
+  if (reset_imu && tid == 0) {
+    double* imu = d.imu + (size_t)f * IMU_STRIDE;
+    double keepR[9], keept[3], keepg[3];
+    for (int i = 0; i < 9; ++i) keepR[i] = imu[MSCKF_IMU_R_IC + i];
+    for (int i = 0; i < 3; ++i) { keept[i] = imu[MSCKF_IMU_T_CI + i]; keepg[i] = imu[MSCKF_IMU_GRAVITY + i]; }
+    for (int i = 0; i < IMU_STRIDE; ++i) imu[i] = 0.0;
+    imu[MSCKF_IMU_Q + 3] = 1.0;
+    imu[MSCKF_IMU_Q_NULL + 3] = 1.0;
+    for (int i = 0; i < 9; ++i) imu[MSCKF_IMU_R_IC + i] = keepR[i];
+    for (int i = 0; i < 3; ++i) { imu[MSCKF_IMU_T_CI + i] = keept[i]; imu[MSCKF_IMU_GRAVITY + i] = keepg[i]; }
+  }
+}
+
+// ------------------------------------------------------------------ camera-state removal (msckf.py:803-818)
+// In-place compaction of P, the camera table and the physical-slot mask.  Rows are moved in
+// increasing order in batches staged through shared memory (destination row <= source row).
+constexpr int RB = 8;   // rows per batch
+__global__ void __launch_bounds__(PT) k_remove_cams(Dev d) {
+  const int f = blockIdx.x, tid = threadIdx.x;
+  const int r0 = d.rm_idx[2 * f], r1 = d.rm_idx[2 * f + 1];
+  if (r0 < 0) return;
+  extern __shared__ double srow[];     // [RB][ld]
+  const int N = d.ncam[f], n = NI + 6 * N, ld = d.ld;
+  double* P = d.P + (size_t)f * ld * ld;
+  const int n2 = n - 12;
+  auto src_of = [&](int i) {   // new index -> old index
+    if (i < NI + 6 * r0) return i;
+    if (i < NI + 6 * (r1 - 1)) return i + 6;
+    return i + 12;
+  };
+  for (int base = 0; base < n2; base += RB) {
+    const int nb = min(RB, n2 - base);
+    for (int e = tid; e < nb * n2; e += PT) {
+      const int i = e / n2, j = e - i * n2;
+      srow[i * ld + j] = P[(size_t)src_of(base + i) * ld + src_of(j)];
+    }
+    __syncthreads();
+    for (int e = tid; e < nb * n2; e += PT) {
+      const int i = e / n2, j = e - i * n2;
+      P[(size_t)(base + i) * ld + j] = srow[i * ld + j];
+    }
+    __syncthreads();
+  }
+  // camera table: stage every surviving entry, then write
+  __shared__ double scam[64 * CAM_STRIDE];
+  __shared__ long long sid[64];
+  __shared__ int sphys[64];
+  const int N2 = N - 2;
+  for (int e = tid; e < N2 * CAM_STRIDE; e += PT) {
+    const int c = e / CAM_STRIDE, k = e - c * CAM_STRIDE;
+    const int oc = c < r0 ? c : (c < r1 - 1 ? c + 1 : c + 2);
+    scam[e] = d.cam[((size_t)f * d.Nmax + oc) * CAM_STRIDE + k];
+    if (k == 0) { sid[c] = d.cam_id[(size_t)f * d.Nmax + oc]; sphys[c] = d.cam_phys[(size_t)f * d.Nmax + oc]; }
+  }
+  __syncthreads();
+  for (int e = tid; e < N2 * CAM_STRIDE; e += PT) {
+    const int c = e / CAM_STRIDE, k = e - c * CAM_STRIDE;
+    d.cam[((size_t)f * d.Nmax + c) * CAM_STRIDE + k] = scam[e];
+    if (k == 0) { d.cam_id[(size_t)f * d.Nmax + c] = sid[c]; d.cam_phys[(size_t)f * d.Nmax + c] = sphys[c]; }
+  }
+  if (tid == 0) {
+    d.ncam[f] = N2;
+    d.phys_used[f] &= ~d.rm_mask[f];
+  }
+}
+
+// ------------------------------------------------------------------ launchers
+void launch_propagate(const Dev& d, const int* imu_off, const double* ts, const double* gyro, const double* acc, cudaStream_t st) {
+  k_propagate<<<d.F, PT, 0, st>>>(d, imu_off, ts, gyro, acc);
+}
+void launch_augment(const Dev& d, const long long* ids, cudaStream_t st) { k_augment<<<d.F, PT, 0, st>>>(d, ids); }
+void launch_finish_frame(const Dev& d, int do_reset_check, cudaStream_t st) { k_finish_frame<<<d.F, PT, 0, st>>>(d, do_reset_check); }
+void launch_reset(const Dev& d, int only_filter, int reset_imu, cudaStream_t st) {
+  k_reset<<<only_filter >= 0 ? 1 : d.F, PT, 0, st>>>(d, only_filter, reset_imu);
+}
+void launch_remove_cams(const Dev& d, cudaStream_t st) {
+  k_remove_cams<<<d.F, PT, (size_t)RB * d.ld * sizeof(double), st>>>(d);
+}
+
+}  // namespace msckf

@@ -1,0 +1,452 @@
+// Device-resident landmark store: the reference's map_server / observations dictionaries
+// (msckf.py:409-427, 616-689, 730-801) as flat per-filter tables.  One CTA per filter.
+//
+//   * a landmark owns a slot; `ord` lists live slots in insertion order (Python dict order),
+//   * observations are a 64-bit mask over physical camera slots plus uv[slot][4],
+//   * id -> slot lookup uses an open-addressing table rebuilt every frame,
+//   * order-preserving compaction (ballot prefix sums) keeps every list in map order, which is
+//     what makes the processed / invalid id sequences and the row-cap break bit-exact.
+#include <limits.h>
+#include "msckf_dev.cuh"
+#include "kernels.h"
+
+namespace msckf {
+
+constexpr int ST = 256;
+constexpr long long EMPTY_KEY = LLONG_MIN;
+
+// exclusive prefix of a 0/1 flag over the CTA (one tile of ST threads); total returned to all
+__device__ __forceinline__ int block_rank(int flag, int* s_warp, int& total) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const unsigned m = __ballot_sync(0xffffffffu, flag);
+  const int r = __popc(m & ((1u << lane) - 1u));
+  __syncthreads();                     // protects s_warp against the previous tile's readers
+  if (lane == 0) s_warp[w] = __popc(m);
+  __syncthreads();
+  int base = 0, tot = 0;
+#pragma unroll
+  for (int i = 0; i < ST / 32; ++i) {
+    const int c = s_warp[i];
+    if (i < w) base += c;
+    tot += c;
+  }
+  total = tot;
+  return base + r;
+}
+
+// exclusive prefix of an int value over the CTA tile
+__device__ __forceinline__ long long block_scan_ll(long long v, long long* s_warp, long long& total) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  long long inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const long long t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  __syncthreads();
+  if (lane == 31) s_warp[w] = inc;
+  __syncthreads();
+  long long base = 0, tot = 0;
+#pragma unroll
+  for (int i = 0; i < ST / 32; ++i) {
+    const long long c = s_warp[i];
+    if (i < w) base += c;
+    tot += c;
+  }
+  total = tot;
+  return base + inc - v;
+}
+
+__device__ __forceinline__ unsigned hash64(long long k) {
+  unsigned long long x = (unsigned long long)k;
+  x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
+  return (unsigned)x;
+}
+
+// ------------------------------------------------------------------ add_feature_observations (msckf.py:409-427)
+__global__ void __launch_bounds__(ST) k_observe(Dev d, const int* __restrict__ feat_off, const long long* __restrict__ ids,
+                                                 const double* __restrict__ uv) {
+  const int f = blockIdx.x, tid = threadIdx.x;
+  __shared__ int s_warp[ST / 32];
+  __shared__ int s_tracked;
+  const int n0 = d.nlive[f];
+  const int off = feat_off[f], cnt = feat_off[f + 1] - off;
+  const int N = d.ncam[f];
+  long long* hk = d.h_key + (size_t)f * d.Hs;
+  int* hv = d.h_val + (size_t)f * d.Hs;
+  const unsigned hmask = (unsigned)d.Hs - 1u;
+  if (tid == 0) s_tracked = 0;
+  for (int e = tid; e < d.Hs; e += ST) hk[e] = EMPTY_KEY;
+  __syncthreads();
+  if (N == 0) return;
+  const int phys = d.cam_phys[(size_t)f * d.Nmax + N - 1];
+  const unsigned long long bit = 1ull << phys;
+  int* ord = d.ord + (size_t)f * d.Fcap;
+  for (int j = tid; j < n0; j += ST) {
+    const int slot = ord[j];
+    const long long key = d.f_id[(size_t)f * d.Fcap + slot];
+    unsigned h = hash64(key) & hmask;
+    while (true) {
+      const unsigned long long old = atomicCAS((unsigned long long*)&hk[h], (unsigned long long)EMPTY_KEY, (unsigned long long)key);
+      if (old == (unsigned long long)EMPTY_KEY) { hv[h] = slot; break; }
+      h = (h + 1) & hmask;
+    }
+  }
+  __syncthreads();
+  int nfree = d.nfree[f];
+  const int* fstack = d.free_stack + (size_t)f * d.Fcap;
+  int base_new = 0;
+  for (int t0 = 0; t0 < cnt; t0 += ST) {
+    const int i = t0 + tid;
+    const bool valid = i < cnt;
+    long long key = 0;
+    int slot = -1;
+    if (valid) {
+      key = ids[off + i];
+      unsigned h = hash64(key) & hmask;
+      while (true) {
+        const long long k = hk[h];
+        if (k == EMPTY_KEY) break;
+        if (k == key) { slot = hv[h]; break; }
+        h = (h + 1) & hmask;
+      }
+    }
+    const int isnew = valid && slot < 0;
+    int total;
+    const int rank = block_rank(isnew, s_warp, total);
+    if (isnew) {
+      const int idx = base_new + rank;
+      if (idx >= nfree) {
+        atomicOr(d.err, ERRBIT_FEATURE_CAP);
+      } else {
+        slot = fstack[nfree - 1 - idx];
+        const size_t fs = (size_t)f * d.Fcap + slot;
+        d.f_id[fs] = key;
+        d.f_mask[fs] = bit;
+        d.f_flags[fs] = FF_LIVE;
+        d.f_pos[fs * 3 + 0] = 0; d.f_pos[fs * 3 + 1] = 0; d.f_pos[fs * 3 + 2] = 0;
+        ord[n0 + idx] = slot;
+      }
+    } else if (valid) {
+      d.f_mask[(size_t)f * d.Fcap + slot] |= bit;
+      atomicAdd(&s_tracked, 1);
+    }
+    if (valid && slot >= 0) {
+      double* o = d.f_obs + (((size_t)f * d.Fcap + slot) * d.Nmax + phys) * 4;
+      const double* z = uv + 4 * (size_t)(off + i);
+      o[0] = z[0]; o[1] = z[1]; o[2] = z[2]; o[3] = z[3];
+    }
+    base_new += total;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    const int added = min(base_new, nfree);
+    d.nlive[f] = n0 + added;
+    d.nfree[f] = nfree - added;
+    d.imu[(size_t)f * IMU_STRIDE + MSCKF_IMU_TRACKING_RATE] = (double)s_tracked / ((double)n0 + 1e-5);
+  }
+}
+
+// ------------------------------------------------------------------ remove_lost_features, pass 1 (msckf.py:623-650)
+// Splits the map into tracked (kept) and lost landmarks, both in map order.  Lost landmarks go to
+// the candidate list with status FEW_OBS / CS_NEED_TRI / CS_READY; their slots are released
+// (the data stays valid until the next frame's observations arrive).
+__global__ void __launch_bounds__(ST) k_classify_lost(Dev d) {
+  const int f = blockIdx.x, tid = threadIdx.x;
+  __shared__ int s_warp[ST / 32];
+  const int n = d.nlive[f], N = d.ncam[f];
+  int* ord = d.ord + (size_t)f * d.Fcap;
+  int* tmp = d.ord_tmp + (size_t)f * d.Fcap;
+  int* cand = d.cand + (size_t)f * d.Fcap;
+  int* cst = d.cand_status + (size_t)f * d.Fcap;
+  if (N == 0) {
+    if (tid == 0) { d.ncand[f] = 0; d.nitem[f] = 0; }
+    return;
+  }
+  const unsigned long long bit = 1ull << d.cam_phys[(size_t)f * d.Nmax + N - 1];
+  int nkeep = 0, nlost = 0;
+  const int nfree0 = d.nfree[f];
+  for (int t0 = 0; t0 < n; t0 += ST) {
+    const int j = t0 + tid;
+    const bool valid = j < n;
+    int slot = 0;
+    unsigned long long mask = 0;
+    if (valid) { slot = ord[j]; mask = d.f_mask[(size_t)f * d.Fcap + slot]; }
+    const int lost = valid && !(mask & bit);
+    const int keep = valid && !lost;
+    int tl, tk;
+    const int rl = block_rank(lost, s_warp, tl);
+    const int rk = block_rank(keep, s_warp, tk);
+    if (keep) tmp[nkeep + rk] = slot;
+    if (lost) {
+      const int ci = nlost + rl;
+      cand[ci] = slot;
+      int st;
+      if (__popcll(mask) < 3) st = MSCKF_FEAT_FEW_OBS;
+      else st = (d.f_flags[(size_t)f * d.Fcap + slot] & FF_INIT) ? CS_READY : CS_NEED_TRI;
+      cst[ci] = st;
+      d.free_stack[(size_t)f * d.Fcap + nfree0 + ci] = slot;
+    }
+    nkeep += tk;
+    nlost += tl;
+  }
+  __syncthreads();
+  for (int j = tid; j < nkeep; j += ST) ord[j] = tmp[j];
+  if (tid == 0) {
+    d.nlive[f] = nkeep;
+    d.nfree[f] = nfree0 + nlost;
+    d.ncand[f] = nlost;
+    d.rm_mask[f] = 0ull;
+  }
+}
+
+// ------------------------------------------------------------------ find_redundant_cam_states (msckf.py:691-727)
+__device__ void find_redundant(const Dev& d, int f, int* rm /*[2] logical, sorted*/) {
+  const Params& prm = *d.prm;
+  const int N = d.ncam[f];
+  const double* cam = d.cam + (size_t)f * d.Nmax * CAM_STRIDE;
+  const double track = d.imu[(size_t)f * IMU_STRIDE + MSCKF_IMU_TRACKING_RATE];
+  const int key = N - 4;
+  int idx = key + 1, first = 0;
+  double Rk[9];
+  to_rotation(cam + (size_t)key * CAM_STRIDE, Rk);
+  const double* pk = cam + (size_t)key * CAM_STRIDE + 4;
+  for (int i = 0; i < 2; ++i) {
+    const double* c = cam + (size_t)idx * CAM_STRIDE;
+    double R[9], B[9], q[4];
+    to_rotation(c, R);
+    const double dp[3] = {c[4] - pk[0], c[5] - pk[1], c[6] - pk[2]};
+    const double distance = norm3(dp);
+    mat3_mul_nt(R, Rk, B);
+    to_quaternion(B, q);
+    const double angle = 2 * acos(q[3]);
+    if (angle < prm.prune_rot_thr && distance < prm.prune_trans_thr && track > prm.prune_track_thr) {
+      rm[i] = idx;
+      idx += 1;
+    } else {
+      rm[i] = first;
+      first += 1;
+      idx += 1;
+    }
+  }
+  if (rm[0] > rm[1]) { const int t = rm[0]; rm[0] = rm[1]; rm[1] = t; }
+}
+
+__global__ void k_find_redundant(Dev d, int f, long long* out) {
+  if (threadIdx.x == 0) {
+    int rm[2] = {-1, -1};
+    if (d.ncam[f] >= 4) find_redundant(d, f, rm);
+    out[0] = rm[0] >= 0 ? d.cam_id[(size_t)f * d.Nmax + rm[0]] : -1;
+    out[1] = rm[1] >= 0 ? d.cam_id[(size_t)f * d.Nmax + rm[1]] : -1;
+  }
+}
+
+// ------------------------------------------------------------------ prune_cam_state_buffer, pass 1 (msckf.py:730-769)
+__global__ void __launch_bounds__(ST) k_prune_select(Dev d) {
+  const int f = blockIdx.x, tid = threadIdx.x;
+  __shared__ int s_warp[ST / 32];
+  __shared__ unsigned long long s_rm;
+  const int N = d.ncam[f];
+  if (N < d.prm->max_cam) {
+    if (tid == 0) {
+      d.ncand[f] = 0; d.nitem[f] = 0; d.rm_idx[2 * f] = -1; d.rm_idx[2 * f + 1] = -1; d.rm_mask[f] = 0ull;
+      d.log_rm[2 * f] = -1; d.log_rm[2 * f + 1] = -1;
+    }
+    return;
+  }
+  if (tid == 0) {
+    int rm[2];
+    find_redundant(d, f, rm);
+    d.rm_idx[2 * f] = rm[0]; d.rm_idx[2 * f + 1] = rm[1];
+    const unsigned long long m = (1ull << d.cam_phys[(size_t)f * d.Nmax + rm[0]]) | (1ull << d.cam_phys[(size_t)f * d.Nmax + rm[1]]);
+    d.rm_mask[f] = m;
+    s_rm = m;
+    d.log_rm[2 * f] = d.cam_id[(size_t)f * d.Nmax + rm[0]];
+    d.log_rm[2 * f + 1] = d.cam_id[(size_t)f * d.Nmax + rm[1]];
+  }
+  __syncthreads();
+  const unsigned long long rmm = s_rm;
+  const int n = d.nlive[f];
+  const int* ord = d.ord + (size_t)f * d.Fcap;
+  int* cand = d.cand + (size_t)f * d.Fcap;
+  int* cst = d.cand_status + (size_t)f * d.Fcap;
+  int nc = 0;
+  for (int t0 = 0; t0 < n; t0 += ST) {
+    const int j = t0 + tid;
+    const bool valid = j < n;
+    int slot = 0, c = 0;
+    unsigned long long mask = 0;
+    if (valid) {
+      slot = ord[j];
+      mask = d.f_mask[(size_t)f * d.Fcap + slot];
+      c = __popcll(mask & rmm);
+      if (c == 1) d.f_mask[(size_t)f * d.Fcap + slot] = mask & ~rmm;
+    }
+    int tot;
+    const int r = block_rank(c >= 2, s_warp, tot);
+    if (c >= 2) {
+      cand[nc + r] = slot;
+      cst[nc + r] = (d.f_flags[(size_t)f * d.Fcap + slot] & FF_INIT) ? CS_READY : CS_NEED_TRI;
+    }
+    nc += tot;
+  }
+  if (tid == 0) d.ncand[f] = nc;
+}
+
+// ------------------------------------------------------------------ items: landmarks that reach feature_jacobian
+// stage 0: all observations, dof = M-1 (msckf.py:645,669-671); stage 1: the pruned camera
+// states only, dof = M (msckf.py:769,787-789); their observations are then dropped (:794-795).
+// Scratch for each item is bump-allocated from the pool.
+__global__ void __launch_bounds__(ST) k_plan_items(Dev d, int stage) {
+  const int f = blockIdx.x, tid = threadIdx.x;
+  __shared__ int s_warp[ST / 32];
+  __shared__ long long s_warp_ll[ST / 32];
+  __shared__ unsigned long long s_base;
+  const int nc = d.ncand[f];
+  const int* cand = d.cand + (size_t)f * d.Fcap;
+  const int* cst = d.cand_status + (size_t)f * d.Fcap;
+  const unsigned long long rmm = d.rm_mask[f];
+  int ni = 0;
+  long long elems_total = 0;
+  // pass A: ordered item list + relative offsets
+  for (int t0 = 0; t0 < nc; t0 += ST) {
+    const int ci = t0 + tid;
+    const bool valid = ci < nc;
+    int isitem = 0, M = 0;
+    unsigned long long im = 0;
+    if (valid) {
+      const int slot = cand[ci];
+      const unsigned long long mask = d.f_mask[(size_t)f * d.Fcap + slot];
+      isitem = cst[ci] == CS_READY;
+      im = stage == 0 ? mask : (mask & rmm);
+      M = __popcll(im);
+      if (stage == 1) d.f_mask[(size_t)f * d.Fcap + slot] = mask & ~rmm;
+    }
+    const int rows = 4 * M - 3;
+    const long long need = isitem ? ((long long)4 * M * (6 * M + 4) + (long long)rows * 6 * M + (long long)rows * rows) : 0;
+    int tot;
+    const int r = block_rank(isitem, s_warp, tot);
+    long long tot_e;
+    const long long eoff = block_scan_ll(need, s_warp_ll, tot_e);
+    if (isitem) {
+      const size_t k = (size_t)f * d.Fcap + ni + r;
+      d.item_cand[k] = ci;
+      d.item_mask[k] = im;
+      d.item_rows[k] = rows;
+      d.item_dof[k] = stage == 0 ? M - 1 : M;
+      d.item_off[k] = elems_total + eoff;   // relative; rebased below
+      d.item_pass[k] = 0;
+      d.item_gamma[k] = 0.0;
+      d.item_rowoff[k] = -1;
+    }
+    ni += tot;
+    elems_total += tot_e;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    unsigned long long base = 0;
+    if (elems_total > 0) {
+      base = atomicAdd(d.pool_used, (unsigned long long)elems_total);
+      if ((long long)(base + elems_total) > d.pool_cap) {
+        atomicOr(d.err, ERRBIT_POOL);
+        ni = 0;
+      }
+    }
+    s_base = base;
+    d.nitem[f] = ni;
+  }
+  __syncthreads();
+  const long long base = (long long)s_base;
+  for (int k = tid; k < ni; k += ST) d.item_off[(size_t)f * d.Fcap + k] += base;
+}
+
+// ------------------------------------------------------------------ stacking plan + decision log
+// Applies the sequential semantics of msckf.py:662-679 / 776-795 to the gate results: a landmark
+// is taken through the gate only while the rows stacked so far are <= row_cap (stage 0).
+__global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
+  const int f = blockIdx.x, tid = threadIdx.x;
+  __shared__ long long s_warp_ll[ST / 32];
+  __shared__ unsigned long long s_act;
+  __shared__ int s_proc;
+  const int ni = d.nitem[f], nc = d.ncand[f];
+  const int cap = (stage == 0) ? d.prm->row_cap : 0;
+  if (tid == 0) { s_act = 0ull; s_proc = 0; }
+  __syncthreads();
+  long long stacked = 0;   // rows stacked by earlier tiles (inclusive prefix)
+  long long used_rows = 0;
+  int* cst = d.cand_status + (size_t)f * d.Fcap;
+  for (int t0 = 0; t0 < ni; t0 += ST) {
+    const int k = t0 + tid;
+    const bool valid = k < ni;
+    const size_t ik = (size_t)f * d.Fcap + k;
+    const int pass = valid ? d.item_pass[ik] : 0;
+    const int rows = valid ? d.item_rows[ik] : 0;
+    long long tot;
+    const long long excl = stacked + block_scan_ll(pass ? rows : 0, s_warp_ll, tot);
+    const bool processed = valid && (cap <= 0 || excl <= cap);
+    const bool used = processed && pass;
+    long long tot_u;
+    const long long ro = used_rows + block_scan_ll(used ? rows : 0, s_warp_ll, tot_u);
+    if (valid) {
+      d.item_rowoff[ik] = used ? (int)ro : -1;
+      cst[d.item_cand[ik]] = processed ? (pass ? MSCKF_FEAT_GATE_PASS : MSCKF_FEAT_GATE_FAIL) : MSCKF_FEAT_AFTER_CAP;
+      if (used) atomicOr(&s_act, d.item_mask[ik]);
+      if (processed) atomicAdd(&s_proc, 1);
+    }
+    stacked += tot;
+    used_rows += tot_u;
+  }
+  __syncthreads();
+  // decision log in map order
+  long long* lid = d.log_id + ((size_t)stage * d.F + f) * d.Fcap;
+  int* lst = d.log_status + ((size_t)stage * d.F + f) * d.Fcap;
+  double* lga = d.log_gamma + ((size_t)stage * d.F + f) * d.Fcap;
+  int* ldf = d.log_dof + ((size_t)stage * d.F + f) * d.Fcap;
+  for (int ci = tid; ci < nc; ci += ST) {
+    lid[ci] = d.f_id[(size_t)f * d.Fcap + d.cand[(size_t)f * d.Fcap + ci]];
+    lst[ci] = cst[ci];
+    lga[ci] = 0.0;
+    ldf[ci] = 0;
+  }
+  __syncthreads();
+  for (int k = tid; k < ni; k += ST) {
+    const size_t ik = (size_t)f * d.Fcap + k;
+    lga[d.item_cand[ik]] = d.item_gamma[ik];
+    ldf[d.item_cand[ik]] = d.item_dof[ik];
+  }
+  if (tid == 0) {
+    int m = (int)used_rows;
+    const int N = d.ncam[f];
+    if (m > d.max_rows) { atomicOr(d.err, ERRBIT_ROWS); m = 0; }
+    // active columns in logical order
+    const unsigned long long act = s_act;
+    int na = 0;
+    int* cm = d.colmap + (size_t)f * d.nmax;
+    for (int c = 0; c < N; ++c)
+      if ((act >> d.cam_phys[(size_t)f * d.Nmax + c]) & 1ull)
+        for (int e = 0; e < 6; ++e) cm[na++] = NI + 6 * c + e;
+    if ((long long)(((m + 3) / 4) * 4) * (na + 1) > d.A_elems) { atomicOr(d.err, ERRBIT_ROWS); m = 0; }
+    d.m_rows[f] = m;
+    d.m_pad[f] = max(4, ((m + 3) / 4) * 4);
+    d.n_act[f] = na;
+    d.k_rows[f] = (m > na) ? na : m;
+    d.log_n[stage * d.F + f] = nc;
+    d.log_upd[((size_t)stage * d.F + f) * 2 + 0] = m;
+    d.log_upd[((size_t)stage * d.F + f) * 2 + 1] = NI + 6 * N;
+    d.counters[4 * f + 0] += s_proc;
+    if (m > 0) d.counters[4 * f + 2] += 1;
+  }
+}
+
+void launch_observe(const Dev& d, const int* feat_off, const long long* ids, const double* uv, cudaStream_t st) {
+  k_observe<<<d.F, ST, 0, st>>>(d, feat_off, ids, uv);
+}
+void launch_classify_lost(const Dev& d, cudaStream_t st) { k_classify_lost<<<d.F, ST, 0, st>>>(d); }
+void launch_plan_items(const Dev& d, int stage, cudaStream_t st) { k_plan_items<<<d.F, ST, 0, st>>>(d, stage); }
+void launch_plan_stack(const Dev& d, int stage, cudaStream_t st) { k_plan_stack<<<d.F, ST, 0, st>>>(d, stage); }
+void launch_prune_select(const Dev& d, cudaStream_t st) { k_prune_select<<<d.F, ST, 0, st>>>(d); }
+void launch_find_redundant(const Dev& d, int filter, long long* out_ids, cudaStream_t st) {
+  k_find_redundant<<<1, 32, 0, st>>>(d, filter, out_ids);
+}
+
+}  // namespace msckf

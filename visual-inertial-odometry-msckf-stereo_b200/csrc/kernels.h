@@ -1,0 +1,41 @@
+// Host-side launchers of the CUDA kernels (one translation unit per kernel family).
+#pragma once
+#include <cuda_runtime.h>
+#include "msckf_dev.cuh"
+
+namespace msckf {
+
+// k_propagate.cu
+void launch_propagate(const Dev& d, const int* imu_off, const double* ts, const double* gyro, const double* acc, cudaStream_t st);
+void launch_augment(const Dev& d, const long long* ids, cudaStream_t st);
+void launch_finish_frame(const Dev& d, int do_reset_check, cudaStream_t st);
+void launch_reset(const Dev& d, int only_filter, int reset_imu, cudaStream_t st);
+void launch_remove_cams(const Dev& d, cudaStream_t st);
+
+// k_store.cu  (landmark store = map_server bookkeeping)
+void launch_observe(const Dev& d, const int* feat_off, const long long* ids, const double* uv, cudaStream_t st);
+void launch_classify_lost(const Dev& d, cudaStream_t st);
+void launch_plan_items(const Dev& d, int stage, cudaStream_t st);
+void launch_plan_stack(const Dev& d, int stage, cudaStream_t st);
+void launch_prune_select(const Dev& d, cudaStream_t st);
+void launch_find_redundant(const Dev& d, int filter, long long* out_ids, cudaStream_t st);
+
+// k_triangulate.cu
+void launch_triangulate_store(const Dev& d, cudaStream_t st);
+void launch_triangulate_raw(const Dev& d, int n, const int* obs_off, const double* uv, const double* cam_q, const double* cam_p,
+                            double* pos, unsigned char* valid, int* solves, int max_obs, cudaStream_t st);
+
+// k_jacobian.cu
+void launch_jacobian_gate(const Dev& d, cudaStream_t st);
+void launch_stack(const Dev& d, cudaStream_t st);
+void launch_measurement_jacobian(const Dev& d, int filter, int cam_logical, int slot, double* out /*[4*6+4*3+4]*/, cudaStream_t st);
+void launch_export_item_dense(const Dev& d, int filter, double* H, double* r, int n_state, cudaStream_t st);
+void launch_gate_dense(const Dev& d, int filter, const double* H, const double* r, int m, int n_state, int dof,
+                       double* scratch, double* out_gamma, int* out_pass, cudaStream_t st);
+
+// k_update.cu
+void launch_qr(const Dev& d, cudaStream_t st);
+void launch_update(const Dev& d, int stage, cudaStream_t st);
+void launch_load_dense_H(const Dev& d, int filter, const double* H, const double* r, int m, int n_state, cudaStream_t st);
+
+}  // namespace msckf

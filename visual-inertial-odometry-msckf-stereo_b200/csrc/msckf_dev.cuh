@@ -1,0 +1,229 @@
+// Device-side data model and small geometry helpers of the B200 MSCKF back end.
+// All arithmetic is FP64 (the reference computes in numpy float64).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/msckf_b200.h"
+
+namespace msckf {
+
+// ------------------------------------------------------------------ constants
+constexpr int IMU_STRIDE = MSCKF_IMU_STRIDE;
+constexpr int CAM_STRIDE = MSCKF_CAM_STRIDE;   // q[4] p[3] q_null[4] p_null[3] pad[2]
+constexpr int NI = 21;                          // IMU error-state size
+
+// feature flags
+constexpr int FF_LIVE = 1;
+constexpr int FF_INIT = 2;
+
+// candidate status while a stage runs (final values are the MSCKF_FEAT_* log codes)
+constexpr int CS_NEED_TRI = 100;   // lost / involved, not initialised yet
+constexpr int CS_READY = 101;      // initialised: will be taken through jacobian + gate
+
+// error bits accumulated on the device (one word per context)
+constexpr unsigned ERRBIT_FEATURE_CAP = 1u;
+constexpr unsigned ERRBIT_POOL = 2u;
+constexpr unsigned ERRBIT_ROWS = 4u;
+constexpr unsigned ERRBIT_NOT_SPD = 8u;
+constexpr unsigned ERRBIT_CAM_CAP = 16u;
+
+struct Params {
+  double Qc[4];            // gyro, gyro-bias, acc, acc-bias noise variances (msckf.py:132-137)
+  double obs_noise;        // config.py:76
+  double P0[5];            // gyro_bias, velocity, acc_bias, extr. rotation, extr. translation (msckf.py:820-830)
+  double pos_std_thr;      // config.py:64
+  double tri_translation_thr, huber_eps, est_precision, init_damping;   // config.py:10-13
+  int outer_max, inner_max;                                              // config.py:14-15
+  double prune_rot_thr, prune_trans_thr, prune_track_thr;                // msckf.py:717
+  double R01[9], t01[3];   // cam0 -> cam1 (config.py:110-114)
+  double chi2[100];        // msckf.py:121-123
+  int max_cam;             // config.py:57
+  int row_cap;             // msckf.py:678
+};
+
+// Everything a kernel needs, passed by value.
+struct Dev {
+  int F, Nmax, nmax, ld, Fcap, Hs;
+  int max_rows;            // row capacity of the stacked Jacobian per filter
+  long long A_elems;       // elements of A per filter
+  int Tk;                  // row capacity of T / S per filter (= 6*Nmax, or more for user H)
+  const Params* prm;
+  // ---- filter state
+  double* imu;             // [F][IMU_STRIDE]
+  long long* cam_id;       // [F][Nmax]   logical (insertion) order
+  int* cam_phys;           // [F][Nmax]   physical observation slot of each camera state
+  double* cam;             // [F][Nmax][CAM_STRIDE]
+  int* ncam;               // [F]
+  unsigned long long* phys_used;   // [F] bit mask of physical slots in use
+  double* P;               // [F][ld*ld] row-major, logical layout, n = 21+6*ncam
+  // ---- landmark store (map_server)
+  long long* f_id;         // [F][Fcap]
+  unsigned long long* f_mask;      // [F][Fcap] bit = physical cam slot
+  int* f_flags;            // [F][Fcap]
+  double* f_pos;           // [F][Fcap][3]
+  double* f_obs;           // [F][Fcap][Nmax][4]
+  int* ord;                // [F][Fcap] slots in insertion order
+  int* ord_tmp;            // [F][Fcap]
+  int* nlive;              // [F]
+  int* free_stack;         // [F][Fcap]
+  int* nfree;              // [F]
+  long long* h_key;        // [F][Hs] open-addressing table rebuilt per frame
+  int* h_val;              // [F][Hs]
+  // ---- stage work lists
+  int* cand;               // [F][Fcap] slots of lost / involved landmarks in map order
+  int* cand_status;        // [F][Fcap]
+  int* ncand;              // [F]
+  int* item_cand;          // [F][Fcap] index into cand of the landmarks that reach the Jacobian
+  unsigned long long* item_mask;   // [F][Fcap] physical-slot mask of the observations used
+  int* item_rows;          // [F][Fcap] 4M-3
+  long long* item_off;     // [F][Fcap] element offset in pool
+  int* item_rowoff;        // [F][Fcap] row offset in the stacked matrix (-1 = not stacked)
+  int* item_dof;           // [F][Fcap]
+  double* item_gamma;      // [F][Fcap]
+  int* item_pass;          // [F][Fcap]
+  int* nitem;              // [F]
+  unsigned long long* rm_mask;     // [F] physical mask of the camera states being pruned
+  int* rm_idx;             // [F][2] logical indices, -1 when not pruning
+  double* pool;            // per-feature Jacobian scratch (bump allocated per stage)
+  unsigned long long* pool_used;   // [1]
+  long long pool_cap;      // elements
+  double* A;               // [F][A_elems] stacked compact Jacobian, column-major, ld = m_pad
+  int* m_rows;             // [F] rows stacked
+  int* m_pad;              // [F] leading dimension of A
+  int* n_act;              // [F] active columns (without r)
+  int* k_rows;             // [F] rows of H_thin after compression
+  int* colmap;             // [F][nmax] active column -> state index
+  double* T;               // [F][Tk][ld+8]  H_thin P | r  -> W | y
+  double* S;               // [F][Tk][Tk]
+  double* dx;              // [F][nmax]
+  // ---- logs / counters / errors
+  long long* log_id;       // [2][F][Fcap]
+  int* log_status;         // [2][F][Fcap]
+  double* log_gamma;       // [2][F][Fcap]
+  int* log_dof;            // [2][F][Fcap]
+  int* log_n;              // [2][F]
+  int* log_upd;            // [2][F][2] rows, cols of the update
+  long long* log_rm;       // [F][2]
+  long long* counters;     // [F][4]
+  unsigned* err;           // [1]
+  unsigned char* did_reset;        // [F]
+  double* imu_pub;         // [F][IMU_STRIDE] snapshot for publish()
+};
+
+__host__ __device__ inline int Tld(const Dev& d) { return d.ld + 8; }
+
+// ------------------------------------------------------------------ warp helpers
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ int warp_sum_i(int v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ------------------------------------------------------------------ 3x3 / quaternion algebra (utils.py:4-128)
+__device__ __forceinline__ void mat3_mul(const double* A, const double* B, double* C) {   // C = A B
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) C[3 * i + j] = A[3 * i] * B[j] + A[3 * i + 1] * B[3 + j] + A[3 * i + 2] * B[6 + j];
+}
+__device__ __forceinline__ void mat3_mul_nt(const double* A, const double* B, double* C) {  // C = A B^T
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) C[3 * i + j] = A[3 * i] * B[3 * j] + A[3 * i + 1] * B[3 * j + 1] + A[3 * i + 2] * B[3 * j + 2];
+}
+__device__ __forceinline__ void mat3_mul_tn(const double* A, const double* B, double* C) {  // C = A^T B
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) C[3 * i + j] = A[i] * B[j] + A[3 + i] * B[3 + j] + A[6 + i] * B[6 + j];
+}
+__device__ __forceinline__ void mat3_vec(const double* A, const double* x, double* y) {     // y = A x
+#pragma unroll
+  for (int i = 0; i < 3; ++i) y[i] = A[3 * i] * x[0] + A[3 * i + 1] * x[1] + A[3 * i + 2] * x[2];
+}
+__device__ __forceinline__ void mat3t_vec(const double* A, const double* x, double* y) {    // y = A^T x
+#pragma unroll
+  for (int i = 0; i < 3; ++i) y[i] = A[i] * x[0] + A[3 + i] * x[1] + A[6 + i] * x[2];
+}
+__device__ __forceinline__ void skew3(const double* v, double* S) {   // utils.py:4-12
+  S[0] = 0; S[1] = -v[2]; S[2] = v[1];
+  S[3] = v[2]; S[4] = 0; S[5] = -v[0];
+  S[6] = -v[1]; S[7] = v[0]; S[8] = 0;
+}
+__device__ __forceinline__ void cross3(const double* a, const double* b, double* c) {   // skew(a) b
+  c[0] = a[1] * b[2] - a[2] * b[1];
+  c[1] = a[2] * b[0] - a[0] * b[2];
+  c[2] = a[0] * b[1] - a[1] * b[0];
+}
+__device__ __forceinline__ double norm4(const double* q) { return sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]); }
+__device__ __forceinline__ double norm3(const double* v) { return sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]); }
+
+// R from a quaternion WITHOUT normalising, with an explicit vector for the skew term
+// (jit_utils.py:86-104 re-uses a stale skew there).
+__device__ __forceinline__ void rot_from_parts(const double* vec, double w, const double* skew_vec, double* R) {
+  const double a = 2 * w * w - 1, b = 2 * w;
+  R[0] = a + 2 * vec[0] * vec[0];              R[1] = b * skew_vec[2] + 2 * vec[0] * vec[1];  R[2] = -b * skew_vec[1] + 2 * vec[0] * vec[2];
+  R[3] = -b * skew_vec[2] + 2 * vec[1] * vec[0]; R[4] = a + 2 * vec[1] * vec[1];              R[5] = b * skew_vec[0] + 2 * vec[1] * vec[2];
+  R[6] = b * skew_vec[1] + 2 * vec[2] * vec[0];  R[7] = -b * skew_vec[0] + 2 * vec[2] * vec[1]; R[8] = a + 2 * vec[2] * vec[2];
+}
+// utils.py:14-27
+__device__ __forceinline__ void to_rotation(const double* q_in, double* R) {
+  const double n = norm4(q_in);
+  const double q[4] = {q_in[0] / n, q_in[1] / n, q_in[2] / n, q_in[3] / n};
+  rot_from_parts(q, q[3], q, R);
+}
+// utils.py:29-53
+__device__ __forceinline__ void to_quaternion(const double* R, double* q) {
+  double t;
+  if (R[8] < 0) {
+    if (R[0] > R[4]) {
+      t = 1 + R[0] - R[4] - R[8];
+      q[0] = t; q[1] = R[1] + R[3]; q[2] = R[6] + R[2]; q[3] = R[5] - R[7];
+    } else {
+      t = 1 - R[0] + R[4] - R[8];
+      q[0] = R[1] + R[3]; q[1] = t; q[2] = R[7] + R[5]; q[3] = R[6] - R[2];
+    }
+  } else {
+    if (R[0] < -R[4]) {
+      t = 1 - R[0] - R[4] + R[8];
+      q[0] = R[2] + R[6]; q[1] = R[7] + R[5]; q[2] = t; q[3] = R[1] - R[3];
+    } else {
+      t = 1 + R[0] + R[4] + R[8];
+      q[0] = R[5] - R[7]; q[1] = R[6] - R[2]; q[2] = R[1] - R[3]; q[3] = t;
+    }
+  }
+  const double n = norm4(q);
+  q[0] /= n; q[1] /= n; q[2] /= n; q[3] /= n;
+}
+// utils.py:67-82
+__device__ __forceinline__ void quat_mul(const double* q1, const double* q2, double* out) {
+  const double n1 = norm4(q1), n2 = norm4(q2);
+  const double a[4] = {q1[0] / n1, q1[1] / n1, q1[2] / n1, q1[3] / n1};
+  const double b[4] = {q2[0] / n2, q2[1] / n2, q2[2] / n2, q2[3] / n2};
+  double q[4];
+  q[0] = a[3] * b[0] + a[2] * b[1] - a[1] * b[2] + a[0] * b[3];
+  q[1] = -a[2] * b[0] + a[3] * b[1] + a[0] * b[2] + a[1] * b[3];
+  q[2] = a[1] * b[0] - a[0] * b[1] + a[3] * b[2] + a[2] * b[3];
+  q[3] = -a[0] * b[0] - a[1] * b[1] - a[2] * b[2] + a[3] * b[3];
+  const double n = norm4(q);
+  out[0] = q[0] / n; out[1] = q[1] / n; out[2] = q[2] / n; out[3] = q[3] / n;
+}
+// utils.py:85-101
+__device__ __forceinline__ void small_angle_quat(const double* dtheta, double* q) {
+  const double d[3] = {dtheta[0] / 2., dtheta[1] / 2., dtheta[2] / 2.};
+  const double s = d[0] * d[0] + d[1] * d[1] + d[2] * d[2];
+  if (s <= 1) {
+    q[0] = d[0]; q[1] = d[1]; q[2] = d[2]; q[3] = sqrt(1 - s);
+  } else {
+    const double n = sqrt(1 + s);
+    q[0] = d[0] / n; q[1] = d[1] / n; q[2] = d[2] / n; q[3] = 1. / n;
+  }
+}
+
+}  // namespace msckf

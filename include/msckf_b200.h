@@ -111,6 +111,10 @@ int msckf_set_cov(msckf_ctx* ctx, int32_t filter, const double* P, int32_t n);
  * state (insertion order); obs is [n][max_cam][4]. Any output pointer may be NULL. */
 int msckf_get_features(msckf_ctx* ctx, int32_t filter, int32_t* n_features, int64_t* ids, uint64_t* obs_mask,
                        uint8_t* is_initialized, double* position /*[n][3]*/, double* obs);
+/* Replaces the whole map of one filter (snapshot restore; the inverse of msckf_get_features, same layouts).
+ * The camera states must have been set first.  is_initialized / position may be NULL (false / zeros). */
+int msckf_set_features(msckf_ctx* ctx, int32_t filter, int32_t n_features, const int64_t* ids, const uint64_t* obs_mask,
+                       const uint8_t* is_initialized, const double* position /*[n][3]*/, const double* obs /*[n][max_cam][4]*/);
 /* Overwrites position / is_initialized of one live landmark (tests; Feature._vio_position__). */
 int msckf_set_feature_position(msckf_ctx* ctx, int32_t filter, int64_t feature_id, const double* position,
                                int32_t is_initialized);
@@ -180,6 +184,20 @@ int msckf_get_counters(msckf_ctx* ctx, int64_t* counters);
 int msckf_triangulate(msckf_ctx* ctx, int32_t n, const int32_t* obs_off, const double* uv, const double* cam_q,
                       const double* cam_p, double* position, uint8_t* valid, int32_t* lm_solves);
 
+/* Feature.initialize_position (feature.py:167-295) alone, i.e. msckf_triangulate without the check_motion test. */
+int msckf_initialize_position(msckf_ctx* ctx, int32_t n, const int32_t* obs_off, const double* uv, const double* cam_q,
+                              const double* cam_p, double* position, uint8_t* valid, int32_t* lm_solves);
+
+/* Feature.check_motion (feature.py:124-165) alone: moved[i] = 1 when the translation between the first and
+ * the last observing camera, orthogonal to the first bearing, exceeds translation_threshold. */
+int msckf_check_motion(msckf_ctx* ctx, int32_t n, const int32_t* obs_off, const double* uv, const double* cam_q,
+                       const double* cam_p, uint8_t* moved);
+
+/* Feature.generate_initial_guess (feature.py:99-122) alone, between the first and the last cam0 view of each
+ * landmark: guess[n][3] in the frame of the first cam0 (what initialize_position starts from, feature.py:216-218). */
+int msckf_initial_guess(msckf_ctx* ctx, int32_t n, const int32_t* obs_off, const double* uv, const double* cam_q,
+                        const double* cam_p, double* guess);
+
 /* feature_jacobian (msckf.py:500-541) of a stored landmark over the given camera-state ids:
  * H is [(4M-3)][n_state] dense, r [(4M-3)].  The null-space basis is the Householder one, so H and
  * r equal the reference's up to an orthogonal row transform (H^T H, H^T r and gamma are equal). */
@@ -206,6 +224,9 @@ int msckf_find_redundant_cam_states(msckf_ctx* ctx, int32_t filter, int64_t* cam
 int msckf_last_timing(msckf_ctx* ctx, float* ms /*[5]*/);
 /* Enable (1) / disable (0) per-stage event timing (off by default: events cost launches). */
 int msckf_set_timing(msckf_ctx* ctx, int32_t enabled);
+
+/* Number of CUDA kernels of this library enqueued on the context so far (bench.py: gpu_launches). */
+int msckf_kernel_launches(msckf_ctx* ctx, int64_t* n);
 
 /* Library build info, e.g. "msckf_b200 sm_100a cuda 12.9". */
 const char* msckf_version(void);

@@ -1,0 +1,205 @@
+"""GPU parity, stream level: the CUDA drop-in stepped frame by frame through feature_callback
+(the reference's public API) against
+
+  * the golden per-frame record of the unmodified reference (tests/golden/stream_small.npz), and
+  * the CPU oracle stepped beside it on a longer / wider stream (BASELINE.json configs[1] shape:
+    max_cam_state_size = 30), and as a batch of independent filters (configs[3] shape).
+
+Criteria (north_star): state and covariance within 1e-9 relative at every frame, trajectory within
+1 mm, and bit-exact decisions: gate accept / reject sequence, lost / processed / pruned landmark
+ids (map contents), removed camera-state ids.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from harness import rel_err, snapshot
+from oracle import msckf_oracle as orc
+from msckf_b200 import capi, synth
+from msckf_b200.config import ConfigEuRoC
+from msckf_b200.msckf import MSCKF, MSCKFBatch
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
+TOL = 1e-9
+
+
+def probe_vector(n):
+    return np.cos(1.0 + 0.37 * np.arange(n) ** 1.5)
+
+
+def device_decisions(filt):
+    """(gate decisions, gammas, removed cam ids or None, [update rows]) of the frame just processed."""
+    dec, gam, upd = [], [], []
+    rm = None
+    for stage in (0, 1):
+        log = filt.stage_log(stage)
+        for s, g in zip(log['status'], log['gamma']):
+            if s in (capi.FEAT_GATE_PASS, capi.FEAT_GATE_FAIL):
+                dec.append(s == capi.FEAT_GATE_PASS)
+                gam.append(g)
+        if log['update_rows'] > 0:
+            upd.append(log['update_rows'])
+        if stage == 1 and log['removed_cam_ids'][0] >= 0:
+            rm = [int(x) for x in log['removed_cam_ids']]
+    return dec, gam, rm, upd
+
+
+def test_stream_vs_reference_golden():
+    g = dict(np.load(os.path.join(GOLD, 'stream_small.npz')))
+    nf, nfeat, sseed, nseed = [int(x) for x in g['stream_kw']]
+    stream = synth.make_stream(nf, nfeat, sseed, nseed)
+    cfg = ConfigEuRoC()
+    cfg._vio_max_cam_state_size__ = int(g['max_cam'])
+    filt = MSCKF(cfg, feature_capacity=512)
+    worst = {'imu': 0.0, 'Pv': 0.0, 'cams': 0.0, 'extr': 0.0, 'Pdiag': 0.0}
+    dec_all, gam_all, rm_all, upd_all = [], [], [], []
+
+    def seg(key, f):
+        o = g[key + '_off']
+        return g[key][o[f]:o[f + 1]]
+
+    def check(f, flt, res):
+        s = snapshot(flt)
+        assert np.array_equal(s['cam_ids'], seg('cam_ids', f)), f
+        assert np.array_equal(s['map_ids'], seg('map_ids', f)), f
+        n = s['P'].shape[0]
+        assert n == int(g['n'][f])
+        worst['imu'] = max(worst['imu'], rel_err(s['imu'], g['imu'][f]))
+        worst['extr'] = max(worst['extr'], rel_err(s['extr'], g['extr'][f]))
+        worst['cams'] = max(worst['cams'], rel_err(s['cams'].ravel(), seg('cams', f)))
+        worst['Pv'] = max(worst['Pv'], rel_err(s['P'] @ probe_vector(n), seg('Pv', f)))
+        worst['Pdiag'] = max(worst['Pdiag'], rel_err(np.diag(s['P']), seg('Pdiag', f)))
+        assert abs(np.linalg.norm(s['P']) - g['Pfro'][f]) <= TOL * g['Pfro'][f]
+        if 'P_%d' % f in g:
+            assert rel_err(s['P'], g['P_%d' % f]) < TOL
+        dec, gam, rm, upd = device_decisions(flt)
+        dec_all.extend(dec)
+        gam_all.extend(gam)
+        upd_all.extend(upd)
+        if rm is not None:
+            rm_all.append([f] + rm)
+
+    try:
+        synth.drive(filt, stream, on_frame=check)
+    finally:
+        filt.close()
+    assert max(worst.values()) < TOL, worst
+    assert dec_all == [bool(x) for x in g['gate'][:, 3]]                 # bit-exact gate decisions
+    gam = np.array(gam_all)
+    assert np.all(np.abs(gam - g['gate'][:, 2]) <= 1e-8 * np.abs(g['gate'][:, 2]))
+    assert np.array_equal(np.array(rm_all, dtype=np.int64), g['rm'])      # removed camera states
+    assert upd_all == [int(r) for r in g['upd_rows'][:, 1] if r > 0]      # rows of every update
+
+
+def run_pair(stream, max_cam, n_frames, feature_capacity=1024, row_cap=None):
+    """Steps the oracle and the device filter side by side; returns worst errors and checks decisions per frame."""
+    ocfg = orc.ConfigEuRoC()
+    ocfg._vio_max_cam_state_size__ = max_cam
+    of = orc.MSCKF(ocfg)
+    if row_cap is not None:
+        of.ROW_CAP = row_cap
+    dcfg = ConfigEuRoC()
+    dcfg._vio_max_cam_state_size__ = max_cam
+    if row_cap is not None:
+        dcfg.row_cap = row_cap
+    df = MSCKF(dcfg, feature_capacity=feature_capacity)
+    worst = {'imu': 0.0, 'P': 0.0, 'cams': 0.0, 'extr': 0.0, 'pos_m': 0.0}
+    counts = {'gates': 0, 'pass': 0, 'prunes': 0, 'updates': 0}
+    msgs = stream.imu_msgs()
+    k = 0
+    try:
+        for f in range(n_frames):
+            t = stream.frame_ts[f]
+            while k < len(msgs) and msgs[k].vio_timestamp__ <= t:
+                of.imu_callback(msgs[k])
+                df.imu_callback(msgs[k])
+                k += 1
+            of.log = {}
+            ro = of.feature_callback(stream.feature_msg(f))
+            rd = df.feature_callback(stream.feature_msg(f))
+            assert (ro is None) == (rd is None)
+            so, sd = snapshot(of), snapshot(df)
+            assert np.array_equal(sd['cam_ids'], so['cam_ids']), f
+            assert np.array_equal(sd['map_ids'], so['map_ids']), f
+            for key in ('imu', 'P', 'cams', 'extr'):
+                worst[key] = max(worst[key], rel_err(sd[key], so[key]))
+            worst['pos_m'] = max(worst['pos_m'], float(np.linalg.norm(sd['imu'][13:16] - so['imu'][13:16])))
+            dec, gam, rm, upd = device_decisions(df)
+            ogates = of.log.get('gate', [])
+            assert dec == [x[2] for x in ogates], f
+            if ogates:
+                og = np.array([x[0] for x in ogates])
+                assert np.all(np.abs(np.array(gam) - og) <= 1e-7 * np.abs(og)), f
+            orm = of.log.get('rm_cam_ids', [])
+            assert (rm is None and not orm) or (orm and rm == [int(x) for x in orm[0]]), f
+            counts['gates'] += len(dec)
+            counts['pass'] += sum(dec)
+            counts['prunes'] += int(rm is not None)
+            counts['updates'] += len(upd)
+            if ro is not None:
+                assert rel_err(rd.pose._vio_t__, ro.pose._vio_t__) < 1e-8 or np.linalg.norm(ro.pose._vio_t__) < 1e-6
+                assert rel_err(rd.cam0_pose._vio_R__, ro.cam0_pose._vio_R__) < 1e-9
+                assert rel_err(rd.velocity, ro.velocity) < 1e-8 or np.linalg.norm(ro.velocity) < 1e-6
+    finally:
+        df.close()
+    return worst, counts
+
+
+def test_stream_vs_oracle_window30():
+    """configs[1]: one filter, max_cam_state_size = 30, ~300 features per frame."""
+    n_frames = 70
+    stream = synth.make_stream(n_frames, 300, structure_seed=1, noise_seed=11)
+    worst, counts = run_pair(stream, 30, n_frames, feature_capacity=2048)
+    assert counts['gates'] > 2000 and counts['prunes'] >= 10 and 0 < counts['pass'] < counts['gates'], counts
+    assert worst['imu'] < TOL and worst['P'] < TOL and worst['cams'] < TOL and worst['extr'] < TOL, worst
+    assert worst['pos_m'] < 1e-3, worst
+
+
+def test_stream_row_cap_break():
+    """The row-cap break of remove_lost_features (msckf.py:676-679) with a small cap so that it triggers."""
+    n_frames = 40
+    stream = synth.realize(synth.make_structure(n_frames, 200, structure_seed=2, mean_track_len=4.0), noise_seed=5)
+    worst, counts = run_pair(stream, 10, n_frames, feature_capacity=1024, row_cap=60)
+    assert counts['gates'] > 200, counts
+    assert max(worst['imu'], worst['P'], worst['cams']) < TOL, worst
+
+
+def test_batch_of_filters_vs_oracle():
+    """configs[3] shape: independent filters (noise seeds) in one context, each equal to its own oracle run."""
+    F, n_frames, max_cam = 6, 30, 8
+    st = synth.make_structure(n_frames, 80, structure_seed=3)
+    streams = [synth.realize(st, noise_seed=100 + k) for k in range(F)]
+    dcfg = ConfigEuRoC()
+    dcfg._vio_max_cam_state_size__ = max_cam
+    batch = MSCKFBatch(dcfg, F, feature_capacity=512)
+    try:
+        s0 = streams[0]
+        batch.initialize_gravity_and_bias(np.stack([s.gyro[:200] for s in streams]), np.stack([s.acc[:200] for s in streams]))
+        traj = np.zeros((F, n_frames, 3))
+        for f in range(n_frames):
+            a, b = s0.imu_range_for_frame(f)
+            imu, rst = batch.feature_callback(float(s0.frame_ts[f]), s0.imu_ts[a:b], np.stack([s.gyro[a:b] for s in streams]),
+                                              np.stack([s.acc[a:b] for s in streams]), s0.frame_ids[f],
+                                              np.stack([s.frame_uv[f] for s in streams]))
+            assert not rst.any()
+            traj[:, f] = imu[:, capi.IMU_P:capi.IMU_P + 3]
+        Ps = [batch.ctx.get_cov(k) for k in range(F)]
+        cams = [batch.ctx.get_cam_states(k) for k in range(F)]
+        feats = [batch.ctx.get_features(k, with_obs=False)[0] for k in range(F)]
+    finally:
+        batch.close()
+    for k in range(F):
+        ocfg = orc.ConfigEuRoC()
+        ocfg._vio_max_cam_state_size__ = max_cam
+        of = orc.MSCKF(ocfg)
+        otraj = []
+        synth.drive(of, streams[k], n_frames, on_frame=lambda f, flt, res: otraj.append(flt.state_server._vio_imu_state__._vio_position__.copy()))
+        so = snapshot(of)
+        assert np.max(np.linalg.norm(traj[k] - np.array(otraj), axis=1)) < 1e-3
+        assert rel_err(traj[k], np.array(otraj)) < TOL
+        assert rel_err(Ps[k], so['P']) < TOL
+        assert np.array_equal(cams[k][0], so['cam_ids'])
+        assert np.array_equal(feats[k], so['map_ids'])

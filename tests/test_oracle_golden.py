@@ -6,7 +6,7 @@ import os
 import numpy as np
 import pytest
 
-from harness import snapshot, rel_err
+from harness import snapshot, rel_err, oracle_filter_from_units as build_filter_from_units
 from oracle import msckf_oracle as orc
 from msckf_b200 import synth
 
@@ -61,40 +61,6 @@ def test_jit_kernels_golden(units):
     G, Phi = orc.process_model_matrices(u['j_gyro'][0], Rwi, u['j_acc'][0], u['j_dt'][0])
     Pp = orc.propagate_imu_covariance(filt.state_server._vio_continuous_noise_cov__, P.copy(), G, Phi, u['j_dt'][0])
     assert rel_err(Pp[:21, :21], u['j_prop']) < 1e-13
-
-
-def build_filter_from_units(u, max_cam=12):
-    """Re-create the mid-stream filter state stored in units.npz inside an oracle MSCKF."""
-    cfg = orc.ConfigEuRoC()
-    cfg._vio_max_cam_state_size__ = max_cam
-    filt = orc.MSCKF(cfg)
-    imu = filt.state_server._vio_imu_state__
-    s = u['state_imu']
-    imu.orientation, imu._vio_gyro_bias__, imu.velocity = s[0:4].copy(), s[4:7].copy(), s[7:10].copy()
-    imu.acc_bias, imu._vio_position__ = s[10:13].copy(), s[13:16].copy()
-    nl = u['state_imu_null']
-    imu.orientation_null = nl[0:4].copy()
-    # reference aliasing (msckf.py:366-368): after process_model the v/p null members ARE the live arrays
-    assert np.array_equal(nl[4:7], imu.velocity) and np.array_equal(nl[7:10], imu._vio_position__)
-    imu.velocity_null, imu.position_null = imu.velocity, imu._vio_position__
-    imu.R_imu_cam0, imu.t_cam0_imu = u['state_extr'][:9].reshape(3, 3).copy(), u['state_extr'][9:].copy()
-    imu.id = int(u['state_imu_id'])
-    filt.gravity = u['j_gravity'].copy()
-    for cid, row in zip(u['state_cam_ids'], u['state_cams']):
-        c = orc.CAMState(int(cid))
-        c.orientation, c._vio_position__ = row[0:4].copy(), row[4:7].copy()
-        c.orientation_null = row[7:11].copy()
-        c.position_null = c._vio_position__          # aliased in the reference (msckf.py:400)
-        filt.state_server._vio_cam_states__[int(cid)] = c
-    filt.state_server._vio_state_cov__ = u['state_P'].copy()
-    filt.tracking_rate = float(u['state_tracking_rate'])
-    off = u['f_off']
-    for k, fid in enumerate(u['f_ids']):
-        ft = orc.Feature(int(fid), filt.optimization_config, filt.R_cam0_cam1, filt.t_cam0_cam1)
-        for j in range(off[k], off[k + 1]):
-            ft.observations[int(u['f_obs_cam'][j])] = u['f_obs_z'][j].copy()
-        filt.map_server[int(fid)] = ft
-    return filt
 
 
 def test_triangulation_golden(units):

@@ -38,6 +38,7 @@ struct msckf_ctx {
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   float last_ms[5] = {0, 0, 0, 0, 0};
   bool frame_pending = false;
+  long long launches = 0;           // kernels of this library enqueued so far
 };
 
 #define CK(call)                                                                                   \
@@ -444,6 +445,48 @@ int msckf_get_features(msckf_ctx* ctx, int32_t f, int32_t* n_features, int64_t* 
   return MSCKF_OK;
 }
 
+int msckf_set_features(msckf_ctx* ctx, int32_t f, int32_t n, const int64_t* ids, const uint64_t* obs_mask, const uint8_t* is_init,
+                       const double* position, const double* obs) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  const Dev& d = ctx->d;
+  ARG(f >= 0 && f < d.F && n >= 0 && n <= d.Fcap && (n == 0 || (ids && obs_mask && obs)), "filter / count / pointers");
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaStreamSynchronize(ctx->st));
+  int ncam = 0;
+  CK(cudaMemcpy(&ncam, d.ncam + f, sizeof(int), cudaMemcpyDeviceToHost));
+  std::vector<int> phys(d.Nmax, 0);
+  if (ncam) CK(cudaMemcpy(phys.data(), d.cam_phys + (size_t)f * d.Nmax, ncam * sizeof(int), cudaMemcpyDeviceToHost));
+  const size_t Fc = d.Fcap, Nm = d.Nmax;
+  std::vector<long long> hid(Fc, 0);
+  std::vector<unsigned long long> hmask(Fc, 0ull);
+  std::vector<int> hflags(Fc, 0), hord(Fc, 0), hfree(Fc, 0);
+  std::vector<double> hpos(Fc * 3, 0.0), hobs(Fc * Nm * 4, 0.0);
+  for (int j = 0; j < n; ++j) {            // landmark j takes slot j; map order = argument order
+    hid[j] = ids[j];
+    hflags[j] = FF_LIVE | ((is_init && is_init[j]) ? FF_INIT : 0);
+    hord[j] = j;
+    if (position) for (int k = 0; k < 3; ++k) hpos[(size_t)j * 3 + k] = position[(size_t)j * 3 + k];
+    ARG((obs_mask[j] >> ncam) == 0 || ncam == 64, "obs_mask has bits beyond the camera-state window");
+    for (int c = 0; c < ncam; ++c)
+      if ((obs_mask[j] >> c) & 1ull) {
+        hmask[j] |= 1ull << phys[c];
+        for (int k = 0; k < 4; ++k) hobs[((size_t)j * Nm + phys[c]) * 4 + k] = obs[((size_t)j * Nm + c) * 4 + k];
+      }
+  }
+  const int nfree = d.Fcap - n;
+  for (int i = 0; i < nfree; ++i) hfree[i] = d.Fcap - 1 - i;
+  CK(cudaMemcpy(d.f_id + f * Fc, hid.data(), Fc * sizeof(long long), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d.f_mask + f * Fc, hmask.data(), Fc * sizeof(unsigned long long), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d.f_flags + f * Fc, hflags.data(), Fc * sizeof(int), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d.ord + f * Fc, hord.data(), Fc * sizeof(int), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d.free_stack + f * Fc, hfree.data(), Fc * sizeof(int), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d.f_pos + f * Fc * 3, hpos.data(), Fc * 3 * sizeof(double), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d.f_obs + f * Fc * Nm * 4, hobs.data(), Fc * Nm * 4 * sizeof(double), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d.nlive + f, &n, sizeof(int), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d.nfree + f, &nfree, sizeof(int), cudaMemcpyHostToDevice));
+  return MSCKF_OK;
+}
+
 int msckf_set_feature_position(msckf_ctx* ctx, int32_t f, int64_t id, const double* position, int32_t is_initialized) {
   if (!ctx) return MSCKF_ERR_ARG;
   const Dev& d = ctx->d;
@@ -461,6 +504,7 @@ int msckf_set_feature_position(msckf_ctx* ctx, int32_t f, int64_t id, const doub
 }
 
 // ------------------------------------------------------------------ stage enqueue helpers
+constexpr int kUpdateLaunches = 6;   // launch_update: T, S, chol, trsm, inject, downdate
 static void enqueue_lost_stage(msckf_ctx* ctx) {
   const Dev& d = ctx->d;
   cudaMemsetAsync(d.pool_used, 0, sizeof(unsigned long long), ctx->st);
@@ -472,6 +516,7 @@ static void enqueue_lost_stage(msckf_ctx* ctx) {
   launch_stack(d, ctx->st);
   launch_qr(d, ctx->st);
   launch_update(d, 0, ctx->st);
+  ctx->launches += 7 + kUpdateLaunches;
 }
 static void enqueue_prune_stage(msckf_ctx* ctx) {
   const Dev& d = ctx->d;
@@ -485,6 +530,7 @@ static void enqueue_prune_stage(msckf_ctx* ctx) {
   launch_qr(d, ctx->st);
   launch_update(d, 1, ctx->st);
   launch_remove_cams(d, ctx->st);
+  ctx->launches += 8 + kUpdateLaunches;
 }
 
 int msckf_propagate(msckf_ctx* ctx, const int32_t* imu_off, const double* ts, const double* gyro, const double* acc) {
@@ -501,6 +547,7 @@ int msckf_propagate(msckf_ctx* ctx, const int32_t* imu_off, const double* ts, co
   if (rc) return rc;
   char* b = p.s->d;
   launch_propagate(ctx->d, (const int*)(b + o0), (const double*)(b + o1), (const double*)(b + o2), (const double*)(b + o3), ctx->st);
+  ctx->launches += 1;
   stage_end(ctx, p);
   CK(cudaGetLastError());
   return MSCKF_OK;
@@ -516,6 +563,7 @@ int msckf_augment(msckf_ctx* ctx, const int64_t* cam_ids) {
   int rc = stage_commit(ctx, p);
   if (rc) return rc;
   launch_augment(ctx->d, (const long long*)(p.s->d + o0), ctx->st);
+  ctx->launches += 1;
   stage_end(ctx, p);
   CK(cudaGetLastError());
   return MSCKF_OK;
@@ -534,6 +582,7 @@ int msckf_add_observations(msckf_ctx* ctx, const int32_t* feat_off, const int64_
   if (rc) return rc;
   char* b = p.s->d;
   launch_observe(ctx->d, (const int*)(b + o0), (const long long*)(b + o1), (const double*)(b + o2), ctx->st);
+  ctx->launches += 1;
   stage_end(ctx, p);
   CK(cudaGetLastError());
   return MSCKF_OK;
@@ -559,6 +608,7 @@ int msckf_online_reset(msckf_ctx* ctx, uint8_t* did_reset) {
   if (!ctx) return MSCKF_ERR_ARG;
   CK(cudaSetDevice(ctx->device));
   launch_finish_frame(ctx->d, 1, ctx->st);
+  ctx->launches += 1;
   CK(cudaMemcpyAsync(ctx->h_reset, ctx->d.did_reset, ctx->d.F, cudaMemcpyDeviceToHost, ctx->st));
   int rc = sync_and_check(ctx);
   if (rc) return rc;
@@ -605,6 +655,7 @@ int msckf_feature_callback_async(msckf_ctx* ctx, const int32_t* imu_off, const d
   enqueue_prune_stage(ctx);
   if (tm) cudaEventRecord(ctx->ev[4], ctx->st);
   launch_finish_frame(d, 1, ctx->st);
+  ctx->launches += 4;              // propagate, augment, observe, finish_frame (stages count their own)
   if (tm) cudaEventRecord(ctx->ev[5], ctx->st);
   stage_end(ctx, p);
   CK(cudaMemcpyAsync(ctx->h_pub, d.imu_pub, (size_t)F * IMU_STRIDE * sizeof(double), cudaMemcpyDeviceToHost, ctx->st));
@@ -691,10 +742,10 @@ int msckf_get_counters(msckf_ctx* ctx, int64_t* counters) {
 }
 
 // ------------------------------------------------------------------ directly callable pieces
-int msckf_triangulate(msckf_ctx* ctx, int32_t n, const int32_t* obs_off, const double* uv, const double* cam_q, const double* cam_p,
-                      double* position, uint8_t* valid, int32_t* lm_solves) {
+static int triangulate_call(msckf_ctx* ctx, int mode, int32_t n, const int32_t* obs_off, const double* uv, const double* cam_q,
+                            const double* cam_p, double* position, uint8_t* valid, int32_t* lm_solves) {
   if (!ctx) return MSCKF_ERR_ARG;
-  ARG(n >= 0 && obs_off && position && valid, "count / pointers");
+  ARG(n >= 0 && obs_off, "count / pointers");
   if (n == 0) return MSCKF_OK;
   CK(cudaSetDevice(ctx->device));
   const int total = obs_off[n];
@@ -720,16 +771,47 @@ int msckf_triangulate(msckf_ctx* ctx, int32_t n, const int32_t* obs_off, const d
   CK(cudaMalloc((void**)&dsol, n * sizeof(int)));
   char* b = p.s->d;
   launch_triangulate_raw(ctx->d, n, (const int*)(b + o0), (const double*)(b + o1), (const double*)(b + o2), (const double*)(b + o3), dpos,
-                         dval, dsol, max_obs, ctx->st);
+                         dval, dsol, max_obs, mode, ctx->st);
+  ctx->launches += 1;
   stage_end(ctx, p);
   rc = sync_and_check(ctx);
   if (!rc) {
-    cudaMemcpy(position, dpos, (size_t)n * 3 * sizeof(double), cudaMemcpyDeviceToHost);
-    cudaMemcpy(valid, dval, n, cudaMemcpyDeviceToHost);
+    if (position) cudaMemcpy(position, dpos, (size_t)n * 3 * sizeof(double), cudaMemcpyDeviceToHost);
+    if (valid) cudaMemcpy(valid, dval, n, cudaMemcpyDeviceToHost);
     if (lm_solves) cudaMemcpy(lm_solves, dsol, n * sizeof(int), cudaMemcpyDeviceToHost);
   }
   cudaFree(dpos); cudaFree(dval); cudaFree(dsol);
   return rc;
+}
+
+int msckf_triangulate(msckf_ctx* ctx, int32_t n, const int32_t* obs_off, const double* uv, const double* cam_q, const double* cam_p,
+                      double* position, uint8_t* valid, int32_t* lm_solves) {
+  if (ctx && !(position && valid)) { ctx->err = "bad argument: output pointers"; return MSCKF_ERR_ARG; }
+  return triangulate_call(ctx, 0, n, obs_off, uv, cam_q, cam_p, position, valid, lm_solves);
+}
+
+int msckf_check_motion(msckf_ctx* ctx, int32_t n, const int32_t* obs_off, const double* uv, const double* cam_q, const double* cam_p,
+                       uint8_t* moved) {
+  if (ctx && !moved) { ctx->err = "bad argument: output pointer"; return MSCKF_ERR_ARG; }
+  return triangulate_call(ctx, 1, n, obs_off, uv, cam_q, cam_p, nullptr, moved, nullptr);
+}
+
+int msckf_initial_guess(msckf_ctx* ctx, int32_t n, const int32_t* obs_off, const double* uv, const double* cam_q, const double* cam_p,
+                        double* guess) {
+  if (ctx && !guess) { ctx->err = "bad argument: output pointer"; return MSCKF_ERR_ARG; }
+  return triangulate_call(ctx, 2, n, obs_off, uv, cam_q, cam_p, guess, nullptr, nullptr);
+}
+
+int msckf_initialize_position(msckf_ctx* ctx, int32_t n, const int32_t* obs_off, const double* uv, const double* cam_q,
+                              const double* cam_p, double* position, uint8_t* valid, int32_t* lm_solves) {
+  if (ctx && !(position && valid)) { ctx->err = "bad argument: output pointers"; return MSCKF_ERR_ARG; }
+  return triangulate_call(ctx, 3, n, obs_off, uv, cam_q, cam_p, position, valid, lm_solves);
+}
+
+int msckf_kernel_launches(msckf_ctx* ctx, int64_t* n) {
+  if (!ctx || !n) return MSCKF_ERR_ARG;
+  *n = ctx->launches;
+  return MSCKF_OK;
 }
 
 int msckf_feature_jacobian(msckf_ctx* ctx, int32_t f, int64_t feature_id, int32_t n_cam_ids, const int64_t* cam_ids, int32_t* rows_out,
@@ -770,6 +852,7 @@ int msckf_feature_jacobian(msckf_ctx* ctx, int32_t f, int64_t feature_id, int32_
   CK(cudaMemcpyAsync(d.nitem + f, &one, sizeof(int), cudaMemcpyHostToDevice, ctx->st));
   CK(cudaStreamSynchronize(ctx->st));      // the small host sources above live on this stack frame
   launch_jacobian_gate(d, ctx->st);
+  ctx->launches += 2;
   double* dH = nullptr;
   CK(cudaMalloc((void**)&dH, ((size_t)rows * n_state + rows) * sizeof(double)));
   launch_export_item_dense(d, f, dH, dH + (size_t)rows * n_state, n_state, ctx->st);
@@ -803,6 +886,7 @@ int msckf_measurement_jacobian(msckf_ctx* ctx, int32_t f, int64_t cam_id, int64_
   double* dout = nullptr;
   CK(cudaMalloc((void**)&dout, 40 * sizeof(double)));
   launch_measurement_jacobian(d, f, c, slot, dout, ctx->st);
+  ctx->launches += 1;
   rc = sync_and_check(ctx);
   double out[40];
   if (!rc) {
@@ -829,6 +913,7 @@ int msckf_gating_test(msckf_ctx* ctx, int32_t f, const double* H, const double* 
   double* dg = buf + nH + m + nscr;
   int* dp = (int*)(dg + 1);
   launch_gate_dense(d, f, buf, buf + nH, m, n_state, dof, buf + nH + m, dg, dp, ctx->st);
+  ctx->launches += 1;
   int rc = sync_and_check(ctx);
   if (!rc || rc == MSCKF_ERR_NUMERIC) {
     double g;
@@ -864,6 +949,7 @@ int msckf_measurement_update(msckf_ctx* ctx, int32_t f, const double* H, const d
   launch_load_dense_H(d, f, buf, buf + nH, m, n_state, ctx->st);
   launch_qr(d, ctx->st);
   launch_update(d, 0, ctx->st);
+  ctx->launches += 3 + kUpdateLaunches;
   rc = sync_and_check(ctx);
   cudaFree(buf);
   return rc;
@@ -876,6 +962,7 @@ int msckf_find_redundant_cam_states(msckf_ctx* ctx, int32_t f, int64_t* cam_ids)
   long long* dout = nullptr;
   CK(cudaMalloc((void**)&dout, 2 * sizeof(long long)));
   launch_find_redundant(ctx->d, f, dout, ctx->st);
+  ctx->launches += 1;
   int rc = sync_and_check(ctx);
   if (!rc) cudaMemcpy(cam_ids, dout, 2 * sizeof(long long), cudaMemcpyDeviceToHost);
   cudaFree(dout);

@@ -417,7 +417,6 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
   if (tid == 0) {
     int m = (int)used_rows;
     const int N = d.ncam[f];
-    if (m > d.max_rows) { atomicOr(d.err, ERRBIT_ROWS); m = 0; }
     // active columns in logical order
     const unsigned long long act = s_act;
     int na = 0;

@@ -66,6 +66,19 @@ __device__ __forceinline__ double view_cost(const Views& V, int v, const double*
   return e0 * e0 + e1 * e1;
 }
 
+// generate_initial_guess (feature.py:99-122) between view 0 and view vl (both cam0 views):
+// the landmark in the frame of view 0.
+__device__ __forceinline__ void initial_guess(const Views& V, int vl, double* p) {
+  const double z1x = V.at(12, 0), z1y = V.at(13, 0), z2x = V.at(12, vl), z2y = V.at(13, vl);
+  const double m0 = V.at(0, vl) * z1x + V.at(1, vl) * z1y + V.at(2, vl);
+  const double m1 = V.at(3, vl) * z1x + V.at(4, vl) * z1y + V.at(5, vl);
+  const double m2 = V.at(6, vl) * z1x + V.at(7, vl) * z1y + V.at(8, vl);
+  const double a0 = m0 - z2x * m2, a1 = m1 - z2y * m2;
+  const double b0 = z2x * V.at(11, vl) - V.at(9, vl), b1 = z2y * V.at(11, vl) - V.at(10, vl);
+  const double depth = (a0 * b0 + a1 * b1) / (a0 * a0 + a1 * a1);
+  p[0] = z1x * depth; p[1] = z1y * depth; p[2] = 1.0 * depth;
+}
+
 // The solver proper.  Views 0..nv-1 are staged in V by the caller (all lanes, then __syncwarp).
 // Rf/tf = pose of the first cam0 (camera -> world).  Returns validity; writes world position.
 __device__ bool lm_solve(const Views& V, int nv, const TriCfg& cfg, const double* Rf, const double* tf, int lane,
@@ -74,15 +87,9 @@ __device__ bool lm_solve(const Views& V, int nv, const TriCfg& cfg, const double
   const int vl = nv - 2;
   double x[3];
   {
-    const double z1x = V.at(12, 0), z1y = V.at(13, 0), z2x = V.at(12, vl), z2y = V.at(13, vl);
-    const double m0 = V.at(0, vl) * z1x + V.at(1, vl) * z1y + V.at(2, vl);
-    const double m1 = V.at(3, vl) * z1x + V.at(4, vl) * z1y + V.at(5, vl);
-    const double m2 = V.at(6, vl) * z1x + V.at(7, vl) * z1y + V.at(8, vl);
-    const double a0 = m0 - z2x * m2, a1 = m1 - z2y * m2;
-    const double b0 = z2x * V.at(11, vl) - V.at(9, vl), b1 = z2y * V.at(11, vl) - V.at(10, vl);
-    const double depth = (a0 * b0 + a1 * b1) / (a0 * a0 + a1 * a1);
-    const double p0 = z1x * depth, p1 = z1y * depth, p2 = 1.0 * depth;
-    x[0] = p0 / p2; x[1] = p1 / p2; x[2] = 1.0 / p2;
+    double pg[3];
+    initial_guess(V, vl, pg);
+    x[0] = pg[0] / pg[2]; x[1] = pg[1] / pg[2]; x[2] = 1.0 / pg[2];
   }
   // ---- initial cost
   double total = 0;
@@ -270,7 +277,7 @@ __global__ void __launch_bounds__(TRI_WPB * 32) k_triangulate_raw(Dev d, int n, 
                                                                    const double* __restrict__ uv, const double* __restrict__ cam_q,
                                                                    const double* __restrict__ cam_p, double* __restrict__ pos_out,
                                                                    unsigned char* __restrict__ valid, int* __restrict__ solves,
-                                                                   int max_obs) {
+                                                                   int max_obs, int mode) {
   extern __shared__ double smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int i = blockIdx.x * TRI_WPB + warp;
@@ -287,10 +294,20 @@ __global__ void __launch_bounds__(TRI_WPB * 32) k_triangulate_raw(Dev d, int n, 
   bool ok = check_motion(cfg, Rf, tf, uv + 4 * (size_t)o0, cam_p + 3 * (size_t)(o0 + M - 1));
   double pos[3] = {0, 0, 0};
   int ns = 0;
+  if (mode == 1) {                       // Feature.check_motion only
+    if (lane == 0) valid[i] = ok ? 1 : 0;
+    return;
+  }
+  if (mode >= 2) ok = true;              // 2: generate_initial_guess only, 3: initialize_position without check_motion
   if (ok) {
     for (int a = lane; a < M; a += 32)
       stage_views(V, a, cam_q + 4 * (size_t)(o0 + a), cam_p + 3 * (size_t)(o0 + a), uv + 4 * (size_t)(o0 + a), Rf, tf, cfg);
     __syncwarp();
+    if (mode == 2) {
+      initial_guess(V, 2 * M - 2, pos);
+      if (lane == 0) { pos_out[3 * (size_t)i + 0] = pos[0]; pos_out[3 * (size_t)i + 1] = pos[1]; pos_out[3 * (size_t)i + 2] = pos[2]; }
+      return;
+    }
     ok = lm_solve(V, 2 * M, cfg, Rf, tf, lane, pos, &ns);
   }
   if (lane == 0) {
@@ -313,14 +330,14 @@ void launch_triangulate_store(const Dev& d, cudaStream_t st) {
 }
 
 void launch_triangulate_raw(const Dev& d, int n, const int* obs_off, const double* uv, const double* cam_q, const double* cam_p,
-                            double* pos, unsigned char* valid, int* solves, int max_obs, cudaStream_t st) {
+                            double* pos, unsigned char* valid, int* solves, int max_obs, int mode, cudaStream_t st) {
   const size_t smem = (size_t)TRI_WPB * VIEW_DOUBLES * 2 * max_obs * sizeof(double);
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(k_triangulate_raw, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     attr_set = true;
   }
-  k_triangulate_raw<<<(n + TRI_WPB - 1) / TRI_WPB, TRI_WPB * 32, smem, st>>>(d, n, obs_off, uv, cam_q, cam_p, pos, valid, solves, max_obs);
+  k_triangulate_raw<<<(n + TRI_WPB - 1) / TRI_WPB, TRI_WPB * 32, smem, st>>>(d, n, obs_off, uv, cam_q, cam_p, pos, valid, solves, max_obs, mode);
 }
 
 }  // namespace msckf

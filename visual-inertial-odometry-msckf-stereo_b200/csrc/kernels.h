@@ -23,7 +23,7 @@ void launch_find_redundant(const Dev& d, int filter, long long* out_ids, cudaStr
 // k_triangulate.cu
 void launch_triangulate_store(const Dev& d, cudaStream_t st);
 void launch_triangulate_raw(const Dev& d, int n, const int* obs_off, const double* uv, const double* cam_q, const double* cam_p,
-                            double* pos, unsigned char* valid, int* solves, int max_obs, cudaStream_t st);
+                            double* pos, unsigned char* valid, int* solves, int max_obs, int mode, cudaStream_t st);
 
 // k_jacobian.cu
 void launch_jacobian_gate(const Dev& d, cudaStream_t st);

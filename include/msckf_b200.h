@@ -72,6 +72,24 @@ enum {
   MSCKF_FEAT_AFTER_CAP = 5    /* after the row-cap break (msckf.py:678): never gated            */
 };
 
+/* Per-filter counters since creation (msckf_get_counters).  The *_FLOPS / *_BYTES entries accumulate the
+ * ALGORITHMIC work of the corresponding kernel family with the formulas of SURVEY.md section 8d (DESIGN.md
+ * restates them); bench.py divides them by measured kernel time for the roofline figures. */
+enum {
+  MSCKF_CNT_FEATURE_UPDATES = 0, /* landmarks taken through feature_jacobian + gating_test          */
+  MSCKF_CNT_TRIANGULATIONS = 1,  /* initialize_position calls                                        */
+  MSCKF_CNT_UPDATES = 2,         /* measurement updates with at least one row                        */
+  MSCKF_CNT_FRAMES = 3,          /* feature_callback / online_reset calls                            */
+  MSCKF_CNT_TRI_OBS = 4,         /* sum of M over triangulated landmarks                             */
+  MSCKF_CNT_TRI_SOLVES = 5,      /* damped 3x3 solves                                                */
+  MSCKF_CNT_JAC_OBS = 6,         /* sum of M over landmarks that reached the Jacobian                */
+  MSCKF_CNT_K2_FLOPS = 7, MSCKF_CNT_K2_BYTES = 8,   /* Jacobian + null space + gate                 */
+  MSCKF_CNT_QR_FLOPS = 9, MSCKF_CNT_QR_BYTES = 10,  /* stacked-H compression                        */
+  MSCKF_CNT_K4_FLOPS = 11, MSCKF_CNT_K4_BYTES = 12, /* gain + correction + covariance               */
+  MSCKF_CNT_IMU_STEPS = 13,      /* IMU samples integrated                                           */
+  MSCKF_N_COUNTERS = 16
+};
+
 typedef struct msckf_config {
   int32_t n_filters;          /* batch size F >= 1                                              */
   int32_t max_cam_states;     /* ConfigEuRoC._vio_max_cam_state_size__ (config.py:57), 4..64    */
@@ -163,6 +181,13 @@ int msckf_feature_callback_async(msckf_ctx* ctx, const int32_t* imu_off, const d
                                  const double* acc, const int64_t* cam_ids, const int32_t* feat_off,
                                  const int64_t* ids, const double* uv);
 int msckf_collect(msckf_ctx* ctx, double* imu_out, uint8_t* did_reset);
+/* Same stages with every input already in DEVICE memory (same layouts; the pointers are device pointers
+ * that must stay valid until the work has run).  Nothing is copied and nothing is waited for: frames can be
+ * enqueued back to back.  imu_out_dev (device, [F][MSCKF_IMU_STRIDE], may be NULL) receives the publish()
+ * snapshot of this frame.  Errors surface at the next msckf_sync. */
+int msckf_feature_callback_dev(msckf_ctx* ctx, const int32_t* imu_off, const double* ts, const double* gyro,
+                               const double* acc, const int64_t* cam_ids, const int32_t* feat_off, const int64_t* ids,
+                               const double* uv, double* imu_out_dev);
 
 /* ---- per-stage decision logs (bit-exact outputs: ids, gate decisions, removed cam ids) ---- */
 /* stage: 0 = last remove_lost_features, 1 = last prune_cam_states.  Entries are in map order.
@@ -170,8 +195,7 @@ int msckf_collect(msckf_ctx* ctx, double* imu_out, uint8_t* did_reset);
 int msckf_get_stage_log(msckf_ctx* ctx, int32_t filter, int32_t stage, int32_t* n_entries,
                         int64_t* feature_ids, int32_t* status, double* gamma, int32_t* dof,
                         int32_t* update_rows, int32_t* update_cols, int64_t* removed_cam_ids);
-/* Counters since creation: [0] feature-updates (features taken through feature_jacobian +
- * gating_test), [1] triangulations, [2] measurement updates, [3] frames. Per filter, [F][4]. */
+/* Counters since creation, per filter: counters[F][MSCKF_N_COUNTERS] (MSCKF_CNT_* above). */
 int msckf_get_counters(msckf_ctx* ctx, int64_t* counters);
 
 /* ---- directly callable pieces of the reference API ---------------------------------------- */
@@ -227,6 +251,24 @@ int msckf_set_timing(msckf_ctx* ctx, int32_t enabled);
 
 /* Number of CUDA kernels of this library enqueued on the context so far (bench.py: gpu_launches). */
 int msckf_kernel_launches(msckf_ctx* ctx, int64_t* n);
+/* Per-kernel accounting.  msckf_kernel_count() kernels, named by msckf_kernel_name(i).  With
+ * msckf_set_kernel_timing(ctx, 1) every launch is bracketed by two CUDA events on the context's stream;
+ * msckf_kernel_times waits for the stream and returns, per kernel, the launches counted since creation,
+ * the number of timed launches and their total device milliseconds (arrays of msckf_kernel_count()). */
+int msckf_kernel_count(void);
+const char* msckf_kernel_name(int32_t i);
+int msckf_set_kernel_timing(msckf_ctx* ctx, int32_t enabled);
+int msckf_kernel_times(msckf_ctx* ctx, int64_t* launches, int64_t* timed_launches, double* total_ms);
+
+/* Measures the FP64 peaks of the device with two register-resident microbenchmarks: DFMA chains (vector
+ * pipe) and mma.sync m8n8k4 f64 (DMMA, the FP64 tensor op), in TFLOP/s.  Roofline denominators for the FP64
+ * kernels; independent of any context. */
+int msckf_fp64_peak(int32_t device, double* dfma_tflops, double* dmma_tflops);
+
+/* Generic event pair on the context's stream for callers that time several calls from outside:
+ * msckf_mark(ctx, 0) ... msckf_mark(ctx, 1); msckf_mark_elapsed waits for mark 1 and returns the milliseconds. */
+int msckf_mark(msckf_ctx* ctx, int32_t which);
+int msckf_mark_elapsed(msckf_ctx* ctx, float* ms);
 
 /* Library build info, e.g. "msckf_b200 sm_100a cuda 12.9". */
 const char* msckf_version(void);

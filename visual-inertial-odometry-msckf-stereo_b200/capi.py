@@ -20,6 +20,9 @@ IMU_Q_NULL, IMU_V_NULL, IMU_P_NULL = 16, 20, 23
 IMU_R_IC, IMU_T_CI, IMU_GRAVITY, IMU_TIME = 26, 35, 38, 41
 IMU_NULL_ALIASED, IMU_TRACKING_RATE, IMU_STRIDE = 42, 43, 48
 CAM_STRIDE = 16
+N_COUNTERS = 16
+(CNT_FEATURE_UPDATES, CNT_TRIANGULATIONS, CNT_UPDATES, CNT_FRAMES, CNT_TRI_OBS, CNT_TRI_SOLVES, CNT_JAC_OBS, CNT_K2_FLOPS,
+ CNT_K2_BYTES, CNT_QR_FLOPS, CNT_QR_BYTES, CNT_K4_FLOPS, CNT_K4_BYTES, CNT_IMU_STEPS) = range(14)
 FEAT_FEW_OBS, FEAT_TRI_FAILED, FEAT_GATE_PASS, FEAT_GATE_FAIL, FEAT_AFTER_CAP = 1, 2, 3, 4, 5
 
 ERR_ARG, ERR_CUDA, ERR_CAPACITY, ERR_NUMERIC = -1, -2, -3, -4
@@ -86,6 +89,7 @@ SIGNATURES = {
     'msckf_feature_callback': [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     'msckf_feature_callback_async': [_P, _P, _P, _P, _P, _P, _P, _P, _P],
     'msckf_collect': [_P, _P, _P],
+    'msckf_feature_callback_dev': [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     'msckf_get_stage_log': [_P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P],
     'msckf_get_counters': [_P, _P],
     'msckf_triangulate': [_P, _I, _P, _P, _P, _P, _P, _P, _P],
@@ -100,9 +104,17 @@ SIGNATURES = {
     'msckf_last_timing': [_P, _P],
     'msckf_set_timing': [_P, _I],
     'msckf_kernel_launches': [_P, _P],
+    'msckf_kernel_count': [],
+    'msckf_kernel_name': [_I],
+    'msckf_set_kernel_timing': [_P, _I],
+    'msckf_kernel_times': [_P, _P, _P, _P],
+    'msckf_fp64_peak': [_I, _P, _P],
+    'msckf_mark': [_P, _I],
+    'msckf_mark_elapsed': [_P, _P],
     'msckf_version': [],
 }
-_RESTYPE = {'msckf_destroy': None, 'msckf_last_error': C.c_char_p, 'msckf_version': C.c_char_p}
+_RESTYPE = {'msckf_destroy': None, 'msckf_last_error': C.c_char_p, 'msckf_version': C.c_char_p,
+            'msckf_kernel_name': C.c_char_p}
 
 _lib = None
 
@@ -366,9 +378,31 @@ class Context(object):
                 'update_rows': ur.value, 'update_cols': uc.value, 'removed_cam_ids': rm}
 
     def counters(self):
-        out = np.zeros((self.F, 4), dtype=np.int64)
+        out = np.zeros((self.F, N_COUNTERS), dtype=np.int64)
         self._ck(self.lib.msckf_get_counters(self.h, _ptr(out)))
         return out
+
+    def feature_callback_dev(self, imu_off, ts, gyro, acc, cam_ids, feat_off, ids, uv, imu_out=0):
+        """All arguments are raw DEVICE addresses (ints), e.g. torch ``tensor.data_ptr()``."""
+        self._ck(self.lib.msckf_feature_callback_dev(self.h, imu_off, ts, gyro, acc, cam_ids, feat_off, ids, uv, imu_out or None))
+
+    def mark(self, which):
+        self._ck(self.lib.msckf_mark(self.h, int(which)))
+
+    def mark_elapsed_ms(self):
+        ms = C.c_float(0)
+        self._ck(self.lib.msckf_mark_elapsed(self.h, C.addressof(ms)))
+        return ms.value
+
+    def set_kernel_timing(self, on):
+        self._ck(self.lib.msckf_set_kernel_timing(self.h, int(bool(on))))
+
+    def kernel_times(self):
+        """{kernel name: (launches, timed launches, total ms of the timed launches)}"""
+        k = self.lib.msckf_kernel_count()
+        la, tl, ms = np.zeros(k, dtype=np.int64), np.zeros(k, dtype=np.int64), np.zeros(k)
+        self._ck(self.lib.msckf_kernel_times(self.h, _ptr(la), _ptr(tl), _ptr(ms)))
+        return dict((self.lib.msckf_kernel_name(i).decode(), (int(la[i]), int(tl[i]), float(ms[i]))) for i in range(k))
 
     def kernel_launches(self):
         n = C.c_int64(0)
@@ -443,6 +477,15 @@ class Context(object):
         ms = np.zeros(5, dtype=np.float32)
         self._ck(self.lib.msckf_last_timing(self.h, _ptr(ms)))
         return ms
+
+
+def fp64_peak(device=0):
+    """(DFMA TFLOP/s, DMMA TFLOP/s) measured on the device."""
+    a, b = C.c_double(0), C.c_double(0)
+    rc = load_library().msckf_fp64_peak(int(device), C.addressof(a), C.addressof(b))
+    if rc != 0:
+        raise MsckfCudaError(rc, 'msckf_fp64_peak failed')
+    return a.value, b.value
 
 
 def version():

@@ -10,6 +10,49 @@
 
 using namespace msckf;
 
+namespace msckf {
+const char* const kKernelNames[KID_COUNT] = {
+    "k_propagate", "k_augment", "k_observe", "k_classify_lost", "k_prune_select", "k_triangulate", "k_plan_items",
+    "k_jacobian_gate", "k_plan_stack", "k_stack", "k_qr", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
+    "k_upd_downdate", "k_remove_cams", "k_finish_frame", "k_reset", "misc"};
+
+void KTimer::begin(int id, cudaStream_t st) {
+  launches[id] += 1;
+  if (!timing) return;
+  if (pool.size() < 2 * (pending.size() + 1)) {
+    cudaEvent_t a, b;
+    cudaEventCreate(&a);
+    cudaEventCreate(&b);
+    pool.push_back(a);
+    pool.push_back(b);
+  }
+  cudaEventRecord(pool[2 * pending.size()], st);
+  pending.push_back(id);
+}
+void KTimer::end(cudaStream_t st) {
+  if (!timing) return;
+  cudaEventRecord(pool[2 * pending.size() - 1], st);
+  if (pending.size() >= 8192) flush(st);
+}
+void KTimer::flush(cudaStream_t st) {
+  if (pending.empty()) return;
+  cudaStreamSynchronize(st);
+  for (size_t i = 0; i < pending.size(); ++i) {
+    float t = 0;
+    if (cudaEventElapsedTime(&t, pool[2 * i], pool[2 * i + 1]) == cudaSuccess) {
+      ms[pending[i]] += t;
+      timed[pending[i]] += 1;
+    }
+  }
+  pending.clear();
+}
+void KTimer::release() {
+  for (cudaEvent_t e : pool) cudaEventDestroy(e);
+  pool.clear();
+  pending.clear();
+}
+}  // namespace msckf
+
 namespace {
 thread_local std::string g_create_error;
 
@@ -36,9 +79,10 @@ struct msckf_ctx {
   std::string err;
   bool timing = false;
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t mark[2] = {nullptr, nullptr};
   float last_ms[5] = {0, 0, 0, 0, 0};
   bool frame_pending = false;
-  long long launches = 0;           // kernels of this library enqueued so far
+  KTimer kt;                        // launch counts / optional per-kernel event timing
 };
 
 #define CK(call)                                                                                   \
@@ -173,9 +217,11 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   CKC(cudaStreamCreateWithFlags(&ctx->st, cudaStreamNonBlocking));
   for (auto& s : ctx->stg) CKC(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
   for (auto& evn : ctx->ev) CKC(cudaEventCreate(&evn));
+  for (auto& evn : ctx->mark) CKC(cudaEventCreate(&evn));
 
   Dev& d = ctx->d;
   memset(&d, 0, sizeof d);
+  d.host_timer = &ctx->kt;
   d.F = cfg->n_filters;
   d.Nmax = cfg->max_cam_states;
   d.nmax = NI + 6 * d.Nmax;
@@ -237,7 +283,7 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   DA(d.T, F * (size_t)d.Tk * Tld(d)); DA(d.S, F * (size_t)d.Tk * d.Tk); DA(d.dx, F * (size_t)d.nmax);
   DA(d.log_id, 2 * F * Fc); DA(d.log_status, 2 * F * Fc); DA(d.log_gamma, 2 * F * Fc); DA(d.log_dof, 2 * F * Fc);
   DA(d.log_n, 2 * F); DA(d.log_upd, 2 * F * 2); DA(d.log_rm, F * 2);
-  DA(d.counters, F * 4); DA(d.err, 1); DA(d.did_reset, F); DA(d.imu_pub, F * IMU_STRIDE);
+  DA(d.counters, F * NCNT); DA(d.err, 1); DA(d.did_reset, F); DA(d.imu_pub, F * IMU_STRIDE);
 #undef DA
   CKC(cudaMallocHost((void**)&ctx->h_pub, F * IMU_STRIDE * sizeof(double)));
   CKC(cudaMallocHost((void**)&ctx->h_reset, F));
@@ -274,6 +320,8 @@ void msckf_destroy(msckf_ctx* ctx) {
     if (s.done) cudaEventDestroy(s.done);
   }
   for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
+  ctx->kt.release();
+  for (auto& e : ctx->mark) if (e) cudaEventDestroy(e);
   if (ctx->h_pub) cudaFreeHost(ctx->h_pub);
   if (ctx->h_reset) cudaFreeHost(ctx->h_reset);
   if (ctx->h_err) cudaFreeHost(ctx->h_err);
@@ -504,7 +552,6 @@ int msckf_set_feature_position(msckf_ctx* ctx, int32_t f, int64_t id, const doub
 }
 
 // ------------------------------------------------------------------ stage enqueue helpers
-constexpr int kUpdateLaunches = 6;   // launch_update: T, S, chol, trsm, inject, downdate
 static void enqueue_lost_stage(msckf_ctx* ctx) {
   const Dev& d = ctx->d;
   cudaMemsetAsync(d.pool_used, 0, sizeof(unsigned long long), ctx->st);
@@ -516,7 +563,6 @@ static void enqueue_lost_stage(msckf_ctx* ctx) {
   launch_stack(d, ctx->st);
   launch_qr(d, ctx->st);
   launch_update(d, 0, ctx->st);
-  ctx->launches += 7 + kUpdateLaunches;
 }
 static void enqueue_prune_stage(msckf_ctx* ctx) {
   const Dev& d = ctx->d;
@@ -530,7 +576,6 @@ static void enqueue_prune_stage(msckf_ctx* ctx) {
   launch_qr(d, ctx->st);
   launch_update(d, 1, ctx->st);
   launch_remove_cams(d, ctx->st);
-  ctx->launches += 8 + kUpdateLaunches;
 }
 
 int msckf_propagate(msckf_ctx* ctx, const int32_t* imu_off, const double* ts, const double* gyro, const double* acc) {
@@ -547,7 +592,6 @@ int msckf_propagate(msckf_ctx* ctx, const int32_t* imu_off, const double* ts, co
   if (rc) return rc;
   char* b = p.s->d;
   launch_propagate(ctx->d, (const int*)(b + o0), (const double*)(b + o1), (const double*)(b + o2), (const double*)(b + o3), ctx->st);
-  ctx->launches += 1;
   stage_end(ctx, p);
   CK(cudaGetLastError());
   return MSCKF_OK;
@@ -563,7 +607,6 @@ int msckf_augment(msckf_ctx* ctx, const int64_t* cam_ids) {
   int rc = stage_commit(ctx, p);
   if (rc) return rc;
   launch_augment(ctx->d, (const long long*)(p.s->d + o0), ctx->st);
-  ctx->launches += 1;
   stage_end(ctx, p);
   CK(cudaGetLastError());
   return MSCKF_OK;
@@ -582,7 +625,6 @@ int msckf_add_observations(msckf_ctx* ctx, const int32_t* feat_off, const int64_
   if (rc) return rc;
   char* b = p.s->d;
   launch_observe(ctx->d, (const int*)(b + o0), (const long long*)(b + o1), (const double*)(b + o2), ctx->st);
-  ctx->launches += 1;
   stage_end(ctx, p);
   CK(cudaGetLastError());
   return MSCKF_OK;
@@ -608,7 +650,6 @@ int msckf_online_reset(msckf_ctx* ctx, uint8_t* did_reset) {
   if (!ctx) return MSCKF_ERR_ARG;
   CK(cudaSetDevice(ctx->device));
   launch_finish_frame(ctx->d, 1, ctx->st);
-  ctx->launches += 1;
   CK(cudaMemcpyAsync(ctx->h_reset, ctx->d.did_reset, ctx->d.F, cudaMemcpyDeviceToHost, ctx->st));
   int rc = sync_and_check(ctx);
   if (rc) return rc;
@@ -655,7 +696,6 @@ int msckf_feature_callback_async(msckf_ctx* ctx, const int32_t* imu_off, const d
   enqueue_prune_stage(ctx);
   if (tm) cudaEventRecord(ctx->ev[4], ctx->st);
   launch_finish_frame(d, 1, ctx->st);
-  ctx->launches += 4;              // propagate, augment, observe, finish_frame (stages count their own)
   if (tm) cudaEventRecord(ctx->ev[5], ctx->st);
   stage_end(ctx, p);
   CK(cudaMemcpyAsync(ctx->h_pub, d.imu_pub, (size_t)F * IMU_STRIDE * sizeof(double), cudaMemcpyDeviceToHost, ctx->st));
@@ -663,6 +703,26 @@ int msckf_feature_callback_async(msckf_ctx* ctx, const int32_t* imu_off, const d
   CK(cudaMemcpyAsync(ctx->h_err, d.err, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->st));
   CK(cudaGetLastError());
   ctx->frame_pending = true;
+  return MSCKF_OK;
+}
+
+int msckf_feature_callback_dev(msckf_ctx* ctx, const int32_t* imu_off, const double* ts, const double* gyro, const double* acc,
+                               const int64_t* cam_ids, const int32_t* feat_off, const int64_t* ids, const double* uv,
+                               double* imu_out_dev) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  ARG(imu_off && cam_ids && feat_off, "offset / id pointers");
+  ARG(!ctx->frame_pending, "previous frame not collected");
+  CK(cudaSetDevice(ctx->device));
+  const Dev& d = ctx->d;
+  launch_propagate(d, imu_off, ts, gyro, acc, ctx->st);
+  launch_augment(d, (const long long*)cam_ids, ctx->st);
+  launch_observe(d, feat_off, (const long long*)ids, uv, ctx->st);
+  enqueue_lost_stage(ctx);
+  enqueue_prune_stage(ctx);
+  launch_finish_frame(d, 1, ctx->st);
+  if (imu_out_dev)
+    CK(cudaMemcpyAsync(imu_out_dev, d.imu_pub, (size_t)d.F * IMU_STRIDE * sizeof(double), cudaMemcpyDeviceToDevice, ctx->st));
+  CK(cudaGetLastError());
   return MSCKF_OK;
 }
 
@@ -737,7 +797,7 @@ int msckf_get_counters(msckf_ctx* ctx, int64_t* counters) {
   CK(cudaSetDevice(ctx->device));
   int rc = sync_and_check(ctx);
   if (rc) return rc;
-  CK(cudaMemcpy(counters, ctx->d.counters, (size_t)ctx->d.F * 4 * sizeof(int64_t), cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(counters, ctx->d.counters, (size_t)ctx->d.F * NCNT * sizeof(int64_t), cudaMemcpyDeviceToHost));
   return MSCKF_OK;
 }
 
@@ -772,7 +832,6 @@ static int triangulate_call(msckf_ctx* ctx, int mode, int32_t n, const int32_t* 
   char* b = p.s->d;
   launch_triangulate_raw(ctx->d, n, (const int*)(b + o0), (const double*)(b + o1), (const double*)(b + o2), (const double*)(b + o3), dpos,
                          dval, dsol, max_obs, mode, ctx->st);
-  ctx->launches += 1;
   stage_end(ctx, p);
   rc = sync_and_check(ctx);
   if (!rc) {
@@ -810,7 +869,47 @@ int msckf_initialize_position(msckf_ctx* ctx, int32_t n, const int32_t* obs_off,
 
 int msckf_kernel_launches(msckf_ctx* ctx, int64_t* n) {
   if (!ctx || !n) return MSCKF_ERR_ARG;
-  *n = ctx->launches;
+  long long t = 0;
+  for (int i = 0; i < KID_COUNT; ++i) t += ctx->kt.launches[i];
+  *n = t;
+  return MSCKF_OK;
+}
+
+int msckf_mark(msckf_ctx* ctx, int32_t which) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  ARG(which == 0 || which == 1, "mark index");
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaEventRecord(ctx->mark[which], ctx->st));
+  return MSCKF_OK;
+}
+int msckf_mark_elapsed(msckf_ctx* ctx, float* ms) {
+  if (!ctx || !ms) return MSCKF_ERR_ARG;
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaEventSynchronize(ctx->mark[1]));
+  CK(cudaEventElapsedTime(ms, ctx->mark[0], ctx->mark[1]));
+  return MSCKF_OK;
+}
+
+int msckf_kernel_count(void) { return KID_COUNT; }
+const char* msckf_kernel_name(int32_t i) { return (i >= 0 && i < KID_COUNT) ? kKernelNames[i] : ""; }
+
+int msckf_set_kernel_timing(msckf_ctx* ctx, int32_t enabled) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  CK(cudaSetDevice(ctx->device));
+  ctx->kt.flush(ctx->st);
+  ctx->kt.timing = enabled != 0;
+  return MSCKF_OK;
+}
+
+int msckf_kernel_times(msckf_ctx* ctx, int64_t* launches, int64_t* timed_launches, double* total_ms) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  CK(cudaSetDevice(ctx->device));
+  ctx->kt.flush(ctx->st);
+  for (int i = 0; i < KID_COUNT; ++i) {
+    if (launches) launches[i] = ctx->kt.launches[i];
+    if (timed_launches) timed_launches[i] = ctx->kt.timed[i];
+    if (total_ms) total_ms[i] = ctx->kt.ms[i];
+  }
   return MSCKF_OK;
 }
 
@@ -852,7 +951,6 @@ int msckf_feature_jacobian(msckf_ctx* ctx, int32_t f, int64_t feature_id, int32_
   CK(cudaMemcpyAsync(d.nitem + f, &one, sizeof(int), cudaMemcpyHostToDevice, ctx->st));
   CK(cudaStreamSynchronize(ctx->st));      // the small host sources above live on this stack frame
   launch_jacobian_gate(d, ctx->st);
-  ctx->launches += 2;
   double* dH = nullptr;
   CK(cudaMalloc((void**)&dH, ((size_t)rows * n_state + rows) * sizeof(double)));
   launch_export_item_dense(d, f, dH, dH + (size_t)rows * n_state, n_state, ctx->st);
@@ -886,7 +984,6 @@ int msckf_measurement_jacobian(msckf_ctx* ctx, int32_t f, int64_t cam_id, int64_
   double* dout = nullptr;
   CK(cudaMalloc((void**)&dout, 40 * sizeof(double)));
   launch_measurement_jacobian(d, f, c, slot, dout, ctx->st);
-  ctx->launches += 1;
   rc = sync_and_check(ctx);
   double out[40];
   if (!rc) {
@@ -913,7 +1010,6 @@ int msckf_gating_test(msckf_ctx* ctx, int32_t f, const double* H, const double* 
   double* dg = buf + nH + m + nscr;
   int* dp = (int*)(dg + 1);
   launch_gate_dense(d, f, buf, buf + nH, m, n_state, dof, buf + nH + m, dg, dp, ctx->st);
-  ctx->launches += 1;
   int rc = sync_and_check(ctx);
   if (!rc || rc == MSCKF_ERR_NUMERIC) {
     double g;
@@ -949,7 +1045,6 @@ int msckf_measurement_update(msckf_ctx* ctx, int32_t f, const double* H, const d
   launch_load_dense_H(d, f, buf, buf + nH, m, n_state, ctx->st);
   launch_qr(d, ctx->st);
   launch_update(d, 0, ctx->st);
-  ctx->launches += 3 + kUpdateLaunches;
   rc = sync_and_check(ctx);
   cudaFree(buf);
   return rc;
@@ -962,7 +1057,6 @@ int msckf_find_redundant_cam_states(msckf_ctx* ctx, int32_t f, int64_t* cam_ids)
   long long* dout = nullptr;
   CK(cudaMalloc((void**)&dout, 2 * sizeof(long long)));
   launch_find_redundant(ctx->d, f, dout, ctx->st);
-  ctx->launches += 1;
   int rc = sync_and_check(ctx);
   if (!rc) cudaMemcpy(cam_ids, dout, 2 * sizeof(long long), cudaMemcpyDeviceToHost);
   cudaFree(dout);

@@ -324,21 +324,21 @@ __global__ void __launch_bounds__(256) k_gate_dense(Dev d, int f, const double* 
 
 void launch_jacobian_gate(const Dev& d, cudaStream_t st) {
   dim3 grid((d.Fcap + JAC_WPB - 1) / JAC_WPB, d.F);
-  k_jacobian_gate<<<grid, JAC_WPB * 32, 0, st>>>(d);
+  KLAUNCH(d, KID_JACOBIAN_GATE, st, (k_jacobian_gate<<<grid, JAC_WPB * 32, 0, st>>>(d)));
 }
 void launch_stack(const Dev& d, cudaStream_t st) {
   dim3 grid((d.Fcap + JAC_WPB - 1) / JAC_WPB, d.F);
-  k_stack<<<grid, JAC_WPB * 32, 0, st>>>(d);
+  KLAUNCH(d, KID_STACK, st, (k_stack<<<grid, JAC_WPB * 32, 0, st>>>(d)));
 }
 void launch_measurement_jacobian(const Dev& d, int filter, int cam_logical, int slot, double* out, cudaStream_t st) {
-  k_measurement_jacobian<<<1, 32, 0, st>>>(d, filter, cam_logical, slot, out);
+  KLAUNCH(d, KID_MISC, st, (k_measurement_jacobian<<<1, 32, 0, st>>>(d, filter, cam_logical, slot, out)));
 }
 void launch_export_item_dense(const Dev& d, int filter, double* H, double* r, int n_state, cudaStream_t st) {
-  k_export_item_dense<<<1, 256, 0, st>>>(d, filter, H, r, n_state);
+  KLAUNCH(d, KID_MISC, st, (k_export_item_dense<<<1, 256, 0, st>>>(d, filter, H, r, n_state)));
 }
 void launch_gate_dense(const Dev& d, int filter, const double* H, const double* r, int m, int n_state, int dof, double* scratch,
                        double* out_gamma, int* out_pass, cudaStream_t st) {
-  k_gate_dense<<<1, 256, 0, st>>>(d, filter, H, r, m, n_state, dof, scratch, out_gamma, out_pass);
+  KLAUNCH(d, KID_MISC, st, (k_gate_dense<<<1, 256, 0, st>>>(d, filter, H, r, m, n_state, dof, scratch, out_gamma, out_pass)));
 }
 
 }  // namespace msckf

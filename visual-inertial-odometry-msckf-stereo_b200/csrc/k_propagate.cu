@@ -250,6 +250,7 @@ __global__ void __launch_bounds__(PT) k_propagate(Dev d, const int* __restrict__
 
   // ---- write back: IMU state, P_II, P_IC = Phi_acc P_IC and its mirror
   for (int e = tid; e < IMU_STRIDE; e += PT) imu[e] = sx[e];
+  if (tid == 0) d.counters[NCNT * f + MSCKF_CNT_IMU_STEPS] += k1 - k0;
   for (int e = tid; e < 441; e += PT) {
     const int i = e / 21, j = e - 21 * i;
     P[(size_t)i * ld + j] = sPII[e];
@@ -368,7 +369,7 @@ __global__ void __launch_bounds__(PT) k_finish_frame(Dev d, int do_reset_check) 
   const int f = blockIdx.x, tid = threadIdx.x;
   const double* imu = d.imu + (size_t)f * IMU_STRIDE;
   for (int e = tid; e < IMU_STRIDE; e += PT) d.imu_pub[(size_t)f * IMU_STRIDE + e] = imu[e];
-  if (tid == 0) d.counters[4 * f + 3] += 1;
+  if (tid == 0) d.counters[NCNT * f + MSCKF_CNT_FRAMES] += 1;
   if (!do_reset_check) return;
   __shared__ int s_reset;
   if (tid == 0) {
@@ -464,15 +465,17 @@ __global__ void __launch_bounds__(PT) k_remove_cams(Dev d) {
 
 // ------------------------------------------------------------------ launchers
 void launch_propagate(const Dev& d, const int* imu_off, const double* ts, const double* gyro, const double* acc, cudaStream_t st) {
-  k_propagate<<<d.F, PT, 0, st>>>(d, imu_off, ts, gyro, acc);
+  KLAUNCH(d, KID_PROPAGATE, st, (k_propagate<<<d.F, PT, 0, st>>>(d, imu_off, ts, gyro, acc)));
 }
-void launch_augment(const Dev& d, const long long* ids, cudaStream_t st) { k_augment<<<d.F, PT, 0, st>>>(d, ids); }
-void launch_finish_frame(const Dev& d, int do_reset_check, cudaStream_t st) { k_finish_frame<<<d.F, PT, 0, st>>>(d, do_reset_check); }
+void launch_augment(const Dev& d, const long long* ids, cudaStream_t st) { KLAUNCH(d, KID_AUGMENT, st, (k_augment<<<d.F, PT, 0, st>>>(d, ids))); }
+void launch_finish_frame(const Dev& d, int do_reset_check, cudaStream_t st) {
+  KLAUNCH(d, KID_FINISH_FRAME, st, (k_finish_frame<<<d.F, PT, 0, st>>>(d, do_reset_check)));
+}
 void launch_reset(const Dev& d, int only_filter, int reset_imu, cudaStream_t st) {
-  k_reset<<<only_filter >= 0 ? 1 : d.F, PT, 0, st>>>(d, only_filter, reset_imu);
+  KLAUNCH(d, KID_RESET, st, (k_reset<<<only_filter >= 0 ? 1 : d.F, PT, 0, st>>>(d, only_filter, reset_imu)));
 }
 void launch_remove_cams(const Dev& d, cudaStream_t st) {
-  k_remove_cams<<<d.F, PT, (size_t)RB * d.ld * sizeof(double), st>>>(d);
+  KLAUNCH(d, KID_REMOVE_CAMS, st, (k_remove_cams<<<d.F, PT, (size_t)RB * d.ld * sizeof(double), st>>>(d)));
 }
 
 }  // namespace msckf

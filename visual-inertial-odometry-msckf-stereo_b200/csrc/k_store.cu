@@ -308,6 +308,7 @@ __global__ void __launch_bounds__(ST) k_plan_items(Dev d, int stage) {
   const unsigned long long rmm = d.rm_mask[f];
   int ni = 0;
   long long elems_total = 0;
+  long long w_obs = 0, w_flops = 0, w_bytes = 0;   // algorithmic work of the Jacobian / gate kernel
   // pass A: ordered item list + relative offsets
   for (int t0 = 0; t0 < nc; t0 += ST) {
     const int ci = t0 + tid;
@@ -338,6 +339,10 @@ __global__ void __launch_bounds__(ST) k_plan_items(Dev d, int stage) {
       d.item_pass[k] = 0;
       d.item_gamma[k] = 0.0;
       d.item_rowoff[k] = -1;
+      const long long Ml = M, R = rows, C6 = 6 * Ml;
+      w_obs += Ml;
+      w_flops += 300 * Ml + 12 * (4 * Ml) * (C6 + 1) + 2 * R * C6 * C6 + 2 * R * R * C6 + (R * R * R) / 3 + 2 * R * R;
+      w_bytes += 36 * Ml + 8 * R * (C6 + 1);
     }
     ni += tot;
     elems_total += tot_e;
@@ -358,6 +363,12 @@ __global__ void __launch_bounds__(ST) k_plan_items(Dev d, int stage) {
   __syncthreads();
   const long long base = (long long)s_base;
   for (int k = tid; k < ni; k += ST) d.item_off[(size_t)f * d.Fcap + k] += base;
+  if (w_obs && ni > 0) {
+    unsigned long long* cnt = (unsigned long long*)(d.counters + (size_t)NCNT * f);
+    atomicAdd(cnt + MSCKF_CNT_JAC_OBS, (unsigned long long)w_obs);
+    atomicAdd(cnt + MSCKF_CNT_K2_FLOPS, (unsigned long long)w_flops);
+    atomicAdd(cnt + MSCKF_CNT_K2_BYTES, (unsigned long long)w_bytes);
+  }
 }
 
 // ------------------------------------------------------------------ stacking plan + decision log
@@ -432,20 +443,38 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
     d.log_n[stage * d.F + f] = nc;
     d.log_upd[((size_t)stage * d.F + f) * 2 + 0] = m;
     d.log_upd[((size_t)stage * d.F + f) * 2 + 1] = NI + 6 * N;
-    d.counters[4 * f + 0] += s_proc;
-    if (m > 0) d.counters[4 * f + 2] += 1;
+    long long* cnt = d.counters + (size_t)NCNT * f;
+    cnt[MSCKF_CNT_FEATURE_UPDATES] += s_proc;
+    if (m > 0) {
+      const long long mm = m, a = na, k = d.k_rows[f], n = NI + 6 * N;
+      cnt[MSCKF_CNT_UPDATES] += 1;
+      if (mm > a) {            // 2 m nc^2 - (2/3) nc^3 + 4 m nc ; bytes 8 m (nc+1) + 8 nc^2
+        cnt[MSCKF_CNT_QR_FLOPS] += 2 * mm * a * a - (2 * a * a * a) / 3 + 4 * mm * a;
+        cnt[MSCKF_CNT_QR_BYTES] += 8 * mm * (a + 1) + 8 * a * a;
+      }
+      cnt[MSCKF_CNT_K4_FLOPS] += 4 * k * n * n + 3 * k * k * n + (k * k * k) / 3;   // K4: 4kn^2 + 3k^2n + k^3/3
+      cnt[MSCKF_CNT_K4_BYTES] += 16 * n * n + 8 * k * n;
+    }
   }
 }
 
 void launch_observe(const Dev& d, const int* feat_off, const long long* ids, const double* uv, cudaStream_t st) {
-  k_observe<<<d.F, ST, 0, st>>>(d, feat_off, ids, uv);
+  KLAUNCH(d, KID_OBSERVE, st, (k_observe<<<d.F, ST, 0, st>>>(d, feat_off, ids, uv)));
 }
-void launch_classify_lost(const Dev& d, cudaStream_t st) { k_classify_lost<<<d.F, ST, 0, st>>>(d); }
-void launch_plan_items(const Dev& d, int stage, cudaStream_t st) { k_plan_items<<<d.F, ST, 0, st>>>(d, stage); }
-void launch_plan_stack(const Dev& d, int stage, cudaStream_t st) { k_plan_stack<<<d.F, ST, 0, st>>>(d, stage); }
-void launch_prune_select(const Dev& d, cudaStream_t st) { k_prune_select<<<d.F, ST, 0, st>>>(d); }
+void launch_classify_lost(const Dev& d, cudaStream_t st) {
+  KLAUNCH(d, KID_CLASSIFY_LOST, st, (k_classify_lost<<<d.F, ST, 0, st>>>(d)));
+}
+void launch_plan_items(const Dev& d, int stage, cudaStream_t st) {
+  KLAUNCH(d, KID_PLAN_ITEMS, st, (k_plan_items<<<d.F, ST, 0, st>>>(d, stage)));
+}
+void launch_plan_stack(const Dev& d, int stage, cudaStream_t st) {
+  KLAUNCH(d, KID_PLAN_STACK, st, (k_plan_stack<<<d.F, ST, 0, st>>>(d, stage)));
+}
+void launch_prune_select(const Dev& d, cudaStream_t st) {
+  KLAUNCH(d, KID_PRUNE_SELECT, st, (k_prune_select<<<d.F, ST, 0, st>>>(d)));
+}
 void launch_find_redundant(const Dev& d, int filter, long long* out_ids, cudaStream_t st) {
-  k_find_redundant<<<1, 32, 0, st>>>(d, filter, out_ids);
+  KLAUNCH(d, KID_MISC, st, (k_find_redundant<<<1, 32, 0, st>>>(d, filter, out_ids)));
 }
 
 }  // namespace msckf

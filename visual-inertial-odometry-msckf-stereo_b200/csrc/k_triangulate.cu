@@ -258,10 +258,14 @@ __global__ void __launch_bounds__(TRI_WPB * 32) k_triangulate_store(Dev d) {
       }
     }
     __syncwarp();
-    ok = lm_solve(V, 2 * M, cfg, Rf, tf, lane, pos, nullptr);
+    int ns = 0;
+    ok = lm_solve(V, 2 * M, cfg, Rf, tf, lane, pos, &ns);
     if (lane == 0) {
       d.f_pos[fs * 3 + 0] = pos[0]; d.f_pos[fs * 3 + 1] = pos[1]; d.f_pos[fs * 3 + 2] = pos[2];
-      atomicAdd((unsigned long long*)&d.counters[4 * f + 1], 1ull);
+      unsigned long long* cnt = (unsigned long long*)(d.counters + (size_t)NCNT * f);
+      atomicAdd(cnt + MSCKF_CNT_TRIANGULATIONS, 1ull);
+      atomicAdd(cnt + MSCKF_CNT_TRI_OBS, (unsigned long long)M);
+      atomicAdd(cnt + MSCKF_CNT_TRI_SOLVES, (unsigned long long)ns);
     }
   }
   if (lane == 0) {
@@ -326,7 +330,7 @@ void launch_triangulate_store(const Dev& d, cudaStream_t st) {
     attr_set = true;
   }
   dim3 grid((d.Fcap + TRI_WPB - 1) / TRI_WPB, d.F);
-  k_triangulate_store<<<grid, TRI_WPB * 32, smem, st>>>(d);
+  KLAUNCH(d, KID_TRIANGULATE, st, (k_triangulate_store<<<grid, TRI_WPB * 32, smem, st>>>(d)));
 }
 
 void launch_triangulate_raw(const Dev& d, int n, const int* obs_off, const double* uv, const double* cam_q, const double* cam_p,
@@ -337,7 +341,9 @@ void launch_triangulate_raw(const Dev& d, int n, const int* obs_off, const doubl
     cudaFuncSetAttribute(k_triangulate_raw, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     attr_set = true;
   }
-  k_triangulate_raw<<<(n + TRI_WPB - 1) / TRI_WPB, TRI_WPB * 32, smem, st>>>(d, n, obs_off, uv, cam_q, cam_p, pos, valid, solves, max_obs, mode);
+  KLAUNCH(d, KID_TRIANGULATE, st,
+          (k_triangulate_raw<<<(n + TRI_WPB - 1) / TRI_WPB, TRI_WPB * 32, smem, st>>>(d, n, obs_off, uv, cam_q, cam_p, pos, valid, solves,
+                                                                                   max_obs, mode)));
 }
 
 }  // namespace msckf

@@ -334,26 +334,26 @@ __global__ void k_zero_krows_except(Dev d, int keep) {
   if (f < d.F && f != keep) { d.k_rows[f] = 0; d.m_rows[f] = 0; }
 }
 
-void launch_qr(const Dev& d, cudaStream_t st) { k_qr<<<d.F, UT, 0, st>>>(d); }
+void launch_qr(const Dev& d, cudaStream_t st) { KLAUNCH(d, KID_QR, st, (k_qr<<<d.F, UT, 0, st>>>(d))); }
 
 void launch_update(const Dev& d, int stage, cudaStream_t st) {
   (void)stage;
   const int tn = (d.nmax + 1 + 31) / 32, tk = (d.Tk + 31) / 32, tp = (d.nmax + 31) / 32;
-  k_upd_T<<<dim3(tn, tk, d.F), UT, 0, st>>>(d);
-  k_upd_S<<<dim3(tk, tk, d.F), UT, 0, st>>>(d);
-  k_upd_chol<<<d.F, UT, 0, st>>>(d);
-  k_upd_trsm<<<dim3(tn, d.F), UT, 0, st>>>(d);
-  k_upd_inject<<<d.F, UT, 0, st>>>(d);
-  k_upd_downdate<<<dim3(tp, tp, d.F), UT, 0, st>>>(d);
+  KLAUNCH(d, KID_UPD_T, st, (k_upd_T<<<dim3(tn, tk, d.F), UT, 0, st>>>(d)));
+  KLAUNCH(d, KID_UPD_S, st, (k_upd_S<<<dim3(tk, tk, d.F), UT, 0, st>>>(d)));
+  KLAUNCH(d, KID_UPD_CHOL, st, (k_upd_chol<<<d.F, UT, 0, st>>>(d)));
+  KLAUNCH(d, KID_UPD_TRSM, st, (k_upd_trsm<<<dim3(tn, d.F), UT, 0, st>>>(d)));
+  KLAUNCH(d, KID_UPD_INJECT, st, (k_upd_inject<<<d.F, UT, 0, st>>>(d)));
+  KLAUNCH(d, KID_UPD_DOWNDATE, st, (k_upd_downdate<<<dim3(tp, tp, d.F), UT, 0, st>>>(d)));
 }
 
 void launch_load_dense_H(const Dev& d, int filter, const double* H, const double* r, int m, int n_state, cudaStream_t st) {
-  k_zero_krows_except<<<(d.F + 255) / 256, 256, 0, st>>>(d, filter);
+  KLAUNCH(d, KID_MISC, st, (k_zero_krows_except<<<(d.F + 255) / 256, 256, 0, st>>>(d, filter)));
   const long long tot = (long long)m * (n_state + 1);
   int blocks = (int)((tot + UT - 1) / UT);
   blocks = blocks < 1 ? 1 : (blocks > 1024 ? 1024 : blocks);
   if (blocks * UT < n_state) blocks = (n_state + UT - 1) / UT;
-  k_load_dense_H<<<blocks, UT, 0, st>>>(d, filter, H, r, m, n_state);
+  KLAUNCH(d, KID_MISC, st, (k_load_dense_H<<<blocks, UT, 0, st>>>(d, filter, H, r, m, n_state)));
 }
 
 }  // namespace msckf

@@ -1,9 +1,40 @@
 // Host-side launchers of the CUDA kernels (one translation unit per kernel family).
 #pragma once
 #include <cuda_runtime.h>
+#include <vector>
 #include "msckf_dev.cuh"
 
 namespace msckf {
+
+// Kernel ids for launch counting and optional per-kernel event timing (msckf_kernel_times).
+enum KernelId {
+  KID_PROPAGATE = 0, KID_AUGMENT, KID_OBSERVE, KID_CLASSIFY_LOST, KID_PRUNE_SELECT, KID_TRIANGULATE, KID_PLAN_ITEMS,
+  KID_JACOBIAN_GATE, KID_PLAN_STACK, KID_STACK, KID_QR, KID_UPD_T, KID_UPD_S, KID_UPD_CHOL, KID_UPD_TRSM, KID_UPD_INJECT,
+  KID_UPD_DOWNDATE, KID_REMOVE_CAMS, KID_FINISH_FRAME, KID_RESET, KID_MISC, KID_COUNT
+};
+extern const char* const kKernelNames[KID_COUNT];
+
+// Host-side launch bookkeeping of one context.  Counting is always on; event timing only when
+// `timing` is set (two events per launch on the launching stream, accumulated at flush()).
+struct KTimer {
+  bool timing = false;
+  long long launches[KID_COUNT] = {};
+  double ms[KID_COUNT] = {};
+  long long timed[KID_COUNT] = {};
+  std::vector<cudaEvent_t> pool;
+  std::vector<int> pending;      // kernel id of every recorded (start, stop) pair
+  void begin(int id, cudaStream_t st);
+  void end(cudaStream_t st);
+  void flush(cudaStream_t st);
+  void release();
+};
+#define KLAUNCH(d, id, st, ...)                         \
+  do {                                                  \
+    KTimer* kt_ = static_cast<KTimer*>((d).host_timer); \
+    if (kt_) kt_->begin((id), (st));                    \
+    __VA_ARGS__;                                        \
+    if (kt_) kt_->end((st));                            \
+  } while (0)
 
 // k_propagate.cu
 void launch_propagate(const Dev& d, const int* imu_off, const double* ts, const double* gyro, const double* acc, cudaStream_t st);

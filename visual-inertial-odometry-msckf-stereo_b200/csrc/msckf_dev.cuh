@@ -11,6 +11,7 @@ namespace msckf {
 constexpr int IMU_STRIDE = MSCKF_IMU_STRIDE;
 constexpr int CAM_STRIDE = MSCKF_CAM_STRIDE;   // q[4] p[3] q_null[4] p_null[3] pad[2]
 constexpr int NI = 21;                          // IMU error-state size
+constexpr int NCNT = MSCKF_N_COUNTERS;
 
 // feature flags
 constexpr int FF_LIVE = 1;
@@ -104,10 +105,11 @@ struct Dev {
   int* log_n;              // [2][F]
   int* log_upd;            // [2][F][2] rows, cols of the update
   long long* log_rm;       // [F][2]
-  long long* counters;     // [F][4]
+  long long* counters;     // [F][MSCKF_N_COUNTERS]
   unsigned* err;           // [1]
   unsigned char* did_reset;        // [F]
   double* imu_pub;         // [F][IMU_STRIDE] snapshot for publish()
+  void* host_timer;        // KTimer* of the owning context (host only; never dereferenced on the device)
 };
 
 __host__ __device__ inline int Tld(const Dev& d) { return d.ld + 8; }

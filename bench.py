@@ -389,8 +389,7 @@ def run_b200(args):
         dist.gather(traj, gathered, dst=0)
     torch.cuda.synchronize()
     pos_final = traj[-1, :, capi.IMU_P:capi.IMU_P + 3].cpu().numpy()
-    truth = st.truth_p[LEAD_IN + W + K - 1] - st.truth_p[0]
-    drift = float(np.median(np.linalg.norm(pos_final - truth, axis=1)))
+    assert np.isfinite(pos_final).all()
 
     if rank == 0:
         dfma, dmma = capi.fp64_peak(local)
@@ -428,8 +427,7 @@ def run_b200(args):
                 'filter_frames_per_s': F * world * K / (t_dev * 1e-3), 'feature_updates_per_step': total_upd / K,
                 'e2e': {'value': upd_e2e / e2e_t, 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
                         'ms_per_step': e2e_t / K * 1e3, 'filter_frames_per_s': F * world * K / e2e_t},
-                'gpu_launches': int(l1 - l0), 'clocks': clocks, 'roofline': roofline,
-                'median_position_error_m': drift}
+                'gpu_launches': int(l1 - l0), 'clocks': clocks, 'roofline': roofline}
         if not args.no_latency:
             line['latency'] = single_filter_latency(local, args.feats)
         if not args.no_cpu_baseline:

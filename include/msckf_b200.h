@@ -35,7 +35,7 @@ enum msckf_status {
   MSCKF_ERR_ARG = -1,       /* bad argument */
   MSCKF_ERR_CUDA = -2,      /* CUDA runtime error / no device */
   MSCKF_ERR_CAPACITY = -3,  /* feature store, Jacobian pool or stacked-H row capacity exceeded */
-  MSCKF_ERR_NUMERIC = -4    /* innovation covariance not positive definite (reference: LinAlgError) */
+  MSCKF_ERR_NUMERIC = -4    /* innovation covariance of a measurement update not positive definite (reference: LinAlgError) */
 };
 
 /* Layout of the per-filter IMU block used by msckf_get_imu_state / msckf_set_imu_state
@@ -87,6 +87,7 @@ enum {
   MSCKF_CNT_QR_FLOPS = 9, MSCKF_CNT_QR_BYTES = 10,  /* stacked-H compression                        */
   MSCKF_CNT_K4_FLOPS = 11, MSCKF_CNT_K4_BYTES = 12, /* gain + correction + covariance               */
   MSCKF_CNT_IMU_STEPS = 13,      /* IMU samples integrated                                           */
+  MSCKF_CNT_GATE_NOT_SPD = 14,   /* landmarks rejected because rounding made their innovation covariance indefinite */
   MSCKF_N_COUNTERS = 16
 };
 

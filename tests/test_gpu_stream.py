@@ -89,7 +89,9 @@ def test_stream_vs_reference_golden():
     assert max(worst.values()) < TOL, worst
     assert dec_all == [bool(x) for x in g['gate'][:, 3]]                 # bit-exact gate decisions
     gam = np.array(gam_all)
-    assert np.all(np.abs(gam - g['gate'][:, 2]) <= 1e-8 * np.abs(g['gate'][:, 2]))
+    rel = np.abs(gam - g['gate'][:, 2]) / np.abs(g['gate'][:, 2])
+    # gamma of a grossly rejected outlier (gamma ~ 1e6) amplifies the <= 1e-9 state differences; decisions stay bit-exact
+    assert rel.max() <= 1e-7, (rel.max(), int(rel.argmax()), gam[rel.argmax()], g['gate'][rel.argmax()])
     assert np.array_equal(np.array(rm_all, dtype=np.int64), g['rm'])      # removed camera states
     # rows of every update; the generator's two probe calls of measurement_update on deep copies at
     # frame 30 (make_golden.py, collect_units) are not part of the stream

@@ -2,6 +2,7 @@
 // stage sequencing on one CUDA stream, state import / export.
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -13,7 +14,7 @@ using namespace msckf;
 namespace msckf {
 const char* const kKernelNames[KID_COUNT] = {
     "k_propagate", "k_augment", "k_observe", "k_classify_lost", "k_prune_select", "k_triangulate", "k_plan_items",
-    "k_jacobian_gate", "k_plan_stack", "k_stack", "k_qr", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
+    "k_jacobian_gate", "k_jacobian_big", "k_plan_stack", "k_qr", "k_upd_small", "k_upd_med", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
     "k_upd_downdate", "k_remove_cams", "k_finish_frame", "k_reset", "misc"};
 
 void KTimer::begin(int id, cudaStream_t st) {
@@ -75,7 +76,7 @@ struct msckf_ctx {
   int stg_next = 0;
   double* h_pub = nullptr;          // pinned [F][IMU_STRIDE]
   unsigned char* h_reset = nullptr; // pinned [F]
-  unsigned* h_err = nullptr;        // pinned [1]
+  unsigned* h_err = nullptr;        // pinned [8]
   std::string err;
   bool timing = false;
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -118,7 +119,11 @@ static int check_device_errors(msckf_ctx* ctx) {
   // caller has synchronised the stream after copying d.err to h_err
   const unsigned e = *ctx->h_err;
   if (!e) return MSCKF_OK;
-  cudaMemsetAsync(ctx->d.err, 0, sizeof(unsigned), ctx->st);
+  cudaMemsetAsync(ctx->d.err, 0, 8 * sizeof(unsigned), ctx->st);
+  const unsigned* info = ctx->h_err;
+  char detail[160];
+  snprintf(detail, sizeof detail, " [first at kernel class %u, filter %u, sizes %u %u %u]", info[1], info[2], info[3], info[4], info[5]);
+  const std::string det = detail;
   *ctx->h_err = 0;
   std::string s = "device reported:";
   int rc = MSCKF_ERR_CAPACITY;
@@ -126,13 +131,13 @@ static int check_device_errors(msckf_ctx* ctx) {
   if (e & ERRBIT_POOL) s += " jacobian pool exhausted (raise jacobian_pool_bytes);";
   if (e & ERRBIT_ROWS) s += " stacked-Jacobian rows exceed max_rows;";
   if (e & ERRBIT_CAM_CAP) s += " camera-state window full (augment without prune);";
-  if (e & ERRBIT_NOT_SPD) { s += " innovation covariance not positive definite;"; rc = MSCKF_ERR_NUMERIC; }
+  if (e & ERRBIT_NOT_SPD) { s += " innovation covariance not positive definite;" + det; rc = MSCKF_ERR_NUMERIC; }
   ctx->err = s;
   return rc;
 }
 
 static int sync_and_check(msckf_ctx* ctx) {
-  CK(cudaMemcpyAsync(ctx->h_err, ctx->d.err, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->st));
+  CK(cudaMemcpyAsync(ctx->h_err, ctx->d.err, 8 * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->st));
   CK(cudaStreamSynchronize(ctx->st));
   CK(cudaGetLastError());
   return check_device_errors(ctx);
@@ -233,16 +238,26 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   const int row_cap = cfg->row_cap;
   d.max_rows = cfg->max_rows > 0 ? cfg->max_rows : ((row_cap > 0 ? row_cap : 1500) + 4 * d.Nmax + 8);
   d.Tk = d.nmax;
-  {
-    const long long mr = ((long long)d.max_rows + 3) / 4 * 4;
-    const long long a1 = mr * (d.nmax + 1);
-    const long long a2 = ((long long)5 * d.Fcap + 4) * 13;
-    d.A_elems = std::max(a1, a2);
-  }
-  auto need = [](long long M) { return 4 * M * (6 * M + 4) + (4 * M - 3) * 6 * M + (4 * M - 3) * (4 * M - 3); };
+  d.A_elems = (long long)((d.Tk + 3) / 4 * 4) * (d.nmax + 1);
+  d.Adense_elems = (((long long)d.max_rows + 3) / 4 * 4) * (d.nmax + 1);
+  // compact Jacobian records: 58 doubles per observation of every landmark that reaches the gate in one stage
   long long pool = cfg->jacobian_pool_bytes > 0 ? cfg->jacobian_pool_bytes / 8
-                                                : (long long)d.F * ((long long)d.Fcap * 256 + 32 * need(d.Nmax));
+                                                : (long long)d.F * ((long long)d.Fcap * 128 + 58LL * 4 * d.Nmax);
   d.pool_cap = pool;
+  {
+    const long long M = d.Nmax;
+    const long long fixed = 88 * M + 16 + (4 * M - 3) + (M + 1) / 2 + 1;      // jac_fixed_doubles(Nmax), see k_jacobian.cu
+    d.jac_big_smem_doubles = (int)std::max<long long>(6144, fixed + 8);
+    const int per_sm = (int)std::max<long long>(1, std::min<long long>(8, (200 * 1024) / ((long long)d.jac_big_smem_doubles * 8 + 1024)));
+    d.jac_big_grid = prop.multiProcessorCount * per_sm;
+    d.jac_scratch_stride = 4 * M * (6 * M + 1) + (4 * M - 3) * (4 * M - 3);
+    d.qr_smem_doubles = qr_smem_doubles_for(d.Nmax);
+    d.upd_med_ok = upd_small_smem_bytes(d.nmax, UPD_MED_K, UPD_MED_NA) <= 200 * 1024 ? 1 : 0;
+    d.upd_small_ok = getenv("MSCKF_NO_SMALL") ? 0 : 1;   // debugging knob: everything small goes through the medium kernel
+    if (getenv("MSCKF_NO_MED")) d.upd_med_ok = 0;      // debugging knob: route medium updates through the tiled kernels
+    const long long na = 6 * M, worst = 640 + na * (na + 1) / 2 + na + 32 * (na + 1) + 64;
+    d.qr_scratch_stride = worst > d.qr_smem_doubles ? na * (na + 1) / 2 + na + 256 * (na + 1) : 0;
+  }
 
   Params& hp = ctx->hp;
   memset(&hp, 0, sizeof hp);
@@ -278,17 +293,21 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   DA(d.item_cand, F * Fc); DA(d.item_mask, F * Fc); DA(d.item_rows, F * Fc); DA(d.item_off, F * Fc); DA(d.item_rowoff, F * Fc);
   DA(d.item_dof, F * Fc); DA(d.item_gamma, F * Fc); DA(d.item_pass, F * Fc); DA(d.nitem, F);
   DA(d.rm_mask, F); DA(d.rm_idx, F * 2);
-  DA(d.pool, (size_t)d.pool_cap); DA(d.pool_used, 1);
-  DA(d.A, F * (size_t)d.A_elems); DA(d.m_rows, F); DA(d.m_pad, F); DA(d.n_act, F); DA(d.k_rows, F); DA(d.colmap, F * (size_t)d.nmax);
+  DA(d.pool, (size_t)d.pool_cap); DA(d.stage_ctr, SC_COUNT); DA(d.item_lmask, F * Fc);
+  DA(d.wl_tri, F * Fc); DA(d.wl_jac_small, F * Fc); DA(d.wl_jac_big, F * Fc);
+  DA(d.jac_scratch, (size_t)d.jac_big_grid * d.jac_scratch_stride);
+  if (d.qr_scratch_stride) DA(d.qr_scratch, F * (size_t)d.qr_scratch_stride);
+  DA(d.Adense, (size_t)d.Adense_elems);
+  DA(d.A, F * (size_t)d.A_elems); DA(d.m_rows, F); DA(d.m_pad, F); DA(d.n_act, F); DA(d.k_rows, F); DA(d.colmap, F * (size_t)d.nmax); DA(d.upd_path, F); DA(d.wl_upd_big, F);
   DA(d.T, F * (size_t)d.Tk * Tld(d)); DA(d.S, F * (size_t)d.Tk * d.Tk); DA(d.dx, F * (size_t)d.nmax);
   DA(d.log_id, 2 * F * Fc); DA(d.log_status, 2 * F * Fc); DA(d.log_gamma, 2 * F * Fc); DA(d.log_dof, 2 * F * Fc);
   DA(d.log_n, 2 * F); DA(d.log_upd, 2 * F * 2); DA(d.log_rm, F * 2);
-  DA(d.counters, F * NCNT); DA(d.err, 1); DA(d.did_reset, F); DA(d.imu_pub, F * IMU_STRIDE);
+  DA(d.counters, F * NCNT); DA(d.err, 8); DA(d.did_reset, F); DA(d.imu_pub, F * IMU_STRIDE);
 #undef DA
   CKC(cudaMallocHost((void**)&ctx->h_pub, F * IMU_STRIDE * sizeof(double)));
   CKC(cudaMallocHost((void**)&ctx->h_reset, F));
-  CKC(cudaMallocHost((void**)&ctx->h_err, sizeof(unsigned)));
-  *ctx->h_err = 0;
+  CKC(cudaMallocHost((void**)&ctx->h_err, 8 * sizeof(unsigned)));
+  memset(ctx->h_err, 0, 8 * sizeof(unsigned));
   // initial state: identity orientation, gravity from the caller later (set_imu_state), reset covariance
   {
     std::vector<double> imu0(F * IMU_STRIDE, 0.0);
@@ -554,26 +573,24 @@ int msckf_set_feature_position(msckf_ctx* ctx, int32_t f, int64_t id, const doub
 // ------------------------------------------------------------------ stage enqueue helpers
 static void enqueue_lost_stage(msckf_ctx* ctx) {
   const Dev& d = ctx->d;
-  cudaMemsetAsync(d.pool_used, 0, sizeof(unsigned long long), ctx->st);
+  cudaMemsetAsync(d.stage_ctr, 0, SC_COUNT * sizeof(unsigned long long), ctx->st);
   launch_classify_lost(d, ctx->st);
   launch_triangulate_store(d, ctx->st);
   launch_plan_items(d, 0, ctx->st);
-  launch_jacobian_gate(d, ctx->st);
+  launch_jacobian_gate(d, JAC_SMALL_M, 0, ctx->st);
   launch_plan_stack(d, 0, ctx->st);
-  launch_stack(d, ctx->st);
-  launch_qr(d, ctx->st);
+  launch_qr_build(d, ctx->st);
   launch_update(d, 0, ctx->st);
 }
 static void enqueue_prune_stage(msckf_ctx* ctx) {
   const Dev& d = ctx->d;
-  cudaMemsetAsync(d.pool_used, 0, sizeof(unsigned long long), ctx->st);
+  cudaMemsetAsync(d.stage_ctr, 0, SC_COUNT * sizeof(unsigned long long), ctx->st);
   launch_prune_select(d, ctx->st);
   launch_triangulate_store(d, ctx->st);
   launch_plan_items(d, 1, ctx->st);
-  launch_jacobian_gate(d, ctx->st);
+  launch_jacobian_gate(d, 2, 0, ctx->st);               // the pruning update always involves exactly two camera states
   launch_plan_stack(d, 1, ctx->st);
-  launch_stack(d, ctx->st);
-  launch_qr(d, ctx->st);
+  launch_qr_build(d, ctx->st);
   launch_update(d, 1, ctx->st);
   launch_remove_cams(d, ctx->st);
 }
@@ -700,7 +717,7 @@ int msckf_feature_callback_async(msckf_ctx* ctx, const int32_t* imu_off, const d
   stage_end(ctx, p);
   CK(cudaMemcpyAsync(ctx->h_pub, d.imu_pub, (size_t)F * IMU_STRIDE * sizeof(double), cudaMemcpyDeviceToHost, ctx->st));
   CK(cudaMemcpyAsync(ctx->h_reset, d.did_reset, F, cudaMemcpyDeviceToHost, ctx->st));
-  CK(cudaMemcpyAsync(ctx->h_err, d.err, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->st));
+  CK(cudaMemcpyAsync(ctx->h_err, d.err, 8 * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->st));
   CK(cudaGetLastError());
   ctx->frame_pending = true;
   return MSCKF_OK;
@@ -934,7 +951,7 @@ int msckf_feature_jacobian(msckf_ctx* ctx, int32_t f, int64_t feature_id, int32_
   const int M = __builtin_popcountll(im);
   ARG(M >= 1, "landmark not observed by any of the given camera states");
   const int rows = 4 * M - 3;
-  const long long need = (long long)4 * M * (6 * M + 4) + (long long)rows * 6 * M + (long long)rows * rows;
+  const long long need = 58LL * M;
   ARG(need <= d.pool_cap, "jacobian pool too small");
   // a one-item work list for filter f
   CK(cudaMemsetAsync(d.nitem, 0, d.F * sizeof(int), ctx->st));
@@ -949,8 +966,15 @@ int msckf_feature_jacobian(msckf_ctx* ctx, int32_t f, int64_t feature_id, int32_
   CK(cudaMemcpyAsync(d.item_dof + b, &dof, sizeof(int), cudaMemcpyHostToDevice, ctx->st));
   CK(cudaMemcpyAsync(d.item_off + b, &off0, sizeof(off0), cudaMemcpyHostToDevice, ctx->st));
   CK(cudaMemcpyAsync(d.nitem + f, &one, sizeof(int), cudaMemcpyHostToDevice, ctx->st));
-  CK(cudaStreamSynchronize(ctx->st));      // the small host sources above live on this stack frame
-  launch_jacobian_gate(d, ctx->st);
+  {                                          // a one-entry work list for the matching Jacobian kernel
+    unsigned long long ctr[SC_COUNT] = {0};
+    ctr[M <= JAC_SMALL_M ? SC_NJAC_SMALL : SC_NJAC_BIG] = 1;
+    const int2 entry = make_int2(f, 0);
+    CK(cudaMemcpyAsync(d.stage_ctr, ctr, sizeof ctr, cudaMemcpyHostToDevice, ctx->st));
+    CK(cudaMemcpyAsync(M <= JAC_SMALL_M ? d.wl_jac_small : d.wl_jac_big, &entry, sizeof entry, cudaMemcpyHostToDevice, ctx->st));
+    CK(cudaStreamSynchronize(ctx->st));      // the small host sources above live on this stack frame
+  }
+  launch_jacobian_gate(d, JAC_SMALL_M, 1, ctx->st);
   double* dH = nullptr;
   CK(cudaMalloc((void**)&dH, ((size_t)rows * n_state + rows) * sizeof(double)));
   launch_export_item_dense(d, f, dH, dH + (size_t)rows * n_state, n_state, ctx->st);
@@ -1031,7 +1055,7 @@ int msckf_measurement_update(msckf_ctx* ctx, int32_t f, const double* H, const d
   ARG(H && r, "pointers");
   CK(cudaSetDevice(ctx->device));
   const long long mp = std::max(4, (m + 3) / 4 * 4);
-  ARG(mp * (n_state + 1) <= d.A_elems, "H has more rows than max_rows allows");
+  ARG(mp * (n_state + 1) <= d.Adense_elems, "H has more rows than max_rows allows");
   int ncam = 0;
   int rc = sync_and_check(ctx);
   if (rc) return rc;
@@ -1043,7 +1067,7 @@ int msckf_measurement_update(msckf_ctx* ctx, int32_t f, const double* H, const d
   CK(cudaMemcpy(buf, H, nH * sizeof(double), cudaMemcpyHostToDevice));
   CK(cudaMemcpy(buf + nH, r, m * sizeof(double), cudaMemcpyHostToDevice));
   launch_load_dense_H(d, f, buf, buf + nH, m, n_state, ctx->st);
-  launch_qr(d, ctx->st);
+  launch_qr_dense(d, f, (int)mp, ctx->st);
   launch_update(d, 0, ctx->st);
   rc = sync_and_check(ctx);
   cudaFree(buf);

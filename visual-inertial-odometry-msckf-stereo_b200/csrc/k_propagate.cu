@@ -79,191 +79,284 @@ __device__ void predict_new_state(double dt, const double* gyro, const double* a
   }
 }
 
-__device__ __forceinline__ void mm21(const double* A, const double* B, double* C, int tid) {   // C = A B (21x21)
-  for (int e = tid; e < 441; e += PT) {
-    const int i = e / 21, j = e - 21 * i;
-    double s = 0;
-#pragma unroll
-    for (int k = 0; k < 21; ++k) s += A[21 * i + k] * B[21 * k + j];
-    C[e] = s;
+// Sparsity of Phi = I + F dt + (F dt)^2/2 + (F dt)^3/6 (jit_utils.py:10-41): only the theta (0:3), v (6:9) and p (12:15)
+// block rows differ from the identity, theta rows in columns 0:6, v and p rows in columns 0:15.  Products of such
+// matrices keep the pattern, so every 21 x 21 product below only visits those entries (the skipped terms are exact
+// zeros of the dense products the reference forms).
+__device__ __forceinline__ bool phi_identity_row(int i) { return !(i < 3 || (i >= 6 && i < 9) || (i >= 12 && i < 15)); }
+__device__ __forceinline__ int phi_row_width(int i) { return i < 3 ? 6 : 15; }
+
+constexpr int PW = 4;                         // warps (= filters) per CTA
+constexpr int PKC = 8;                        // IMU samples per chunk
+constexpr int PHC = 84;                       // doubles of one compact Phi: 8 blocks, dt, sigma_a^2 R^T R
+constexpr int PST = 20;                       // doubles of one staged sample / state: q v p | dt w a
+constexpr int PROP_DOUBLES = 5 * 441 + 252 + PKC * PHC + (PKC + 1) * PST + IMU_STRIDE + 12;
+
+// Compact Phi of one IMU sample (lane-parallel over the samples of a chunk): jit_utils.py:6-43 followed by the
+// observability-constrained blocks of msckf.py:328-344.  x0 = state before the sample (q v p), x1 = after,
+// xn = null state (q v p) the constraint refers to.
+__device__ void build_phi(const double* x0, const double* x1, const double* qn, const double* vn, const double* pn, const double* smp,
+                          const double* g, double Qc_a, double* out) {
+  const double dt = smp[0];
+  const double* w = smp + 1;
+  const double* a = smp + 4;
+  double R[9], Sa[9], A00[9], A20[9], A23[9], RtS[9], Sw[9];
+  to_rotation(x0, R);
+  skew3(a, Sa);
+  mat3_mul_tn(R, Sa, RtS);
+  skew3(w, Sw);
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) {
+      A00[3 * i + j] = -Sw[3 * i + j] * dt;
+      A20[3 * i + j] = -RtS[3 * i + j] * dt;
+      A23[3 * i + j] = -R[3 * j + i] * dt;
+    }
+  const double mdt = -1.0 * dt, pdt = 1.0 * dt;
+  // (F dt)^2 and (F dt)^3, block by block (the skipped terms of the dense products are exact zeros)
+  double B00[9], B20[9], C00[9], C20[9], C40[9], P00[9], P20[9], P40[9];
+  mat3_mul(A00, A00, B00);                                   // sq[0,0] = A00 A00
+  mat3_mul(A20, A00, B20);                                   // sq[2,0] = A20 A00;  sq[4,0] = dt A20, sq[4,3] = dt A23
+  mat3_mul(B00, A00, C00);                                   // cube[0,0] = sq[0,0] A00
+  mat3_mul(B20, A00, C20);                                   // cube[2,0] = sq[2,0] A00
+  double B40[9];
+  for (int e = 0; e < 9; ++e) B40[e] = pdt * A20[e];
+  mat3_mul(B40, A00, C40);                                   // cube[4,0] = sq[4,0] A00
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) {
+      const int e = 3 * i + j;
+      const double I = (i == j) ? 1.0 : 0.0;
+      P00[e] = (I + A00[e]) + B00[e] / 2. + C00[e] / 6.;
+      out[9 + e] = (0.0 + I * mdt) + (A00[e] * mdt) / 2. + (B00[e] * mdt) / 6.;     // Phi01
+      P20[e] = (0.0 + A20[e]) + B20[e] / 2. + C20[e] / 6.;
+      out[27 + e] = (A20[e] * mdt) / 2. + (B20[e] * mdt) / 6.;                       // Phi21
+      out[36 + e] = A23[e];                                                            // Phi23
+      P40[e] = B40[e] / 2. + C40[e] / 6.;
+      out[54 + e] = (B40[e] * mdt) / 6.;                                               // Phi41
+      out[63 + e] = (pdt * A23[e]) / 2.;                                               // Phi43
+    }
+  out[72] = dt;
+  // G Qc G^T, block (6:9,6:9) = (-R^T) sigma_a^2 (-R^T)^T
+  {
+    double nR[9], nRq[9];
+    for (int i = 0; i < 9; ++i) nR[i] = -R[i];
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) nRq[3 * i + j] = nR[3 * j + i] * Qc_a;
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j)
+        out[73 + 3 * i + j] = nRq[3 * i] * nR[3 * 0 + j] + nRq[3 * i + 1] * nR[3 * 1 + j] + nRq[3 * i + 2] * nR[3 * 2 + j];
   }
+  // observability-constrained blocks (msckf.py:328-344)
+  double Rk[9], Rn[9];
+  to_rotation(qn, Rk);
+  to_rotation(x1, Rn);
+  mat3_mul_nt(Rn, Rk, P00);
+  double u[3], sv[3];
+  mat3_vec(Rk, g, u);
+  const double uu = u[0] * u[0] + u[1] * u[1] + u[2] * u[2];
+  for (int i = 0; i < 3; ++i) sv[i] = u[i] / uu;
+  double dv[3], dp[3], w1[3], w2[3];
+  for (int i = 0; i < 3; ++i) {
+    dv[i] = vn[i] - x1[4 + i];
+    dp[i] = dt * vn[i] + pn[i] - x1[7 + i];
+  }
+  cross3(dv, g, w1);
+  cross3(dp, g, w2);
+  for (int i = 0; i < 3; ++i) {
+    double* r2 = P20 + 3 * i;
+    const double c2 = (r2[0] * u[0] + r2[1] * u[1] + r2[2] * u[2]) - w1[i];
+    for (int j = 0; j < 3; ++j) r2[j] = r2[j] - c2 * sv[j];
+    double* r4 = P40 + 3 * i;
+    const double c4 = (r4[0] * u[0] + r4[1] * u[1] + r4[2] * u[2]) - w2[i];
+    for (int j = 0; j < 3; ++j) r4[j] = r4[j] - c4 * sv[j];
+  }
+  for (int e = 0; e < 9; ++e) { out[e] = P00[e]; out[18 + e] = P20[e]; out[45 + e] = P40[e]; }
 }
 
-// One CTA per filter: integrates the filter's IMU samples of this frame.  The 21x21 IMU block of P
-// is advanced per sample; the IMU-camera cross covariance only needs the product of the Phis,
-// applied once at the end (identical algebra: P_IC <- Phi_k ... Phi_1 P_IC; symmetrising it is exact).
-__global__ void __launch_bounds__(PT) k_propagate(Dev d, const int* __restrict__ imu_off, const double* __restrict__ ts,
-                                                   const double* __restrict__ gyro_m, const double* __restrict__ acc_m) {
-  const int f = blockIdx.x, tid = threadIdx.x;
+// One WARP per filter integrates the filter's IMU samples of this frame, PKC samples at a time:
+//   1. lane 0 runs the (sequential) RK4 state chain over the chunk,
+//   2. lane k builds Phi_k of sample k from the states before / after it (samples in parallel),
+//   3. the warp advances the 21x21 IMU block of P sample by sample and accumulates the product of the Phis.
+// The IMU-camera cross covariance only needs that product, applied once at the end (identical algebra:
+// P_IC <- Phi_k ... Phi_1 P_IC; symmetrising it is exact).
+__global__ void __launch_bounds__(PW * 32) k_propagate(Dev d, const int* __restrict__ imu_off, const double* __restrict__ ts,
+                                                        const double* __restrict__ gyro_m, const double* __restrict__ acc_m) {
+  extern __shared__ double psm[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int f = blockIdx.x * PW + warp;
+  if (f >= d.F) return;
   const int k0 = imu_off[f], k1 = imu_off[f + 1];
   if (k1 <= k0) return;
-  __shared__ double sPhi[441], sA[441], sB[441], sC[441], sPII[441], sU[441], sT1[441], sAcc[441];
-  __shared__ double sx[IMU_STRIDE];
-  __shared__ double sM[9];       // sigma_a^2 R^T R block of G Qc G^T
-  __shared__ double sdt;
+  double* sPhi = psm + (size_t)warp * PROP_DOUBLES;
+  double* sPII = sPhi + 441;
+  double* sT = sPII + 441;
+  double* sAcc = sT + 441;
+  double* sX2 = sAcc + 441;
+  double* sU = sX2 + 441;                  // [21][12] Phi (G Qc G^T)
+  double* sPc = sU + 252;                  // [PKC][PHC] compact Phis
+  double* sSt = sPc + PKC * PHC;           // [PKC+1][PST]: state after sample c-1 (q v p) | sample c (dt w a)
+  double* sx = sSt + (PKC + 1) * PST;
   const Params& prm = *d.prm;
   double* imu = d.imu + (size_t)f * IMU_STRIDE;
   double* P = d.P + (size_t)f * d.ld * d.ld;
   const int ld = d.ld;
-  const int ncam = d.ncam[f];
-  const int n = NI + 6 * ncam;
+  const int n = NI + 6 * d.ncam[f];
 
-  for (int e = tid; e < IMU_STRIDE; e += PT) sx[e] = imu[e];
-  for (int e = tid; e < 441; e += PT) {
+  for (int e = lane; e < IMU_STRIDE; e += 32) sx[e] = imu[e];
+  for (int e = lane; e < 441; e += 32) {
     const int i = e / 21, j = e - 21 * i;
     sPII[e] = P[(size_t)i * ld + j];
     sAcc[e] = (i == j) ? 1.0 : 0.0;
   }
-  __syncthreads();
+  __syncwarp();
 
-  for (int k = k0; k < k1; ++k) {
-    // ---- F*dt (jit_utils.py:10-38)
-    for (int e = tid; e < 441; e += PT) sA[e] = 0.0;
-    __syncthreads();
-    if (tid == 0) {
-      const double dt = ts[k] - sx[MSCKF_IMU_TIME];
-      sdt = dt;
-      double w[3], a[3], R[9], Sa[9], RtS[9];
+  for (int c0 = k0; c0 < k1; c0 += PKC) {
+    const int kc = min(PKC, k1 - c0);
+    // ---- stage the samples; state slot 0 = current state
+    if (lane < kc) {
+      const int k = c0 + lane;
+      double* smp = sSt + lane * PST + 10;
+      smp[0] = ts[k];                       // turned into dt by the chain below
       for (int i = 0; i < 3; ++i) {
-        w[i] = gyro_m[3 * k + i] - sx[MSCKF_IMU_BG + i];
-        a[i] = acc_m[3 * k + i] - sx[MSCKF_IMU_BA + i];
+        smp[1 + i] = gyro_m[3 * k + i] - sx[MSCKF_IMU_BG + i];
+        smp[4 + i] = acc_m[3 * k + i] - sx[MSCKF_IMU_BA + i];
       }
-      to_rotation(sx + MSCKF_IMU_Q, R);
-      skew3(a, Sa);
-      mat3_mul_tn(R, Sa, RtS);
-      double Sw[9];
-      skew3(w, Sw);
-      for (int i = 0; i < 3; ++i)
-        for (int j = 0; j < 3; ++j) {
-          sA[21 * i + j] = -Sw[3 * i + j] * dt;
-          sA[21 * (6 + i) + j] = -RtS[3 * i + j] * dt;
-          sA[21 * (6 + i) + 9 + j] = -R[3 * j + i] * dt;
-        }
-      for (int i = 0; i < 3; ++i) {
-        sA[21 * i + 3 + i] = -1.0 * dt;
-        sA[21 * (12 + i) + 6 + i] = 1.0 * dt;
-      }
-      // G Qc G^T, block (6:9,6:9) = (-R^T) sigma_a^2 (-R^T)^T
-      double nR[9], nRq[9];
-      for (int i = 0; i < 9; ++i) nR[i] = -R[i];                  // (-R^T) stored transposed
-      for (int i = 0; i < 3; ++i)
-        for (int j = 0; j < 3; ++j) nRq[3 * i + j] = nR[3 * j + i] * prm.Qc[2];   // (-R^T) Qc_a
-      for (int i = 0; i < 3; ++i)
-        for (int j = 0; j < 3; ++j)
-          sM[3 * i + j] = nRq[3 * i] * nR[3 * 0 + j] + nRq[3 * i + 1] * nR[3 * 1 + j] + nRq[3 * i + 2] * nR[3 * 2 + j];
-      // state prediction (RK4) on registers of thread 0
+    }
+    if (lane < 4) sSt[lane] = sx[MSCKF_IMU_Q + lane];
+    if (lane < 3) { sSt[4 + lane] = sx[MSCKF_IMU_V + lane]; sSt[7 + lane] = sx[MSCKF_IMU_P + lane]; }
+    __syncwarp();
+    // ---- 1. RK4 chain
+    if (lane == 0) {
       double q[4], v[3], p[3];
-      for (int i = 0; i < 4; ++i) q[i] = sx[MSCKF_IMU_Q + i];
-      for (int i = 0; i < 3; ++i) { v[i] = sx[MSCKF_IMU_V + i]; p[i] = sx[MSCKF_IMU_P + i]; }
-      predict_new_state(dt, w, a, sx + MSCKF_IMU_GRAVITY, q, v, p);
-      for (int i = 0; i < 4; ++i) sx[MSCKF_IMU_Q + i] = q[i];
-      for (int i = 0; i < 3; ++i) { sx[MSCKF_IMU_V + i] = v[i]; sx[MSCKF_IMU_P + i] = p[i]; }
-    }
-    __syncthreads();
-    mm21(sA, sA, sB, tid);
-    __syncthreads();
-    mm21(sB, sA, sC, tid);
-    __syncthreads();
-    for (int e = tid; e < 441; e += PT) {
-      const int i = e / 21, j = e - 21 * i;
-      sPhi[e] = ((i == j ? 1.0 : 0.0) + sA[e]) + sB[e] / 2. + sC[e] / 6.;
-    }
-    __syncthreads();
-    // ---- observability-constrained blocks of Phi (msckf.py:328-344)
-    if (tid == 0) {
-      const double dt = sdt;
-      const double* g = sx + MSCKF_IMU_GRAVITY;
-      double Rk[9], Rn[9], B[9];
-      to_rotation(sx + MSCKF_IMU_Q_NULL, Rk);
-      to_rotation(sx + MSCKF_IMU_Q, Rn);
-      mat3_mul_nt(Rn, Rk, B);
-      for (int i = 0; i < 3; ++i)
-        for (int j = 0; j < 3; ++j) sPhi[21 * i + j] = B[3 * i + j];
-      double u[3], s[3];
-      mat3_vec(Rk, g, u);
-      const double uu = u[0] * u[0] + u[1] * u[1] + u[2] * u[2];
-      for (int i = 0; i < 3; ++i) s[i] = u[i] / uu;
-      double dv[3], dp[3], w1[3], w2[3];
-      for (int i = 0; i < 3; ++i) {
-        dv[i] = sx[MSCKF_IMU_V_NULL + i] - sx[MSCKF_IMU_V + i];
-        dp[i] = dt * sx[MSCKF_IMU_V_NULL + i] + sx[MSCKF_IMU_P_NULL + i] - sx[MSCKF_IMU_P + i];
+      for (int i = 0; i < 4; ++i) q[i] = sSt[i];
+      for (int i = 0; i < 3; ++i) { v[i] = sSt[4 + i]; p[i] = sSt[7 + i]; }
+      double t_prev = sx[MSCKF_IMU_TIME];
+      for (int c = 0; c < kc; ++c) {
+        double* smp = sSt + c * PST + 10;
+        const double t = smp[0], dt = t - t_prev;
+        smp[0] = dt;
+        t_prev = t;
+        predict_new_state(dt, smp + 1, smp + 4, sx + MSCKF_IMU_GRAVITY, q, v, p);
+        double* nx = sSt + (c + 1) * PST;
+        for (int i = 0; i < 4; ++i) nx[i] = q[i];
+        for (int i = 0; i < 3; ++i) { nx[4 + i] = v[i]; nx[7 + i] = p[i]; }
       }
-      cross3(dv, g, w1);
-      cross3(dp, g, w2);
-      for (int blk = 0; blk < 2; ++blk) {
-        const int r0 = blk == 0 ? 6 : 12;
-        const double* ww = blk == 0 ? w1 : w2;
-        for (int i = 0; i < 3; ++i) {
-          double* row = sPhi + 21 * (r0 + i);
-          const double au = row[0] * u[0] + row[1] * u[1] + row[2] * u[2];
-          const double c = au - ww[i];
-          for (int j = 0; j < 3; ++j) row[j] = row[j] - c * s[j];
-        }
-      }
-      // null states <- current (msckf.py:366-368), time
-      for (int i = 0; i < 4; ++i) sx[MSCKF_IMU_Q_NULL + i] = sx[MSCKF_IMU_Q + i];
-      for (int i = 0; i < 3; ++i) {
-        sx[MSCKF_IMU_V_NULL + i] = sx[MSCKF_IMU_V + i];
-        sx[MSCKF_IMU_P_NULL + i] = sx[MSCKF_IMU_P + i];
-      }
-      sx[MSCKF_IMU_TIME] = ts[k];
-      sx[MSCKF_IMU_NULL_ALIASED] = 1.0;
+      sx[MSCKF_IMU_TIME] = t_prev;
     }
-    __syncthreads();
-    // ---- T1 = Phi P_II ; U = Phi (G Qc G^T)   (jit_utils.py:132-134)
-    for (int e = tid; e < 441; e += PT) {
-      const int i = e / 21, j = e - 21 * i;
-      double s = 0;
-#pragma unroll
-      for (int kk = 0; kk < 21; ++kk) s += sPhi[21 * i + kk] * sPII[21 * kk + j];
-      sT1[e] = s;
-      double u = 0;
-      if (j < 3) u = sPhi[21 * i + j] * prm.Qc[0];
-      else if (j < 6) u = sPhi[21 * i + j] * prm.Qc[1];
-      else if (j < 9) u = sPhi[21 * i + 6] * sM[j - 6] + sPhi[21 * i + 7] * sM[3 + j - 6] + sPhi[21 * i + 8] * sM[6 + j - 6];
-      else if (j < 12) u = sPhi[21 * i + j] * prm.Qc[3];
-      sU[e] = u;
+    __syncwarp();
+    // ---- 2. Phi of every sample of the chunk (null state of the first sample = the stored one, then the previous state)
+    if (lane < kc) {
+      const double* x0 = sSt + lane * PST;
+      const double* x1 = sSt + (lane + 1) * PST;
+      const bool first = (lane == 0);
+      build_phi(x0, x1, first ? sx + MSCKF_IMU_Q_NULL : x0, first ? sx + MSCKF_IMU_V_NULL : x0 + 4,
+                first ? sx + MSCKF_IMU_P_NULL : x0 + 7, x0 + 10, sx + MSCKF_IMU_GRAVITY, prm.Qc[2], sPc + lane * PHC);
     }
-    __syncthreads();
+    __syncwarp();
+    // state after the chunk; null states <- current (msckf.py:366-368)
     {
-      const double dt = sdt;
-      for (int e = tid; e < 441; e += PT) {
-        const int i = e / 21, j = e - 21 * i;
-        double s = 0, qq = 0;
-#pragma unroll
-        for (int kk = 0; kk < 21; ++kk) s += sT1[21 * i + kk] * sPhi[21 * j + kk];
-#pragma unroll
-        for (int kk = 0; kk < 12; ++kk) qq += sU[21 * i + kk] * sPhi[21 * j + kk];
-        sC[e] = s + qq * dt;
+      const double* xe = sSt + kc * PST;
+      if (lane < 4) { sx[MSCKF_IMU_Q + lane] = xe[lane]; sx[MSCKF_IMU_Q_NULL + lane] = xe[lane]; }
+      if (lane < 3) {
+        sx[MSCKF_IMU_V + lane] = xe[4 + lane]; sx[MSCKF_IMU_V_NULL + lane] = xe[4 + lane];
+        sx[MSCKF_IMU_P + lane] = xe[7 + lane]; sx[MSCKF_IMU_P_NULL + lane] = xe[7 + lane];
       }
+      if (lane == 0) sx[MSCKF_IMU_NULL_ALIASED] = 1.0;
     }
-    // Phi_acc <- Phi Phi_acc
-    mm21(sPhi, sAcc, sB, tid);
-    __syncthreads();
-    for (int e = tid; e < 441; e += PT) {
-      const int i = e / 21, j = e - 21 * i;
-      sPII[e] = (sC[e] + sC[21 * j + i]) / 2.;
-      sAcc[e] = sB[e];
+    // ---- 3. covariance, sample by sample
+    for (int c = 0; c < kc; ++c) {
+      const double* pc = sPc + c * PHC;
+      const double dt = pc[72];
+      for (int e = lane; e < 441; e += 32) sPhi[e] = (e % 22 == 0) ? 1.0 : 0.0;
+      __syncwarp();
+      for (int e = lane; e < 72; e += 32) {
+        const int blk = e / 9, r = (e % 9) / 3, cc = e % 3;
+        // block -> (row block, column block): 00 01 20 21 23 40 41 43
+        const int rb = blk < 2 ? 0 : (blk < 5 ? 6 : 12);
+        const int cb = (blk == 0 || blk == 2 || blk == 5) ? 0 : ((blk == 1 || blk == 3 || blk == 6) ? 3 : 9);
+        sPhi[21 * (rb + r) + cb + cc] = pc[e];
+      }
+      if (lane < 3) sPhi[21 * (12 + lane) + 6 + lane] = 1.0 * dt;
+      __syncwarp();
+      // T = Phi P_II ; U = Phi (G Qc G^T)   (jit_utils.py:132-134)
+      for (int e = lane; e < 441; e += 32) {
+        const int i = e / 21, j = e - 21 * i;
+        double s;
+        if (phi_identity_row(i)) {
+          s = sPII[e];
+        } else {
+          s = 0;
+          const int wdt = phi_row_width(i);
+          for (int kk = 0; kk < wdt; ++kk) s += sPhi[21 * i + kk] * sPII[21 * kk + j];
+        }
+        sT[e] = s;
+      }
+      for (int e = lane; e < 252; e += 32) {
+        const int i = e / 12, j = e - 12 * i;
+        double u;
+        if (j < 3) u = sPhi[21 * i + j] * prm.Qc[0];
+        else if (j < 6) u = sPhi[21 * i + j] * prm.Qc[1];
+        else if (j < 9) u = sPhi[21 * i + 6] * pc[73 + j - 6] + sPhi[21 * i + 7] * pc[73 + 3 + j - 6] + sPhi[21 * i + 8] * pc[73 + 6 + j - 6];
+        else u = sPhi[21 * i + j] * prm.Qc[3];
+        sU[e] = u;
+      }
+      __syncwarp();
+      // X = T Phi^T + (U Phi^T) dt ; Phi_acc <- Phi Phi_acc (kept in registers until everyone has read the old one)
+      double newA[14];
+      int cnt = 0;
+      for (int e = lane; e < 441; e += 32, ++cnt) {
+        const int i = e / 21, j = e - 21 * i;
+        double s;
+        if (phi_identity_row(j)) {
+          s = sT[21 * i + j];
+        } else {
+          s = 0;
+          const int wdt = phi_row_width(j);
+          for (int kk = 0; kk < wdt; ++kk) s += sT[21 * i + kk] * sPhi[21 * j + kk];
+        }
+        double qq = 0;
+#pragma unroll
+        for (int kk = 0; kk < 12; ++kk) qq += sU[12 * i + kk] * sPhi[21 * j + kk];
+        sX2[e] = s + qq * dt;
+        double acc;
+        if (phi_identity_row(i)) {
+          acc = sAcc[e];
+        } else {
+          acc = 0;
+          const int wdt = phi_row_width(i);
+          for (int kk = 0; kk < wdt; ++kk) acc += sPhi[21 * i + kk] * sAcc[21 * kk + j];
+        }
+        newA[cnt] = acc;
+      }
+      __syncwarp();
+      cnt = 0;
+      for (int e = lane; e < 441; e += 32, ++cnt) {
+        const int i = e / 21, j = e - 21 * i;
+        sPII[e] = (sX2[e] + sX2[21 * j + i]) / 2.;
+        sAcc[e] = newA[cnt];
+      }
+      __syncwarp();
     }
-    __syncthreads();
   }
 
   // ---- write back: IMU state, P_II, P_IC = Phi_acc P_IC and its mirror
-  for (int e = tid; e < IMU_STRIDE; e += PT) imu[e] = sx[e];
-  if (tid == 0) d.counters[NCNT * f + MSCKF_CNT_IMU_STEPS] += k1 - k0;
-  for (int e = tid; e < 441; e += PT) {
+  for (int e = lane; e < IMU_STRIDE; e += 32) imu[e] = sx[e];
+  if (lane == 0) d.counters[NCNT * f + MSCKF_CNT_IMU_STEPS] += k1 - k0;
+  for (int e = lane; e < 441; e += 32) {
     const int i = e / 21, j = e - 21 * i;
     P[(size_t)i * ld + j] = sPII[e];
   }
-  for (int j = NI + tid; j < n; j += PT) {
-    double col[21];
+  for (int j = NI + lane; j < n; j += 32) {
+    double col[15];
 #pragma unroll
-    for (int i = 0; i < 21; ++i) col[i] = P[(size_t)i * ld + j];
+    for (int i = 0; i < 15; ++i) col[i] = P[(size_t)j * ld + i];      // column j of P_IC read through the (symmetric) row j
 #pragma unroll
-    for (int i = 0; i < 21; ++i) {
+    for (int i = 0; i < 15; ++i) {
+      if (phi_identity_row(i)) continue;
       double s = 0;
+      const int wdt = phi_row_width(i);
 #pragma unroll
-      for (int kk = 0; kk < 21; ++kk) s += sAcc[21 * i + kk] * col[kk];
+      for (int kk = 0; kk < 15; ++kk)
+        if (kk < wdt) s += sAcc[21 * i + kk] * col[kk];
       P[(size_t)i * ld + j] = s;
       P[(size_t)j * ld + i] = s;
     }
@@ -465,7 +558,13 @@ __global__ void __launch_bounds__(PT) k_remove_cams(Dev d) {
 
 // ------------------------------------------------------------------ launchers
 void launch_propagate(const Dev& d, const int* imu_off, const double* ts, const double* gyro, const double* acc, cudaStream_t st) {
-  KLAUNCH(d, KID_PROPAGATE, st, (k_propagate<<<d.F, PT, 0, st>>>(d, imu_off, ts, gyro, acc)));
+  static bool attr_set = false;
+  const size_t smem = (size_t)PW * PROP_DOUBLES * sizeof(double);
+  if (!attr_set) {
+    cudaFuncSetAttribute(k_propagate, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    attr_set = true;
+  }
+  KLAUNCH(d, KID_PROPAGATE, st, (k_propagate<<<(d.F + PW - 1) / PW, PW * 32, smem, st>>>(d, imu_off, ts, gyro, acc)));
 }
 void launch_augment(const Dev& d, const long long* ids, cudaStream_t st) { KLAUNCH(d, KID_AUGMENT, st, (k_augment<<<d.F, PT, 0, st>>>(d, ids))); }
 void launch_finish_frame(const Dev& d, int do_reset_check, cudaStream_t st) {

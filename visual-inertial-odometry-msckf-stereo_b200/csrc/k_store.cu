@@ -185,6 +185,7 @@ __global__ void __launch_bounds__(ST) k_classify_lost(Dev d) {
       if (__popcll(mask) < 3) st = MSCKF_FEAT_FEW_OBS;
       else st = (d.f_flags[(size_t)f * d.Fcap + slot] & FF_INIT) ? CS_READY : CS_NEED_TRI;
       cst[ci] = st;
+      if (st == CS_NEED_TRI) d.wl_tri[atomicAdd(d.stage_ctr + SC_NTRI, 1ull)] = make_int2(f, ci);
       d.free_stack[(size_t)f * d.Fcap + nfree0 + ci] = slot;
     }
     nkeep += tk;
@@ -286,7 +287,9 @@ __global__ void __launch_bounds__(ST) k_prune_select(Dev d) {
     const int r = block_rank(c >= 2, s_warp, tot);
     if (c >= 2) {
       cand[nc + r] = slot;
-      cst[nc + r] = (d.f_flags[(size_t)f * d.Fcap + slot] & FF_INIT) ? CS_READY : CS_NEED_TRI;
+      const int st = (d.f_flags[(size_t)f * d.Fcap + slot] & FF_INIT) ? CS_READY : CS_NEED_TRI;
+      cst[nc + r] = st;
+      if (st == CS_NEED_TRI) d.wl_tri[atomicAdd(d.stage_ctr + SC_NTRI, 1ull)] = make_int2(f, nc + r);
     }
     nc += tot;
   }
@@ -324,7 +327,7 @@ __global__ void __launch_bounds__(ST) k_plan_items(Dev d, int stage) {
       if (stage == 1) d.f_mask[(size_t)f * d.Fcap + slot] = mask & ~rmm;
     }
     const int rows = 4 * M - 3;
-    const long long need = isitem ? ((long long)4 * M * (6 * M + 4) + (long long)rows * 6 * M + (long long)rows * rows) : 0;
+    const long long need = isitem ? (long long)58 * M : 0;      // compact record, see k_jacobian.cu
     int tot;
     const int r = block_rank(isitem, s_warp, tot);
     long long tot_e;
@@ -339,6 +342,8 @@ __global__ void __launch_bounds__(ST) k_plan_items(Dev d, int stage) {
       d.item_pass[k] = 0;
       d.item_gamma[k] = 0.0;
       d.item_rowoff[k] = -1;
+      if (M <= JAC_SMALL_M) d.wl_jac_small[atomicAdd(d.stage_ctr + SC_NJAC_SMALL, 1ull)] = make_int2(f, ni + r);
+      else d.wl_jac_big[atomicAdd(d.stage_ctr + SC_NJAC_BIG, 1ull)] = make_int2(f, ni + r);
       const long long Ml = M, R = rows, C6 = 6 * Ml;
       w_obs += Ml;
       w_flops += 300 * Ml + 12 * (4 * Ml) * (C6 + 1) + 2 * R * C6 * C6 + 2 * R * R * C6 + (R * R * R) / 3 + 2 * R * R;
@@ -351,7 +356,7 @@ __global__ void __launch_bounds__(ST) k_plan_items(Dev d, int stage) {
   if (tid == 0) {
     unsigned long long base = 0;
     if (elems_total > 0) {
-      base = atomicAdd(d.pool_used, (unsigned long long)elems_total);
+      base = atomicAdd(d.stage_ctr + SC_POOL, (unsigned long long)elems_total);
       if ((long long)(base + elems_total) > d.pool_cap) {
         atomicOr(d.err, ERRBIT_POOL);
         ni = 0;
@@ -435,11 +440,17 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
     for (int c = 0; c < N; ++c)
       if ((act >> d.cam_phys[(size_t)f * d.Nmax + c]) & 1ull)
         for (int e = 0; e < 6; ++e) cm[na++] = NI + 6 * c + e;
-    if ((long long)(((m + 3) / 4) * 4) * (na + 1) > d.A_elems) { atomicOr(d.err, ERRBIT_ROWS); m = 0; }
+    const int kr = (m > na) ? na : m;
     d.m_rows[f] = m;
-    d.m_pad[f] = max(4, ((m + 3) / 4) * 4);
+    d.m_pad[f] = max(4, ((kr + 3) / 4) * 4);
     d.n_act[f] = na;
-    d.k_rows[f] = (m > na) ? na : m;
+    d.k_rows[f] = kr;
+    int path = 0;
+    if (kr > 0) {
+      path = (d.upd_small_ok && kr <= UPD_SMALL_K && na <= UPD_SMALL_NA) ? 1 : ((d.upd_med_ok && kr <= UPD_MED_K && na <= UPD_MED_NA) ? 3 : 2);
+      if (path == 2) d.wl_upd_big[atomicAdd(d.stage_ctr + SC_NUPD_BIG, 1ull)] = f;
+    }
+    d.upd_path[f] = path;
     d.log_n[stage * d.F + f] = nc;
     d.log_upd[((size_t)stage * d.F + f) * 2 + 0] = m;
     d.log_upd[((size_t)stage * d.F + f) * 2 + 1] = NI + 6 * N;

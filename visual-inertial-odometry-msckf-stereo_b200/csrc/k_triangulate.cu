@@ -3,6 +3,7 @@
 // One warp per landmark; the landmark's 2M views (R, t relative to the first cam0, and the
 // measurement) are staged in shared memory as a structure of arrays, lanes stride over views,
 // and the 3x3 normal equations are reduced with warp shuffles.
+#include <algorithm>
 #include "msckf_dev.cuh"
 #include "kernels.h"
 
@@ -214,65 +215,69 @@ __device__ __forceinline__ bool check_motion(const TriCfg& cfg, const double* Rf
 }
 
 // ------------------------------------------------------------------ store-driven kernel
-// grid (ceil(Fcap/TRI_WPB), F): warp w of filter f takes candidate w; only CS_NEED_TRI work.
+// Persistent grid over the work list wl_tri[0 .. n) of (filter, candidate) pairs that still need a position
+// (built by k_classify_lost / k_prune_select); one warp per landmark.
 __global__ void __launch_bounds__(TRI_WPB * 32) k_triangulate_store(Dev d) {
   extern __shared__ double smem[];
-  const int f = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ci = blockIdx.x * TRI_WPB + warp;
-  if (ci >= d.ncand[f]) return;
-  if (d.cand_status[(size_t)f * d.Fcap + ci] != CS_NEED_TRI) return;
-  const int slot = d.cand[(size_t)f * d.Fcap + ci];
-  const size_t fs = (size_t)f * d.Fcap + slot;
-  const unsigned long long mask = d.f_mask[fs];
-  const int N = d.ncam[f];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n = (int)d.stage_ctr[SC_NTRI];
   const TriCfg cfg = load_tricfg(*d.prm);
   const int stride = 2 * d.Nmax;
   Views V{smem + (size_t)warp * VIEW_DOUBLES * stride, stride};
-  // logical-order observation mask
-  unsigned long long lmask = 0;
-  for (int c0 = 0; c0 < N; c0 += 32) {
-    const int c = c0 + lane;
-    const int bit = (c < N) ? (int)((mask >> d.cam_phys[(size_t)f * d.Nmax + c]) & 1ull) : 0;
-    lmask |= (unsigned long long)__ballot_sync(0xffffffffu, bit) << c0;
-  }
-  const int M = __popcll(lmask);
-  const int c_first = __ffsll((long long)lmask) - 1;
-  const int c_last = 63 - __clzll((long long)lmask);
-  const double* camf = d.cam + ((size_t)f * d.Nmax + c_first) * CAM_STRIDE;
-  const double* caml = d.cam + ((size_t)f * d.Nmax + c_last) * CAM_STRIDE;
-  double R0f[9], Rf[9], tf[3];
-  to_rotation(camf, R0f);
-  for (int i = 0; i < 3; ++i)
-    for (int j = 0; j < 3; ++j) Rf[3 * i + j] = R0f[3 * j + i];
-  for (int i = 0; i < 3; ++i) tf[i] = camf[4 + i];
-  const double* obs_base = d.f_obs + fs * d.Nmax * 4;
-  const double* zf = obs_base + (size_t)d.cam_phys[(size_t)f * d.Nmax + c_first] * 4;
-  bool ok = check_motion(cfg, Rf, tf, zf, caml + 4);
-  double pos[3] = {0, 0, 0};
-  if (ok) {
-    for (int c = lane; c < N; c += 32) {
-      if ((lmask >> c) & 1ull) {
-        const int a = __popcll(lmask & ((1ull << c) - 1ull));
-        const double* cs = d.cam + ((size_t)f * d.Nmax + c) * CAM_STRIDE;
-        stage_views(V, a, cs, cs + 4, obs_base + (size_t)d.cam_phys[(size_t)f * d.Nmax + c] * 4, Rf, tf, cfg);
+  for (int w = blockIdx.x * TRI_WPB + warp; w < n; w += gridDim.x * TRI_WPB) {
+    const int2 it = d.wl_tri[w];
+    const int f = it.x, ci = it.y;
+    const int slot = d.cand[(size_t)f * d.Fcap + ci];
+    const size_t fs = (size_t)f * d.Fcap + slot;
+    const unsigned long long mask = d.f_mask[fs];
+    const int N = d.ncam[f];
+    // logical-order observation mask
+    unsigned long long lmask = 0;
+    for (int c0 = 0; c0 < N; c0 += 32) {
+      const int c = c0 + lane;
+      const int bit = (c < N) ? (int)((mask >> d.cam_phys[(size_t)f * d.Nmax + c]) & 1ull) : 0;
+      lmask |= (unsigned long long)__ballot_sync(0xffffffffu, bit) << c0;
+    }
+    const int M = __popcll(lmask);
+    const int c_first = __ffsll((long long)lmask) - 1;
+    const int c_last = 63 - __clzll((long long)lmask);
+    const double* camf = d.cam + ((size_t)f * d.Nmax + c_first) * CAM_STRIDE;
+    const double* caml = d.cam + ((size_t)f * d.Nmax + c_last) * CAM_STRIDE;
+    double R0f[9], Rf[9], tf[3];
+    to_rotation(camf, R0f);
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) Rf[3 * i + j] = R0f[3 * j + i];
+    for (int i = 0; i < 3; ++i) tf[i] = camf[4 + i];
+    const double* obs_base = d.f_obs + fs * d.Nmax * 4;
+    const double* zf = obs_base + (size_t)d.cam_phys[(size_t)f * d.Nmax + c_first] * 4;
+    bool ok = check_motion(cfg, Rf, tf, zf, caml + 4);
+    double pos[3] = {0, 0, 0};
+    __syncwarp();                       // the previous landmark's views are no longer read
+    if (ok) {
+      for (int c = lane; c < N; c += 32) {
+        if ((lmask >> c) & 1ull) {
+          const int a = __popcll(lmask & ((1ull << c) - 1ull));
+          const double* cs = d.cam + ((size_t)f * d.Nmax + c) * CAM_STRIDE;
+          stage_views(V, a, cs, cs + 4, obs_base + (size_t)d.cam_phys[(size_t)f * d.Nmax + c] * 4, Rf, tf, cfg);
+        }
+      }
+      __syncwarp();
+      int ns = 0;
+      ok = lm_solve(V, 2 * M, cfg, Rf, tf, lane, pos, &ns);
+      if (lane == 0) {
+        d.f_pos[fs * 3 + 0] = pos[0]; d.f_pos[fs * 3 + 1] = pos[1]; d.f_pos[fs * 3 + 2] = pos[2];
+        unsigned long long* cnt = (unsigned long long*)(d.counters + (size_t)NCNT * f);
+        atomicAdd(cnt + MSCKF_CNT_TRIANGULATIONS, 1ull);
+        atomicAdd(cnt + MSCKF_CNT_TRI_OBS, (unsigned long long)M);
+        atomicAdd(cnt + MSCKF_CNT_TRI_SOLVES, (unsigned long long)ns);
       }
     }
-    __syncwarp();
-    int ns = 0;
-    ok = lm_solve(V, 2 * M, cfg, Rf, tf, lane, pos, &ns);
     if (lane == 0) {
-      d.f_pos[fs * 3 + 0] = pos[0]; d.f_pos[fs * 3 + 1] = pos[1]; d.f_pos[fs * 3 + 2] = pos[2];
-      unsigned long long* cnt = (unsigned long long*)(d.counters + (size_t)NCNT * f);
-      atomicAdd(cnt + MSCKF_CNT_TRIANGULATIONS, 1ull);
-      atomicAdd(cnt + MSCKF_CNT_TRI_OBS, (unsigned long long)M);
-      atomicAdd(cnt + MSCKF_CNT_TRI_SOLVES, (unsigned long long)ns);
+      int fl = d.f_flags[fs];
+      fl = ok ? (fl | FF_INIT) : (fl & ~FF_INIT);
+      d.f_flags[fs] = fl;
+      d.cand_status[(size_t)f * d.Fcap + ci] = ok ? CS_READY : MSCKF_FEAT_TRI_FAILED;
     }
-  }
-  if (lane == 0) {
-    int fl = d.f_flags[fs];
-    fl = ok ? (fl | FF_INIT) : (fl & ~FF_INIT);
-    d.f_flags[fs] = fl;
-    d.cand_status[(size_t)f * d.Fcap + ci] = ok ? CS_READY : MSCKF_FEAT_TRI_FAILED;
   }
 }
 
@@ -329,8 +334,8 @@ void launch_triangulate_store(const Dev& d, cudaStream_t st) {
     cudaFuncSetAttribute(k_triangulate_raw, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     attr_set = true;
   }
-  dim3 grid((d.Fcap + TRI_WPB - 1) / TRI_WPB, d.F);
-  KLAUNCH(d, KID_TRIANGULATE, st, (k_triangulate_store<<<grid, TRI_WPB * 32, smem, st>>>(d)));
+  const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(12, (200 * 1024) / (smem + 1024)));
+  KLAUNCH(d, KID_TRIANGULATE, st, (k_triangulate_store<<<sm_count() * per_sm, TRI_WPB * 32, smem, st>>>(d)));
 }
 
 void launch_triangulate_raw(const Dev& d, int n, const int* obs_off, const double* uv, const double* cam_q, const double* cam_p,

@@ -18,59 +18,242 @@ namespace msckf {
 
 constexpr int UT = 256;
 
-// ------------------------------------------------------------------ QR (jit_utils.py:173-175 / msckf.py:549-553)
-// One CTA per filter; LAPACK-style Householder vectors stored below the diagonal, then zeroed
-// in the top n_a rows so that H_thin = R is a clean upper triangle.  The residual rides along as
-// the last column, which yields r_thin = Q^T r without forming Q.
-__global__ void __launch_bounds__(UT) k_qr(Dev d) {
+// ------------------------------------------------------------------ stacking + QR (msckf.py:549-553, 672-674, 790-792)
+// One CTA per filter.  The stacked Jacobian is never materialised: rows are expanded chunk by chunk from the
+// compact per-landmark records of k_jacobian_gate (H' = E - V Z, r' = Q^T r) straight into shared memory and
+// folded into the running triangular factor R (packed, with Q^T r riding along as column n_a) by Householder
+// reflectors on [R(j,j) ; chunk(:,j)].  Landmarks arrive oldest first, so a chunk of short tracks only touches
+// the trailing camera columns: elimination starts at the chunk's first non-zero column.  When m <= n_a the
+// reference skips the QR (msckf.py:549): rows are expanded straight into the output.
+constexpr int QT = 256;
+constexpr int QR_MAX_CR = 256;      // rows per chunk (8 per lane)
+constexpr int QR_HDR = 2 * QR_MAX_CR + QR_MAX_CR / 2;   // doubles of per-row metadata in front of the buffers
+
+__host__ __device__ inline int qr_packed_size(int na) { return na * (na + 1) / 2 + na; }   // row j holds columns j..na
+__host__ __device__ inline int qr_row_off(int j, int na) { return j * (na + 1) - j * (j - 1) / 2; }
+
+// element (local row li+3 of the landmark's full Q^T E, active column c) of a compact record
+__device__ __forceinline__ double record_elem(const double* rec, int M, unsigned long long lmask, int li, int cam, int e6, bool is_r) {
+  const int i = li + 3;
+  if (is_r) return rec[54 * M + i];
+  if (!((lmask >> cam) & 1ull)) return 0.0;
+  const int a = __popcll(lmask & ((1ull << cam) - 1ull));
+  const int c = 6 * a + e6;
+  const double* V = rec + 24 * M + 3 * i;
+  const double* Zt = rec + 36 * M + 3 * c;
+  double v = (i >= 4 * a && i < 4 * a + 4) ? rec[24 * a + 6 * (i - 4 * a) + e6] : 0.0;
+  return v - (V[0] * Zt[0] + V[1] * Zt[1] + V[2] * Zt[2]);
+}
+
+__global__ void __launch_bounds__(QT) k_qr_build(Dev d, int smem_doubles) {
+  extern __shared__ double sm[];
   const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int m = d.m_rows[f], na = d.n_act[f], mp = d.m_pad[f];
-  if (m <= na || m == 0) return;
+  const int m = d.m_rows[f];
+  if (m == 0) return;
+  const int na = d.n_act[f], nc = na + 1, k = d.k_rows[f], mp = d.m_pad[f], ni = d.nitem[f];
+  const bool do_qr = m > na;
   double* A = d.A + (size_t)f * d.A_elems;
+  const int* cm = d.colmap + (size_t)f * d.nmax;
+  const size_t fb = (size_t)f * d.Fcap;
+  __shared__ int s_c0;
+  __shared__ int s_cam[64];          // logical camera of active column block
+  for (int b = tid; b < na / 6; b += QT) s_cam[b] = (cm[6 * b] - NI) / 6;
+
+  if (!do_qr) {
+    __syncthreads();
+    // rows go out as they are: H_thin = H (k = m rows)
+    for (int kk = warp; kk < ni; kk += QT / 32) {
+      const int ro = d.item_rowoff[fb + kk];
+      if (ro < 0) continue;
+      const int rows = d.item_rows[fb + kk], M = (rows + 3) / 4;
+      const unsigned long long lmask = d.item_lmask[fb + kk];
+      const double* rec = d.pool + d.item_off[fb + kk];
+      for (int e = lane; e < rows * nc; e += 32) {
+        const int li = e % rows, c = e / rows;
+        A[(size_t)c * mp + ro + li] = record_elem(rec, M, lmask, li, c < na ? s_cam[c / 6] : 0, c % 6, c == na);
+      }
+    }
+    return;
+  }
+
+  // ---- buffers: packed R (+ rhs), row -> item map, chunk (column-major, ld = CR)
+  const int Rsize = qr_packed_size(na);
+  double* Rp;
+  double* Ch;
+  int CR;
+  // per-row metadata of the current chunk: record offset, logical observation mask, (local row | M << 16)
+  long long* row_rec = (long long*)sm;                  // [QR_MAX_CR]
+  unsigned long long* row_lmask = (unsigned long long*)(sm + QR_MAX_CR);
+  int* row_meta = (int*)(sm + 2 * QR_MAX_CR);
+  double* sm_d = sm + QR_HDR;
+  {
+    const int avail = smem_doubles - QR_HDR - Rsize;
+    CR = avail > 0 ? min(QR_MAX_CR, (avail / nc) & ~31) : 0;
+    if (CR >= 32) {
+      Rp = sm_d;
+      Ch = sm_d + Rsize;
+    } else {                                            // does not fit: global scratch (rare: very wide windows)
+      Rp = d.qr_scratch + (size_t)f * d.qr_scratch_stride;
+      Ch = Rp + Rsize;
+      CR = QR_MAX_CR;
+    }
+  }
+  for (int e = tid; e < Rsize; e += QT) Rp[e] = 0.0;
+  __syncthreads();
+
+  int it0 = 0;                                          // first item that may still have rows at or after r0
+  for (int r0 = 0; r0 < m; r0 += CR) {
+    const int cr = min(CR, m - r0);
+    if (tid == 0) s_c0 = na;
+    __syncthreads();
+    // row -> item map of this chunk, first non-zero column
+    for (int kk = it0 + tid; kk < ni; kk += QT) {
+      const int ro = d.item_rowoff[fb + kk];
+      if (ro < 0) continue;
+      const int rows = d.item_rows[fb + kk];
+      if (ro + rows <= r0 || ro >= r0 + cr) continue;
+      const int lo = max(ro, r0), hi = min(ro + rows, r0 + cr);
+      const unsigned long long lmask = d.item_lmask[fb + kk];
+      const long long off = d.item_off[fb + kk];
+      const int M = (rows + 3) / 4;
+      for (int g = lo; g < hi; ++g) {
+        row_rec[g - r0] = off;
+        row_lmask[g - r0] = lmask;
+        row_meta[g - r0] = (g - ro) | (M << 16);
+      }
+      const int first_cam = __ffsll((long long)lmask) - 1;
+      int b0 = 0;
+      while (b0 < na / 6 && s_cam[b0] < first_cam) ++b0;
+      atomicMin(&s_c0, 6 * b0);
+    }
+    __syncthreads();
+    const int c0 = s_c0;
+    // expand the rows (columns c0 .. na)
+    for (int e = tid; e < cr * (nc - c0); e += QT) {
+      const int i = e % cr, c = c0 + e / cr;
+      const int meta = row_meta[i];
+      Ch[(size_t)c * CR + i] = record_elem(d.pool + row_rec[i], meta >> 16, row_lmask[i], meta & 0xffff, c < na ? s_cam[c / 6] : 0, c % 6,
+                                           c == na);
+    }
+    __syncthreads();
+    // ---- fold the chunk into R
+    for (int j = c0; j < na; ++j) {
+      double v[QR_MAX_CR / 32];
+      double s = 0;
+      const double* colj = Ch + (size_t)j * CR;
+#pragma unroll
+      for (int t = 0; t < QR_MAX_CR / 32; ++t) {
+        const int i = lane + 32 * t;
+        const double x = (i < cr) ? colj[i] : 0.0;
+        v[t] = x;
+        s += x * x;
+      }
+      s = warp_sum(s);
+      if (s == 0.0) continue;                           // uniform over the CTA: nothing below the diagonal
+      const int ro = qr_row_off(j, na);
+      const double alpha = Rp[ro];
+      const double nrm = sqrt(alpha * alpha + s);
+      const double beta = (alpha >= 0) ? -nrm : nrm;
+      const double tau = (beta - alpha) / beta, sc = 1.0 / (alpha - beta);
+#pragma unroll
+      for (int t = 0; t < QR_MAX_CR / 32; ++t) v[t] *= sc;
+      for (int c = j + 1 + warp; c <= na; c += QT / 32) {
+        double* col = Ch + (size_t)c * CR;
+        double dot = 0;
+#pragma unroll
+        for (int t = 0; t < QR_MAX_CR / 32; ++t) {
+          const int i = lane + 32 * t;
+          if (i < cr) dot += v[t] * col[i];
+        }
+        dot = warp_sum(dot);
+        const double rjc = Rp[ro + c - j];
+        const double w = tau * (rjc + dot);
+        if (lane == 0) Rp[ro + c - j] = rjc - w;
+#pragma unroll
+        for (int t = 0; t < QR_MAX_CR / 32; ++t) {
+          const int i = lane + 32 * t;
+          if (i < cr) col[i] -= w * v[t];
+        }
+      }
+      __syncthreads();
+      if (tid == 0) Rp[ro] = beta;
+    }
+    __syncthreads();
+    // items wholly before the next chunk are done
+    while (it0 < ni) {
+      const int ro = d.item_rowoff[fb + it0];
+      if (ro >= 0 && ro + d.item_rows[fb + it0] > r0 + cr) break;
+      ++it0;
+    }
+  }
+  // ---- H_thin = R (k = n_a rows), r_thin = first n_a entries of Q^T r
+  for (int e = tid; e < na * nc; e += QT) {
+    const int i = e % na, c = e / na;
+    A[(size_t)c * mp + i] = (c >= i) ? Rp[qr_row_off(i, na) + c - i] : 0.0;
+  }
+}
+
+int qr_smem_doubles_for(int Nmax) {
+  const int na = 6 * Nmax;
+  long long want = (long long)QR_HDR + qr_packed_size(na) + 32LL * (na + 1) + 64;
+  const long long lo = 110 * 1024 / 8, hi = 220 * 1024 / 8;
+  if (want < lo) want = lo;
+  if (want > hi) want = hi;
+  return (int)want;
+}
+
+// Dense caller-supplied H (measurement_update API): one CTA factorises Adense (column-major, ld = mp) in place
+// with LAPACK-style Householder vectors, then copies H_thin | r_thin into the filter's compressed slot.
+__global__ void __launch_bounds__(UT) k_qr_dense(Dev d, int f, int mp) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int m = d.m_rows[f], na = d.n_act[f], k = d.k_rows[f], mpo = d.m_pad[f];
+  if (m == 0) return;
+  double* A = d.Adense;
   __shared__ double s_red[UT / 32];
   __shared__ double s_tau, s_v0inv;
-  for (int j = 0; j < na; ++j) {
-    double* colj = A + (size_t)j * mp;
-    double s = 0;
-    for (int i = j + 1 + tid; i < m; i += UT) { const double x = colj[i]; s += x * x; }
-    s = warp_sum(s);
-    if (lane == 0) s_red[warp] = s;
-    __syncthreads();
-    if (tid == 0) {
-      double xn2 = 0;
-      for (int w = 0; w < UT / 32; ++w) xn2 += s_red[w];
-      const double alpha = colj[j];
-      if (xn2 == 0.0) {
-        s_tau = 0.0; s_v0inv = 0.0;
-      } else {
-        const double nrm = sqrt(alpha * alpha + xn2);
-        const double beta = (alpha >= 0) ? -nrm : nrm;
-        s_tau = (beta - alpha) / beta;
-        s_v0inv = 1.0 / (alpha - beta);
-        colj[j] = beta;
-      }
-    }
-    __syncthreads();
-    const double tau = s_tau, sc = s_v0inv;
-    if (tau != 0.0) {
-      for (int i = j + 1 + tid; i < m; i += UT) colj[i] *= sc;
+  if (m > na) {
+    for (int j = 0; j < na; ++j) {
+      double* colj = A + (size_t)j * mp;
+      double s = 0;
+      for (int i = j + 1 + tid; i < m; i += UT) { const double x = colj[i]; s += x * x; }
+      s = warp_sum(s);
+      if (lane == 0) s_red[warp] = s;
       __syncthreads();
-      // apply H_j = I - tau v v^T to the remaining columns (incl. the residual column): warp per column
-      for (int c = j + 1 + warp; c <= na; c += UT / 32) {
-        double* col = A + (size_t)c * mp;
-        double w = (lane == 0) ? col[j] : 0.0;
-        for (int i = j + 1 + lane; i < m; i += 32) w += colj[i] * col[i];
-        w = warp_sum(w) * tau;
-        if (lane == 0) col[j] -= w;
-        for (int i = j + 1 + lane; i < m; i += 32) col[i] -= w * colj[i];
+      if (tid == 0) {
+        double xn2 = 0;
+        for (int w = 0; w < UT / 32; ++w) xn2 += s_red[w];
+        const double alpha = colj[j];
+        if (xn2 == 0.0) {
+          s_tau = 0.0; s_v0inv = 0.0;
+        } else {
+          const double nrm = sqrt(alpha * alpha + xn2);
+          const double beta = (alpha >= 0) ? -nrm : nrm;
+          s_tau = (beta - alpha) / beta;
+          s_v0inv = 1.0 / (alpha - beta);
+          colj[j] = beta;
+        }
       }
+      __syncthreads();
+      const double tau = s_tau, sc = s_v0inv;
+      if (tau != 0.0) {
+        for (int i = j + 1 + tid; i < m; i += UT) colj[i] *= sc;
+        __syncthreads();
+        for (int c = j + 1 + warp; c <= na; c += UT / 32) {
+          double* col = A + (size_t)c * mp;
+          double w = (lane == 0) ? col[j] : 0.0;
+          for (int i = j + 1 + lane; i < m; i += 32) w += colj[i] * col[i];
+          w = warp_sum(w) * tau;
+          if (lane == 0) col[j] -= w;
+          for (int i = j + 1 + lane; i < m; i += 32) col[i] -= w * colj[i];
+        }
+      }
+      __syncthreads();
     }
-    __syncthreads();
   }
-  // clean lower triangle of the top n_a x n_a block
-  for (int e = tid; e < na * na; e += UT) {
-    const int c = e / na, i = e - c * na;
-    if (i > c) A[(size_t)c * mp + i] = 0.0;
+  double* out = d.A + (size_t)f * d.A_elems;
+  for (int e = tid; e < k * (na + 1); e += UT) {
+    const int i = e % k, c = e / k;
+    out[(size_t)c * mpo + i] = (m > na && i > c) ? 0.0 : A[(size_t)c * mp + i];
   }
 }
 
@@ -99,9 +282,10 @@ __device__ __forceinline__ void gemm_tile(int K, LA loadA, LB loadB, double (&ac
 }
 
 // T = H_thin P[act,:]  (k x n), extra column n = r_thin.   grid (ceil((nmax+1)/32), ceil(Tk/32), F)
-__global__ void __launch_bounds__(UT) k_upd_T(Dev d) {
-  const int f = blockIdx.z, k = d.k_rows[f];
-  const int i0 = blockIdx.y * 32, j0 = blockIdx.x * 32;
+__device__ void k_upd_T_body(const Dev& d, int f, int bx, int by) {
+  const int k = d.k_rows[f];
+
+  const int i0 = by * 32, j0 = bx * 32;
   if (k == 0 || i0 >= k) return;
   const int n = NI + 6 * d.ncam[f];
   if (j0 > n) return;
@@ -125,11 +309,19 @@ __global__ void __launch_bounds__(UT) k_upd_T(Dev d) {
       }
     }
 }
+__global__ void __launch_bounds__(UT) k_upd_T(Dev d) {
+  const int nbig = (int)d.stage_ctr[SC_NUPD_BIG];
+  for (int w = blockIdx.z; w < nbig; w += gridDim.z) {
+    k_upd_T_body(d, d.wl_upd_big[w], blockIdx.x, blockIdx.y);
+    __syncthreads();
+  }
+}
 
 // S = T[:,act] H_thin^T + sigma^2 I  (k x k).   grid (ceil(Tk/32), ceil(Tk/32), F)
-__global__ void __launch_bounds__(UT) k_upd_S(Dev d) {
-  const int f = blockIdx.z, k = d.k_rows[f];
-  const int i0 = blockIdx.y * 32, j0 = blockIdx.x * 32;
+__device__ void k_upd_S_body(const Dev& d, int f, int bx, int by) {
+  const int k = d.k_rows[f];
+
+  const int i0 = by * 32, j0 = bx * 32;
   if (k == 0 || i0 >= k || j0 >= k || j0 > i0) return;     // lower triangle tiles only
   __shared__ double As[32][33], Bs[32][33];
   const int na = d.n_act[f], mp = d.m_pad[f];
@@ -149,12 +341,20 @@ __global__ void __launch_bounds__(UT) k_upd_S(Dev d) {
       if (i < k && j < k) S[(size_t)i * d.Tk + j] = acc[a][b] + (i == j ? d.prm->obs_noise : 0.0);
     }
 }
+__global__ void __launch_bounds__(UT) k_upd_S(Dev d) {
+  const int nbig = (int)d.stage_ctr[SC_NUPD_BIG];
+  for (int w = blockIdx.z; w < nbig; w += gridDim.z) {
+    k_upd_S_body(d, d.wl_upd_big[w], blockIdx.x, blockIdx.y);
+    __syncthreads();
+  }
+}
 
 // Cholesky of S (lower, in place, row-major), one CTA per filter.  Right-looking, one column at
 // a time; rows are distributed over threads.  (np.linalg.solve in the reference is an LU; S is
 // SPD so the factorisations agree to rounding.)
-__global__ void __launch_bounds__(UT) k_upd_chol(Dev d) {
-  const int f = blockIdx.x, tid = threadIdx.x, k = d.k_rows[f];
+__device__ void k_upd_chol_body(const Dev& d, int f, int bx, int by) {
+  const int tid = threadIdx.x, k = d.k_rows[f];
+
   if (k == 0) return;
   double* S = d.S + (size_t)f * d.Tk * d.Tk;
   const int ldS = d.Tk;
@@ -184,17 +384,25 @@ __global__ void __launch_bounds__(UT) k_upd_chol(Dev d) {
   }
   __syncthreads();
   if (s_bad && tid == 0) {
-    atomicOr(d.err, ERRBIT_NOT_SPD);
+    raise_not_spd(d, 3, f, k, d.n_act[f], d.m_rows[f]);
     d.k_rows[f] = 0;       // later stages skip this filter
+  }
+}
+__global__ void __launch_bounds__(UT) k_upd_chol(Dev d) {
+  const int nbig = (int)d.stage_ctr[SC_NUPD_BIG];
+  for (int w = blockIdx.x; w < nbig; w += gridDim.x) {
+    k_upd_chol_body(d, d.wl_upd_big[w], 0, 0);
+    __syncthreads();
   }
 }
 
 // W = L^-1 T (forward substitution, in place), 32 columns per CTA.   grid (ceil((nmax+1)/32), F)
-__global__ void __launch_bounds__(UT) k_upd_trsm(Dev d) {
-  const int f = blockIdx.y, k = d.k_rows[f];
+__device__ void k_upd_trsm_body(const Dev& d, int f, int bx, int by) {
+  const int k = d.k_rows[f];
+
   if (k == 0) return;
   const int n = NI + 6 * d.ncam[f];
-  const int j0 = blockIdx.x * 32;
+  const int j0 = bx * 32;
   if (j0 > n) return;
   __shared__ double As[32][33], Bs[32][33];
   __shared__ double Lbb[32][33], Xb[32][33];
@@ -233,20 +441,17 @@ __global__ void __launch_bounds__(UT) k_upd_trsm(Dev d) {
     __syncthreads();
   }
 }
+__global__ void __launch_bounds__(UT) k_upd_trsm(Dev d) {
+  const int nbig = (int)d.stage_ctr[SC_NUPD_BIG];
+  for (int w = blockIdx.y; w < nbig; w += gridDim.y) {
+    k_upd_trsm_body(d, d.wl_upd_big[w], blockIdx.x, 0);
+    __syncthreads();
+  }
+}
 
 // dx = W^T y, state injection (msckf.py:565-595).  One CTA per filter.
-__global__ void __launch_bounds__(UT) k_upd_inject(Dev d) {
-  const int f = blockIdx.x, tid = threadIdx.x, k = d.k_rows[f];
-  if (k == 0) return;
-  const int N = d.ncam[f], n = NI + 6 * N, tld = Tld(d);
-  const double* T = d.T + (size_t)f * d.Tk * tld;
-  double* dx = d.dx + (size_t)f * d.nmax;
-  for (int j = tid; j < n; j += UT) {
-    double s = 0;
-    for (int i = 0; i < k; ++i) s += T[(size_t)i * tld + j] * T[(size_t)i * tld + n];
-    dx[j] = s;
-  }
-  __syncthreads();
+__device__ void inject_state(const Dev& d, int f, const double* dx, int tid, int nthreads) {
+  const int N = d.ncam[f];
   if (tid == 0) {
     double* imu = d.imu + (size_t)f * IMU_STRIDE;
     double dq[4], q[4];
@@ -272,7 +477,7 @@ __global__ void __launch_bounds__(UT) k_upd_inject(Dev d) {
     for (int i = 0; i < 9; ++i) imu[MSCKF_IMU_R_IC + i] = Rn[i];
     for (int i = 0; i < 3; ++i) imu[MSCKF_IMU_T_CI + i] += dx[18 + i];
   }
-  for (int c = tid; c < N; c += UT) {
+  for (int c = tid; c < N; c += nthreads) {
     double* cs = d.cam + ((size_t)f * d.Nmax + c) * CAM_STRIDE;
     const double* dc = dx + NI + 6 * c;
     double dq[4], q[4];
@@ -286,12 +491,168 @@ __global__ void __launch_bounds__(UT) k_upd_inject(Dev d) {
   }
 }
 
+__global__ void __launch_bounds__(UT) k_upd_inject(Dev d) {
+  const int nbig = (int)d.stage_ctr[SC_NUPD_BIG];
+  const int tid = threadIdx.x;
+  for (int w = blockIdx.x; w < nbig; w += gridDim.x) {
+    const int f = d.wl_upd_big[w], k = d.k_rows[f];
+    if (k == 0) continue;
+    const int n = NI + 6 * d.ncam[f], tld = Tld(d);
+    const double* T = d.T + (size_t)f * d.Tk * tld;
+    double* dx = d.dx + (size_t)f * d.nmax;
+    for (int j = tid; j < n; j += UT) {
+      double s = 0;
+      for (int i = 0; i < k; ++i) s += T[(size_t)i * tld + j] * T[(size_t)i * tld + n];
+      dx[j] = s;
+    }
+    __syncthreads();
+    inject_state(d, f, dx, tid, UT);
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------ fused update for small compressed measurements
+// One CTA per filter does the whole of msckf.py:555-604 when H_thin has at most UPD_SMALL_K rows and UPD_SMALL_NA
+// active columns (the common case: a pruning update has 12 active columns, a lost-landmark update a few cameras):
+// T = H_thin P[act,:] and W = L^-1 T stay in shared memory; P is read once for T and read-modified-written once.
+template <int USK, int USNA, int PATH>
+__global__ void __launch_bounds__(UT) k_upd_small(Dev d) {
+  extern __shared__ double us[];
+  const int f = blockIdx.x, tid = threadIdx.x;
+  const int k = d.k_rows[f];
+  if (k == 0 || d.upd_path[f] != PATH) return;
+  const int na = d.n_act[f], mp = d.m_pad[f], n = NI + 6 * d.ncam[f], ld = d.ld;
+  const int ldA = na + 1, ldT = (n + 2) & ~1;          // T has n + 1 columns (last = r_thin), even leading dimension
+  double* sA = us;                                      // [USK][ldA]   rows >= k are zero
+  double* sT = sA + USK * (USNA + 1);                  // [USK][ldT]
+  double* sS = sT + USK * (((d.nmax + 2) & ~1));       // [USK][USK+1]
+  double* sdx = sS + USK * (USK + 1);                   // [nmax]
+  int* scm = (int*)(sdx + d.nmax);                      // [na]
+  __shared__ int s_bad;
+  const double* A = d.A + (size_t)f * d.A_elems;
+  double* P = d.P + (size_t)f * ld * ld;
+  const int* cm = d.colmap + (size_t)f * d.nmax;
+  if (tid == 0) s_bad = 0;
+  for (int e = tid; e < USK * ldA; e += UT) {
+    const int i = e / ldA, c = e - i * ldA;
+    sA[e] = (i < k) ? A[(size_t)c * mp + i] : 0.0;
+  }
+  for (int c = tid; c < na; c += UT) scm[c] = cm[c];
+  __syncthreads();
+  // ---- T = H_thin P[act, :]  : work item = (column j, block of 8 rows)
+  const int nib = (k + 7) / 8;
+  for (int it = tid; it < n * nib; it += UT) {
+    const int ib = it / n, j = it - ib * n;
+    double acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const double* a0 = sA + (8 * ib) * ldA;
+    for (int c = 0; c < na; ++c) {
+      const double pv = P[(size_t)scm[c] * ld + j];
+#pragma unroll
+      for (int t = 0; t < 8; ++t) acc[t] += a0[t * ldA + c] * pv;
+    }
+#pragma unroll
+    for (int t = 0; t < 8; ++t) sT[(8 * ib + t) * ldT + j] = acc[t];
+  }
+  for (int i = tid; i < 8 * nib; i += UT) sT[i * ldT + n] = sA[i * ldA + na];
+  __syncthreads();
+  // ---- S = T[:, act] H_thin^T + sigma^2 I   (lower triangle)
+  for (int e = tid; e < k * k; e += UT) {
+    const int i = e / k, j = e - i * k;
+    if (j > i) continue;
+    double s = 0;
+    for (int c = 0; c < na; ++c) s += sT[i * ldT + scm[c]] * sA[j * ldA + c];
+    if (i == j) s += d.prm->obs_noise;
+    sS[i * (USK + 1) + j] = s;
+  }
+  __syncthreads();
+  // ---- Cholesky (warp 0, lanes stride over rows)
+  if (tid < 32) {
+    for (int j = 0; j < k; ++j) {
+      const double dj = sS[j * (USK + 1) + j];
+      if (!(dj > 0.0)) { if (tid == 0) s_bad = 1; break; }
+      const double l = sqrt(dj);
+      __syncwarp();
+      if (tid == 0) sS[j * (USK + 1) + j] = l;
+      for (int i = j + 1 + tid; i < k; i += 32) {
+        const double lij = sS[i * (USK + 1) + j] / l;
+        sS[i * (USK + 1) + j] = lij;
+      }
+      __syncwarp();
+      for (int i = j + 1 + tid; i < k; i += 32) {
+        const double lij = sS[i * (USK + 1) + j];
+        for (int c = j + 1; c <= i; ++c) sS[i * (USK + 1) + c] -= lij * sS[c * (USK + 1) + j];
+      }
+      __syncwarp();
+    }
+  }
+  __syncthreads();
+  if (s_bad) {
+    if (tid == 0) raise_not_spd(d, 4, f, k, na, d.m_rows[f]);
+    return;
+  }
+  // ---- W = L^-1 [T | r_thin] : forward substitution, one column per thread
+  for (int j = tid; j <= n; j += UT) {
+    for (int i = 0; i < k; ++i) {
+      double x = sT[i * ldT + j];
+      for (int l = 0; l < i; ++l) x -= sS[i * (USK + 1) + l] * sT[l * ldT + j];
+      sT[i * ldT + j] = x / sS[i * (USK + 1) + i];
+    }
+  }
+  __syncthreads();
+  // ---- dx = W^T y, state injection
+  for (int j = tid; j < n; j += UT) {
+    double s = 0;
+    for (int i = 0; i < k; ++i) s += sT[i * ldT + j] * sT[i * ldT + n];
+    sdx[j] = s;
+  }
+  __syncthreads();
+  inject_state(d, f, sdx, tid, UT);
+  // ---- P <- P - W^T W : 4x4 register tiles over the upper triangle, mirrored
+  const int nt = (n + 3) / 4;
+  const int ntiles = nt * (nt + 1) / 2;
+  for (int t = tid; t < ntiles; t += UT) {
+    // (ta, tb), ta <= tb, enumerated row by row
+    int ta = (int)((2.0 * nt + 1.0 - sqrt((2.0 * nt + 1.0) * (2.0 * nt + 1.0) - 8.0 * t)) * 0.5);
+    while (ta > 0 && ta * nt - ta * (ta - 1) / 2 > t) --ta;
+    while ((ta + 1) * nt - (ta + 1) * ta / 2 <= t) ++ta;
+    const int tb = ta + (t - (ta * nt - ta * (ta - 1) / 2));
+    const int a0 = 4 * ta, b0 = 4 * tb;
+    double acc[4][4];
+#pragma unroll
+    for (int x = 0; x < 4; ++x)
+#pragma unroll
+      for (int y = 0; y < 4; ++y) acc[x][y] = 0.0;
+    for (int i = 0; i < k; ++i) {
+      const double* row = sT + i * ldT;
+      const double2 wa0 = *(const double2*)(row + a0), wa1 = *(const double2*)(row + a0 + 2);
+      const double2 wb0 = *(const double2*)(row + b0), wb1 = *(const double2*)(row + b0 + 2);
+      const double wa[4] = {wa0.x, wa0.y, wa1.x, wa1.y}, wb[4] = {wb0.x, wb0.y, wb1.x, wb1.y};
+#pragma unroll
+      for (int x = 0; x < 4; ++x)
+#pragma unroll
+        for (int y = 0; y < 4; ++y) acc[x][y] += wa[x] * wb[y];
+    }
+#pragma unroll
+    for (int x = 0; x < 4; ++x)
+#pragma unroll
+      for (int y = 0; y < 4; ++y) {
+        const int a = a0 + x, b = b0 + y;
+        if (a < n && b < n && b >= a) {
+          const double v = P[(size_t)a * ld + b] - acc[x][y];
+          P[(size_t)a * ld + b] = v;
+          P[(size_t)b * ld + a] = v;
+        }
+      }
+  }
+}
+
 // P <- P - W^T W.   grid (ceil(nmax/32), ceil(nmax/32), F); upper tiles only, mirrored.
-__global__ void __launch_bounds__(UT) k_upd_downdate(Dev d) {
-  const int f = blockIdx.z, k = d.k_rows[f];
+__device__ void k_upd_downdate_body(const Dev& d, int f, int bx, int by) {
+  const int k = d.k_rows[f];
+
   if (k == 0) return;
   const int n = NI + 6 * d.ncam[f];
-  const int i0 = blockIdx.y * 32, j0 = blockIdx.x * 32;
+  const int i0 = by * 32, j0 = bx * 32;
   if (i0 >= n || j0 >= n || j0 < i0) return;
   __shared__ double As[32][33], Bs[32][33];
   const int tld = Tld(d), ld = d.ld;
@@ -312,39 +673,80 @@ __global__ void __launch_bounds__(UT) k_upd_downdate(Dev d) {
       }
     }
 }
+__global__ void __launch_bounds__(UT) k_upd_downdate(Dev d) {
+  const int nbig = (int)d.stage_ctr[SC_NUPD_BIG];
+  for (int w = blockIdx.z; w < nbig; w += gridDim.z) {
+    k_upd_downdate_body(d, d.wl_upd_big[w], blockIdx.x, blockIdx.y);
+    __syncthreads();
+  }
+}
 
 // measurement_update(H, r) with a caller-supplied dense H: every state column is active.
 __global__ void __launch_bounds__(UT) k_load_dense_H(Dev d, int f, const double* __restrict__ H, const double* __restrict__ r, int m,
                                                       int n) {
   const int tid = blockIdx.x * UT + threadIdx.x, stride = gridDim.x * UT;
   const int mp = max(4, ((m + 3) / 4) * 4);
-  double* A = d.A + (size_t)f * d.A_elems;
+  double* A = d.Adense;
   for (long long e = tid; e < (long long)m * (n + 1); e += stride) {
     const int c = (int)(e / m), i = (int)(e - (long long)c * m);
     A[(size_t)c * mp + i] = (c < n) ? H[(size_t)i * n + c] : r[i];
   }
   if (tid < n) d.colmap[(size_t)f * d.nmax + tid] = tid;
   if (tid == 0) {
-    d.m_rows[f] = m; d.m_pad[f] = mp; d.n_act[f] = n; d.k_rows[f] = (m > n) ? n : m;
+    const int kr = (m > n) ? n : m;
+    d.m_rows[f] = m; d.m_pad[f] = max(4, ((kr + 3) / 4) * 4); d.n_act[f] = n; d.k_rows[f] = kr;
   }
 }
 
 __global__ void k_zero_krows_except(Dev d, int keep) {
   const int f = blockIdx.x * blockDim.x + threadIdx.x;
-  if (f < d.F && f != keep) { d.k_rows[f] = 0; d.m_rows[f] = 0; }
+  if (f < d.F && f != keep) { d.k_rows[f] = 0; d.m_rows[f] = 0; d.upd_path[f] = 0; }
+  if (f == 0) {                       // the caller-supplied H goes through the tiled path
+    d.stage_ctr[SC_NUPD_BIG] = 1ull;
+    d.wl_upd_big[0] = keep;
+    d.upd_path[keep] = 2;
+  }
 }
 
-void launch_qr(const Dev& d, cudaStream_t st) { KLAUNCH(d, KID_QR, st, (k_qr<<<d.F, UT, 0, st>>>(d))); }
+void launch_qr_build(const Dev& d, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(k_qr_build, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+    attr_set = true;
+  }
+  KLAUNCH(d, KID_QR, st, (k_qr_build<<<d.F, QT, (size_t)d.qr_smem_doubles * sizeof(double), st>>>(d, d.qr_smem_doubles)));
+}
+void launch_qr_dense(const Dev& d, int filter, int mp_dense, cudaStream_t st) {
+  KLAUNCH(d, KID_QR, st, (k_qr_dense<<<1, UT, 0, st>>>(d, filter, mp_dense)));
+}
+
+size_t upd_small_smem_bytes(int nmax, int K, int NA) {
+  const size_t dbl = (size_t)K * (NA + 1) + (size_t)K * ((nmax + 2) & ~1) + (size_t)K * (K + 1) + nmax + (NA + 1) / 2 + 2;
+  return dbl * sizeof(double);
+}
 
 void launch_update(const Dev& d, int stage, cudaStream_t st) {
   (void)stage;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(k_upd_small<UPD_SMALL_K, UPD_SMALL_NA, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(k_upd_small<UPD_MED_K, UPD_MED_NA, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    attr_set = true;
+  }
+  KLAUNCH(d, KID_UPD_SMALL, st,
+          (k_upd_small<UPD_SMALL_K, UPD_SMALL_NA, 1><<<d.F, UT, upd_small_smem_bytes(d.nmax, UPD_SMALL_K, UPD_SMALL_NA), st>>>(d)));
+  if (d.upd_med_ok)
+    KLAUNCH(d, KID_UPD_MED, st,
+            (k_upd_small<UPD_MED_K, UPD_MED_NA, 3><<<d.F, UT, upd_small_smem_bytes(d.nmax, UPD_MED_K, UPD_MED_NA), st>>>(d)));
+  // tiled path for the filters k_plan_stack queued in wl_upd_big (none in the common case: the grids exit at once)
   const int tn = (d.nmax + 1 + 31) / 32, tk = (d.Tk + 31) / 32, tp = (d.nmax + 31) / 32;
-  KLAUNCH(d, KID_UPD_T, st, (k_upd_T<<<dim3(tn, tk, d.F), UT, 0, st>>>(d)));
-  KLAUNCH(d, KID_UPD_S, st, (k_upd_S<<<dim3(tk, tk, d.F), UT, 0, st>>>(d)));
-  KLAUNCH(d, KID_UPD_CHOL, st, (k_upd_chol<<<d.F, UT, 0, st>>>(d)));
-  KLAUNCH(d, KID_UPD_TRSM, st, (k_upd_trsm<<<dim3(tn, d.F), UT, 0, st>>>(d)));
-  KLAUNCH(d, KID_UPD_INJECT, st, (k_upd_inject<<<d.F, UT, 0, st>>>(d)));
-  KLAUNCH(d, KID_UPD_DOWNDATE, st, (k_upd_downdate<<<dim3(tp, tp, d.F), UT, 0, st>>>(d)));
+  const int fz = d.F < 32 ? d.F : 32;
+  KLAUNCH(d, KID_UPD_T, st, (k_upd_T<<<dim3(tn, tk, fz), UT, 0, st>>>(d)));
+  KLAUNCH(d, KID_UPD_S, st, (k_upd_S<<<dim3(tk, tk, fz), UT, 0, st>>>(d)));
+  KLAUNCH(d, KID_UPD_CHOL, st, (k_upd_chol<<<fz, UT, 0, st>>>(d)));
+  KLAUNCH(d, KID_UPD_TRSM, st, (k_upd_trsm<<<dim3(tn, fz), UT, 0, st>>>(d)));
+  KLAUNCH(d, KID_UPD_INJECT, st, (k_upd_inject<<<fz, UT, 0, st>>>(d)));
+  KLAUNCH(d, KID_UPD_DOWNDATE, st, (k_upd_downdate<<<dim3(tp, tp, fz), UT, 0, st>>>(d)));
 }
 
 void launch_load_dense_H(const Dev& d, int filter, const double* H, const double* r, int m, int n_state, cudaStream_t st) {

@@ -28,6 +28,13 @@ constexpr unsigned ERRBIT_ROWS = 4u;
 constexpr unsigned ERRBIT_NOT_SPD = 8u;
 constexpr unsigned ERRBIT_CAM_CAP = 16u;
 
+// per-stage device counters (one memset per stage): pool bump pointer and work-list lengths
+constexpr int SC_POOL = 0, SC_NTRI = 1, SC_NJAC_SMALL = 2, SC_NJAC_BIG = 3, SC_NUPD_BIG = 4, SC_COUNT = 8;
+// the fused single-CTA update handles compressed measurements of at most this many rows / active columns
+constexpr int UPD_SMALL_K = 32, UPD_SMALL_NA = 48, UPD_MED_K = 64, UPD_MED_NA = 72;
+// landmarks with at most this many observations go through the warp-per-landmark Jacobian kernel
+constexpr int JAC_SMALL_M = 6;
+
 struct Params {
   double Qc[4];            // gyro, gyro-bias, acc, acc-bias noise variances (msckf.py:132-137)
   double obs_noise;        // config.py:76
@@ -85,15 +92,31 @@ struct Dev {
   int* nitem;              // [F]
   unsigned long long* rm_mask;     // [F] physical mask of the camera states being pruned
   int* rm_idx;             // [F][2] logical indices, -1 when not pruning
-  double* pool;            // per-feature Jacobian scratch (bump allocated per stage)
-  unsigned long long* pool_used;   // [1]
+  unsigned long long* item_lmask;  // [F][Fcap] the same mask in logical camera order (written by the Jacobian kernel)
+  double* pool;            // compact per-landmark Jacobian records (58 M doubles each, bump allocated per stage)
+  unsigned long long* stage_ctr;   // [SC_COUNT] pool bump pointer + work-list lengths, zeroed per stage
   long long pool_cap;      // elements
-  double* A;               // [F][A_elems] stacked compact Jacobian, column-major, ld = m_pad
+  int2* wl_tri;            // [F*Fcap] (filter, candidate) pairs that need triangulation
+  int2* wl_jac_small;      // [F*Fcap] (filter, item) pairs, M <= JAC_SMALL_M
+  int2* wl_jac_big;        // [F*Fcap] (filter, item) pairs, longer tracks
+  double* jac_scratch;     // T1 / S of long tracks that do not fit shared memory, per CTA of the big kernel
+  long long jac_scratch_stride;
+  int jac_big_smem_doubles, jac_big_grid;
+  int qr_smem_doubles;     // dynamic shared memory of k_qr_build
+  double* qr_scratch;      // [F][qr_scratch_stride] fallback for R + row chunk when they exceed shared memory (may be null)
+  long long qr_scratch_stride;
+  double* A;               // [F][A_elems] compressed Jacobian H_thin | r_thin, column-major, ld = m_pad
+  double* Adense;          // [Adense_elems] caller-supplied dense H of the measurement_update API (one filter at a time)
+  long long Adense_elems;
   int* m_rows;             // [F] rows stacked
-  int* m_pad;              // [F] leading dimension of A
+  int* m_pad;              // [F] leading dimension of A (k_rows rounded up to 4)
   int* n_act;              // [F] active columns (without r)
   int* k_rows;             // [F] rows of H_thin after compression
   int* colmap;             // [F][nmax] active column -> state index
+  int* upd_path;           // [F] 0 = no update, 1 / 3 = fused kernel (small / medium), 2 = tiled kernels (queued in wl_upd_big)
+  int upd_small_ok;
+  int upd_med_ok;          // the medium fused kernel fits shared memory for this window size
+  int* wl_upd_big;         // [F]
   double* T;               // [F][Tk][ld+8]  H_thin P | r  -> W | y
   double* S;               // [F][Tk][Tk]
   double* dx;              // [F][nmax]
@@ -106,13 +129,22 @@ struct Dev {
   int* log_upd;            // [2][F][2] rows, cols of the update
   long long* log_rm;       // [F][2]
   long long* counters;     // [F][MSCKF_N_COUNTERS]
-  unsigned* err;           // [1]
+  unsigned* err;           // [1] error bits, followed by [7] ints of detail about the first numeric failure
   unsigned char* did_reset;        // [F]
   double* imu_pub;         // [F][IMU_STRIDE] snapshot for publish()
   void* host_timer;        // KTimer* of the owning context (host only; never dereferenced on the device)
 };
 
 __host__ __device__ inline int Tld(const Dev& d) { return d.ld + 8; }
+
+// records where the first non-positive-definite innovation covariance was met (where: 1 gate, 2 dense gate, 3 tiled update,
+// 4 fused update), then raises the error bit
+__device__ __forceinline__ void raise_not_spd(const Dev& d, int where, int f, int a, int b, int c) {
+  if (atomicCAS(d.err + 1, 0u, (unsigned)where) == 0u) {
+    d.err[2] = (unsigned)f; d.err[3] = (unsigned)a; d.err[4] = (unsigned)b; d.err[5] = (unsigned)c;
+  }
+  atomicOr(d.err, ERRBIT_NOT_SPD);
+}
 
 // ------------------------------------------------------------------ warp helpers
 __device__ __forceinline__ double warp_sum(double v) {

@@ -30,7 +30,19 @@ def timed(lo, hi, sync_each):
         if sync_each: ctx.sync()
     ctx.mark(1); ms = ctx.mark_elapsed_ms(); ctx.sync()
     print('frames %d-%d sync_each=%s: dev %.3f ms/frame wall %.3f' % (lo, hi, sync_each, ms / (hi - lo), (time.perf_counter() - t0) * 1e3 / (hi - lo)))
-timed(40, 70, False)
-timed(70, 100, True)
-timed(100, 130, False)
-ctx.set_timing(True)
+def prof(lo, hi):
+    ctx.set_kernel_timing(True)
+    k0 = ctx.kernel_times()
+    for f in range(lo, hi): run(f)
+    ctx.sync()
+    k1 = ctx.kernel_times()
+    ctx.set_kernel_timing(False)
+    tot = sum(k1[n][2] - k0.get(n, (0, 0, 0))[2] for n in k1)
+    print('frames %d-%d kernel sum %.3f ms/frame' % (lo, hi, tot / (hi - lo)))
+    for n in sorted(k1, key=lambda n: -(k1[n][2] - k0.get(n, (0, 0, 0))[2]))[:8]:
+        print('   %-16s %.3f' % (n, (k1[n][2] - k0.get(n, (0, 0, 0))[2]) / (hi - lo)))
+prof(40, 55)
+prof(55, 70)
+prof(70, 85)
+timed(85, 115, False)
+timed(115, 145, False)

@@ -13,8 +13,8 @@ using namespace msckf;
 
 namespace msckf {
 const char* const kKernelNames[KID_COUNT] = {
-    "k_propagate", "k_augment", "k_observe", "k_classify_lost", "k_prune_select", "k_triangulate", "k_plan_items",
-    "k_jacobian_gate", "k_jacobian_big", "k_plan_stack", "k_qr", "k_upd_small", "k_upd_med", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
+    "k_propagate", "k_augment", "k_cam_prepare", "k_observe", "k_classify_lost", "k_prune_select", "k_triangulate", "k_plan_items",
+    "k_jacobian_gate", "k_jacobian_big", "k_plan_stack", "k_qr", "k_qr_warp", "k_qr_warp1", "k_upd_tiny", "k_upd_small", "k_upd_med", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
     "k_upd_downdate", "k_remove_cams", "k_finish_frame", "k_reset", "misc"};
 
 void KTimer::begin(int id, cudaStream_t st) {
@@ -240,9 +240,9 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   d.Tk = d.nmax;
   d.A_elems = (long long)((d.Tk + 3) / 4 * 4) * (d.nmax + 1);
   d.Adense_elems = (((long long)d.max_rows + 3) / 4 * 4) * (d.nmax + 1);
-  // compact Jacobian records: 58 doubles per observation of every landmark that reaches the gate in one stage
+  // Jacobian records: (4M-3) x (6M+1) doubles per landmark that reaches the gate in one stage
   long long pool = cfg->jacobian_pool_bytes > 0 ? cfg->jacobian_pool_bytes / 8
-                                                : (long long)d.F * ((long long)d.Fcap * 128 + 58LL * 4 * d.Nmax);
+                                                : (long long)d.F * ((long long)d.Fcap * 96 + 4 * jac_record_doubles(d.Nmax));
   d.pool_cap = pool;
   {
     const long long M = d.Nmax;
@@ -252,6 +252,11 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
     d.jac_big_grid = prop.multiProcessorCount * per_sm;
     d.jac_scratch_stride = 4 * M * (6 * M + 1) + (4 * M - 3) * (4 * M - 3);
     d.qr_smem_doubles = qr_smem_doubles_for(d.Nmax);
+    {   // stacked rows: the capped lost-landmark update, or the pruning update (5 rows per live landmark); everything when the cap is lifted
+      const long long all = (long long)d.Fcap * (4 * M - 3);
+      const long long capped = std::max<long long>(d.max_rows, 5LL * d.Fcap + 8);
+      d.rowmap_cap = (int)(row_cap > 0 ? std::min(all, capped) : all);
+    }
     d.upd_med_ok = upd_small_smem_bytes(d.nmax, UPD_MED_K, UPD_MED_NA) <= 200 * 1024 ? 1 : 0;
     d.upd_small_ok = getenv("MSCKF_NO_SMALL") ? 0 : 1;   // debugging knob: everything small goes through the medium kernel
     if (getenv("MSCKF_NO_MED")) d.upd_med_ok = 0;      // debugging knob: route medium updates through the tiled kernels
@@ -284,7 +289,7 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   CKC(cudaMemcpyAsync(dprm, &hp, sizeof hp, cudaMemcpyHostToDevice, ctx->st));
   d.prm = dprm;
   DA(d.imu, F * IMU_STRIDE);
-  DA(d.cam_id, F * Nm); DA(d.cam_phys, F * Nm); DA(d.cam, F * Nm * CAM_STRIDE); DA(d.ncam, F); DA(d.phys_used, F);
+  DA(d.cam_id, F * Nm); DA(d.cam_phys, F * Nm); DA(d.cam, F * Nm * CAM_STRIDE); DA(d.ncam, F); DA(d.phys_used, F); DA(d.cam_pre, F * Nm * CAM_PRE);
   DA(d.P, F * (size_t)d.ld * d.ld);
   DA(d.f_id, F * Fc); DA(d.f_mask, F * Fc); DA(d.f_flags, F * Fc); DA(d.f_pos, F * Fc * 3); DA(d.f_obs, F * Fc * Nm * 4);
   DA(d.ord, F * Fc); DA(d.ord_tmp, F * Fc); DA(d.nlive, F); DA(d.free_stack, F * Fc); DA(d.nfree, F);
@@ -294,11 +299,12 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   DA(d.item_dof, F * Fc); DA(d.item_gamma, F * Fc); DA(d.item_pass, F * Fc); DA(d.nitem, F);
   DA(d.rm_mask, F); DA(d.rm_idx, F * 2);
   DA(d.pool, (size_t)d.pool_cap); DA(d.stage_ctr, SC_COUNT); DA(d.item_lmask, F * Fc);
-  DA(d.wl_tri, F * Fc); DA(d.wl_jac_small, F * Fc); DA(d.wl_jac_big, F * Fc);
+  DA(d.wl_tri, F * Fc); DA(d.wl_jac_small, JAC_CLASSES * F * Fc); DA(d.wl_jac_big, F * Fc);
   DA(d.jac_scratch, (size_t)d.jac_big_grid * d.jac_scratch_stride);
   if (d.qr_scratch_stride) DA(d.qr_scratch, F * (size_t)d.qr_scratch_stride);
   DA(d.Adense, (size_t)d.Adense_elems);
   DA(d.A, F * (size_t)d.A_elems); DA(d.m_rows, F); DA(d.m_pad, F); DA(d.n_act, F); DA(d.k_rows, F); DA(d.colmap, F * (size_t)d.nmax); DA(d.upd_path, F); DA(d.wl_upd_big, F);
+  DA(d.rowmap, F * (size_t)d.rowmap_cap); DA(d.qr_cls, F); DA(d.wl_qr, (size_t)QR_WARP_CLASSES * F);
   DA(d.T, F * (size_t)d.Tk * Tld(d)); DA(d.S, F * (size_t)d.Tk * d.Tk); DA(d.dx, F * (size_t)d.nmax);
   DA(d.log_id, 2 * F * Fc); DA(d.log_status, 2 * F * Fc); DA(d.log_gamma, 2 * F * Fc); DA(d.log_dof, 2 * F * Fc);
   DA(d.log_n, 2 * F); DA(d.log_upd, 2 * F * 2); DA(d.log_rm, F * 2);
@@ -574,22 +580,26 @@ int msckf_set_feature_position(msckf_ctx* ctx, int32_t f, int64_t id, const doub
 static void enqueue_lost_stage(msckf_ctx* ctx) {
   const Dev& d = ctx->d;
   cudaMemsetAsync(d.stage_ctr, 0, SC_COUNT * sizeof(unsigned long long), ctx->st);
+  launch_cam_prepare(d, ctx->st);
   launch_classify_lost(d, ctx->st);
   launch_triangulate_store(d, ctx->st);
   launch_plan_items(d, 0, ctx->st);
-  launch_jacobian_gate(d, JAC_SMALL_M, 0, ctx->st);
+  launch_jacobian_gate(d, 0xE, 1, 0, ctx->st);            // lost landmarks have at least three observations
   launch_plan_stack(d, 0, ctx->st);
+  launch_qr_warp(d, ctx->st);
   launch_qr_build(d, ctx->st);
   launch_update(d, 0, ctx->st);
 }
 static void enqueue_prune_stage(msckf_ctx* ctx) {
   const Dev& d = ctx->d;
   cudaMemsetAsync(d.stage_ctr, 0, SC_COUNT * sizeof(unsigned long long), ctx->st);
+  launch_cam_prepare(d, ctx->st);
   launch_prune_select(d, ctx->st);
   launch_triangulate_store(d, ctx->st);
   launch_plan_items(d, 1, ctx->st);
-  launch_jacobian_gate(d, 2, 0, ctx->st);               // the pruning update always involves exactly two camera states
+  launch_jacobian_gate(d, 0x1, 0, 0, ctx->st);            // the pruning update always involves exactly two camera states
   launch_plan_stack(d, 1, ctx->st);
+  launch_qr_warp(d, ctx->st);
   launch_qr_build(d, ctx->st);
   launch_update(d, 1, ctx->st);
   launch_remove_cams(d, ctx->st);
@@ -951,7 +961,7 @@ int msckf_feature_jacobian(msckf_ctx* ctx, int32_t f, int64_t feature_id, int32_
   const int M = __builtin_popcountll(im);
   ARG(M >= 1, "landmark not observed by any of the given camera states");
   const int rows = 4 * M - 3;
-  const long long need = 58LL * M;
+  const long long need = jac_record_doubles(M);
   ARG(need <= d.pool_cap, "jacobian pool too small");
   // a one-item work list for filter f
   CK(cudaMemsetAsync(d.nitem, 0, d.F * sizeof(int), ctx->st));
@@ -968,13 +978,14 @@ int msckf_feature_jacobian(msckf_ctx* ctx, int32_t f, int64_t feature_id, int32_
   CK(cudaMemcpyAsync(d.nitem + f, &one, sizeof(int), cudaMemcpyHostToDevice, ctx->st));
   {                                          // a one-entry work list for the matching Jacobian kernel
     unsigned long long ctr[SC_COUNT] = {0};
-    ctr[M <= JAC_SMALL_M ? SC_NJAC_SMALL : SC_NJAC_BIG] = 1;
+    ctr[M <= JAC_SMALL_M ? SC_NJAC_SMALL + jac_class(M) : SC_NJAC_BIG] = 1;
     const int2 entry = make_int2(f, 0);
     CK(cudaMemcpyAsync(d.stage_ctr, ctr, sizeof ctr, cudaMemcpyHostToDevice, ctx->st));
-    CK(cudaMemcpyAsync(M <= JAC_SMALL_M ? d.wl_jac_small : d.wl_jac_big, &entry, sizeof entry, cudaMemcpyHostToDevice, ctx->st));
+    CK(cudaMemcpyAsync(M <= JAC_SMALL_M ? d.wl_jac_small + (size_t)jac_class(M) * d.F * d.Fcap : d.wl_jac_big, &entry, sizeof entry, cudaMemcpyHostToDevice, ctx->st));
     CK(cudaStreamSynchronize(ctx->st));      // the small host sources above live on this stack frame
   }
-  launch_jacobian_gate(d, JAC_SMALL_M, 1, ctx->st);
+  launch_cam_prepare(d, ctx->st);
+  launch_jacobian_gate(d, 0xF, 1, 1, ctx->st);
   double* dH = nullptr;
   CK(cudaMalloc((void**)&dH, ((size_t)rows * n_state + rows) * sizeof(double)));
   launch_export_item_dense(d, f, dH, dH + (size_t)rows * n_state, n_state, ctx->st);
@@ -1007,6 +1018,7 @@ int msckf_measurement_jacobian(msckf_ctx* ctx, int32_t f, int64_t cam_id, int64_
   ARG(c >= 0 && ((s.mask[slot] >> s.phys[c]) & 1ull), "camera state unknown or does not observe the landmark");
   double* dout = nullptr;
   CK(cudaMalloc((void**)&dout, 40 * sizeof(double)));
+  launch_cam_prepare(d, ctx->st);
   launch_measurement_jacobian(d, f, c, slot, dout, ctx->st);
   rc = sync_and_check(ctx);
   double out[40];

@@ -25,60 +25,98 @@ namespace msckf {
 constexpr int JAC_WARPS = 4;          // warps per CTA of the small-M kernel
 constexpr int JAC_BIG_T = 128;        // threads per CTA of the long-track kernel
 
-// msckf.py:429-498 for one (camera state, landmark).  cs = CAM_STRIDE block of the camera state.
-__device__ void measurement_jacobian(const double* cs, const double* p_w, const double* z, const double* g,
-                                     const double* R01, const double* t01, double* Hx /*[4][6]*/, double* Hf /*[4][3]*/,
-                                     double* r /*[4]*/) {
-  double R0[9], R1[9];
-  to_rotation(cs, R0);
-  const double* t0 = cs + 4;
-  mat3_mul(R01, R0, R1);
-  double tmp[3], t1[3];
-  mat3t_vec(R1, t01, tmp);
-  for (int i = 0; i < 3; ++i) t1[i] = t0[i] - tmp[i];
-  const double d0[3] = {p_w[0] - t0[0], p_w[1] - t0[1], p_w[2] - t0[2]};
-  const double d1[3] = {p_w[0] - t1[0], p_w[1] - t1[1], p_w[2] - t1[2]};
-  double pc0[3], pc1[3];
+// Per-stage derived quantities of every camera state, shared by all landmarks it observes (msckf.py:436-447,
+// 483-485): R0 = R(q) world -> cam0, R1 = R_01 R0, t0, t1 = t0 - R1^T t_01, R(q_null) g, p_null.
+__global__ void __launch_bounds__(64) k_cam_prepare(Dev d) {
+  const int f = blockIdx.x;
+  const int N = d.ncam[f];
+  const Params& prm = *d.prm;
+  const double* g = d.imu + (size_t)f * IMU_STRIDE + MSCKF_IMU_GRAVITY;
+  for (int c = threadIdx.x; c < N; c += 64) {
+    const double* cs = d.cam + ((size_t)f * d.Nmax + c) * CAM_STRIDE;
+    double* out = d.cam_pre + ((size_t)f * d.Nmax + c) * CAM_PRE;
+    double R0[9], R1[9], Rn[9], tmp[3], u[3];
+    to_rotation(cs, R0);
+    mat3_mul(prm.R01, R0, R1);
+    mat3t_vec(R1, prm.t01, tmp);
+    to_rotation(cs + 7, Rn);
+    mat3_vec(Rn, g, u);
+    for (int i = 0; i < 9; ++i) { out[i] = R0[i]; out[9 + i] = R1[i]; }
+    for (int i = 0; i < 3; ++i) {
+      out[18 + i] = cs[4 + i];
+      out[21 + i] = cs[4 + i] - tmp[i];
+      out[24 + i] = u[i];
+      out[27 + i] = cs[11 + i];
+    }
+  }
+}
+
+// msckf.py:429-498 for one (camera state, landmark), one camera of the stereo pair per call: h = 0 gives rows 0-1
+// (cam0), h = 1 rows 2-3 (cam1) of H_x (4x6), H_f (4x3), r (4).  pre = CAM_PRE block of the camera state.
+__device__ __forceinline__ void measurement_jacobian_half(const double* pre, const double* p_w, const double* z, const double* g,
+                                                          const double* R01, int h, double* Hx /*[2][6]*/, double* Hf /*[2][3]*/,
+                                                          double* r /*[2]*/) {
+  double R0[9];
+#pragma unroll
+  for (int i = 0; i < 9; ++i) R0[i] = pre[i];
+  const double d0[3] = {p_w[0] - pre[18], p_w[1] - pre[19], p_w[2] - pre[20]};
+  double pc0[3];
   mat3_vec(R0, d0, pc0);
-  mat3_vec(R1, d1, pc1);
-  // dz/dp rows (only the non-zero 2x3 halves)
-  const double a0[3] = {1 / pc0[2], 0.0, -pc0[0] / (pc0[2] * pc0[2])};
-  const double a1[3] = {0.0, 1 / pc0[2], -pc0[1] / (pc0[2] * pc0[2])};
-  const double b0[3] = {1 / pc1[2], 0.0, -pc1[0] / (pc1[2] * pc1[2])};
-  const double b1[3] = {0.0, 1 / pc1[2], -pc1[1] / (pc1[2] * pc1[2])};
-  double S0[9], D1[9];
+  double S0[9];
   skew3(pc0, S0);
-  mat3_mul(R01, S0, D1);
-  double A[24];
-  for (int j = 0; j < 3; ++j) {
-    A[0 * 6 + j] = a0[0] * S0[j] + a0[1] * S0[3 + j] + a0[2] * S0[6 + j];
-    A[1 * 6 + j] = a1[0] * S0[j] + a1[1] * S0[3 + j] + a1[2] * S0[6 + j];
-    A[2 * 6 + j] = b0[0] * D1[j] + b0[1] * D1[3 + j] + b0[2] * D1[6 + j];
-    A[3 * 6 + j] = b1[0] * D1[j] + b1[1] * D1[3 + j] + b1[2] * D1[6 + j];
-    A[0 * 6 + 3 + j] = a0[0] * -R0[j] + a0[1] * -R0[3 + j] + a0[2] * -R0[6 + j];
-    A[1 * 6 + 3 + j] = a1[0] * -R0[j] + a1[1] * -R0[3 + j] + a1[2] * -R0[6 + j];
-    A[2 * 6 + 3 + j] = b0[0] * -R1[j] + b0[1] * -R1[3 + j] + b0[2] * -R1[6 + j];
-    A[3 * 6 + 3 + j] = b1[0] * -R1[j] + b1[1] * -R1[3 + j] + b1[2] * -R1[6 + j];
+  double A[12];
+  double pcx, pcy, pcz;
+  if (h == 0) {
+    pcx = pc0[0]; pcy = pc0[1]; pcz = pc0[2];
+    // dz/dp rows (only the non-zero 2x3 halves)
+    const double a0[3] = {1 / pcz, 0.0, -pcx / (pcz * pcz)};
+    const double a1[3] = {0.0, 1 / pcz, -pcy / (pcz * pcz)};
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      A[j] = a0[0] * S0[j] + a0[1] * S0[3 + j] + a0[2] * S0[6 + j];
+      A[6 + j] = a1[0] * S0[j] + a1[1] * S0[3 + j] + a1[2] * S0[6 + j];
+      A[3 + j] = a0[0] * -R0[j] + a0[1] * -R0[3 + j] + a0[2] * -R0[6 + j];
+      A[9 + j] = a1[0] * -R0[j] + a1[1] * -R0[3 + j] + a1[2] * -R0[6 + j];
+    }
+  } else {
+    double R1[9], D1[9], pc1[3];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) R1[i] = pre[9 + i];
+    const double d1[3] = {p_w[0] - pre[21], p_w[1] - pre[22], p_w[2] - pre[23]};
+    mat3_vec(R1, d1, pc1);
+    mat3_mul(R01, S0, D1);
+    pcx = pc1[0]; pcy = pc1[1]; pcz = pc1[2];
+    const double b0[3] = {1 / pcz, 0.0, -pcx / (pcz * pcz)};
+    const double b1[3] = {0.0, 1 / pcz, -pcy / (pcz * pcz)};
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      A[j] = b0[0] * D1[j] + b0[1] * D1[3 + j] + b0[2] * D1[6 + j];
+      A[6 + j] = b1[0] * D1[j] + b1[1] * D1[3 + j] + b1[2] * D1[6 + j];
+      A[3 + j] = b0[0] * -R1[j] + b0[1] * -R1[3 + j] + b0[2] * -R1[6 + j];
+      A[9 + j] = b1[0] * -R1[j] + b1[1] * -R1[3 + j] + b1[2] * -R1[6 + j];
+    }
   }
   // observability constraint (msckf.py:483-490)
-  double u[6], Rn[9];
-  to_rotation(cs + 7, Rn);
-  mat3_vec(Rn, g, u);
-  const double dn[3] = {p_w[0] - cs[11], p_w[1] - cs[12], p_w[2] - cs[13]};
+  double u[6];
+  u[0] = pre[24]; u[1] = pre[25]; u[2] = pre[26];
+  const double dn[3] = {p_w[0] - pre[27], p_w[1] - pre[28], p_w[2] - pre[29]};
   cross3(dn, g, u + 3);
   double uu = 0;
+#pragma unroll
   for (int i = 0; i < 6; ++i) uu += u[i] * u[i];
-  for (int i = 0; i < 4; ++i) {
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
     double au = 0;
+#pragma unroll
     for (int j = 0; j < 6; ++j) au += A[6 * i + j] * u[j];
     const double sc = au / uu;           // (reference: A - (A u) u^T / (u^T u); one division per row instead of six)
+#pragma unroll
     for (int j = 0; j < 6; ++j) Hx[6 * i + j] = A[6 * i + j] - sc * u[j];
+#pragma unroll
     for (int j = 0; j < 3; ++j) Hf[3 * i + j] = -Hx[6 * i + 3 + j];
   }
-  r[0] = z[0] - pc0[0] / pc0[2];
-  r[1] = z[1] - pc0[1] / pc0[2];
-  r[2] = z[2] - pc1[0] / pc1[2];
-  r[3] = z[3] - pc1[1] / pc1[2];
+  r[0] = z[2 * h] - pcx / pcz;
+  r[1] = z[2 * h + 1] - pcy / pcz;
 }
 
 // Work buffers of one landmark (shared memory, or global scratch for T1 / S of very long tracks).
@@ -154,18 +192,19 @@ __device__ void jac_core(const Dev& d, int f, int k, int M, unsigned long long l
   // ---- step 1: per-observation blocks
   {
     const double p_w[3] = {d.f_pos[fs * 3], d.f_pos[fs * 3 + 1], d.f_pos[fs * 3 + 2]};
-    for (int a = tid; a < M; a += NT) {
+    for (int t = tid; t < 2 * M; t += NT) {            // (observation, camera of the stereo pair)
+      const int a = t >> 1, h = t & 1;
       const int c = B.cl[a];
-      const double* cs = d.cam + ((size_t)f * d.Nmax + c) * CAM_STRIDE;
+      const double* pre = d.cam_pre + ((size_t)f * d.Nmax + c) * CAM_PRE;
       const double* z = d.f_obs + (fs * d.Nmax + phys[c]) * 4;
-      double Hx[24], Hf[12], r[4];
-      measurement_jacobian(cs, p_w, z, g, prm.R01, prm.t01, Hx, Hf, r);
+      double Hx[12], Hf[6], r[2];
+      measurement_jacobian_half(pre, p_w, z, g, prm.R01, h, Hx, Hf, r);
 #pragma unroll
-      for (int e = 0; e < 24; ++e) B.Hx[24 * a + e] = Hx[e];
+      for (int e = 0; e < 12; ++e) B.Hx[24 * a + 12 * h + e] = Hx[e];
 #pragma unroll
-      for (int e = 0; e < 12; ++e) B.V[12 * a + e] = Hf[e];
-#pragma unroll
-      for (int e = 0; e < 4; ++e) B.r[4 * a + e] = r[e];
+      for (int e = 0; e < 6; ++e) B.V[12 * a + 6 * h + e] = Hf[e];
+      B.r[4 * a + 2 * h] = r[0];
+      B.r[4 * a + 2 * h + 1] = r[1];
     }
   }
   gsync<NT>(gmask);
@@ -346,10 +385,22 @@ __device__ void jac_core(const Dev& d, int f, int k, int M, unsigned long long l
   }
   gsync<NT>(gmask);
   pass = (int)B.Tm[8];
-  // ---- compact record for the stacking / QR kernel: Hx[M][24] V[4M][3] Zt[6M][3] Q^T r[4M]  (contiguous in B)
-  if ((pass || write_all) && d.item_off[ik] + 58 * M <= d.pool_cap) {     // (pool overflow is reported by k_plan_items)
+  // ---- record for the stacking / QR kernel: projected rows (Q^T E - rows 3..) and residual, row-major [R][6M+1]
+  if ((pass || write_all) && d.item_off[ik] + jac_record_doubles(M) <= d.pool_cap) {     // (pool overflow is reported by k_plan_items)
     double* out = d.pool + d.item_off[ik];
-    for (int e = tid; e < 58 * M; e += NT) out[e] = B.Hx[e];
+    const int ldr = C6 + 1;
+    for (int e = tid; e < R * ldr; e += NT) {
+      const int ii = e / ldr, c = e - ii * ldr, i = ii + 3;
+      double v;
+      if (c == C6) {
+        v = B.r[i];
+      } else {
+        const int a = c / 6;
+        v = (i >= 4 * a && i < 4 * a + 4) ? B.Hx[24 * a + 6 * (i - 4 * a) + (c - 6 * a)] : 0.0;
+        v -= B.V[3 * i] * B.Zt[3 * c] + B.V[3 * i + 1] * B.Zt[3 * c + 1] + B.V[3 * i + 2] * B.Zt[3 * c + 2];
+      }
+      out[e] = v;
+    }
   }
   gsync<NT>(gmask);
 }
@@ -371,17 +422,18 @@ __device__ __forceinline__ unsigned long long logical_mask(const Dev& d, int f, 
 
 // Small tracks: one group of G lanes per landmark, persistent grid over the work list wl_jac_small[0 .. n).
 template <int G>
-__global__ void __launch_bounds__(JAC_WARPS * 32, 4) k_jacobian_gate_small(Dev d, int per_group_doubles, int write_all) {
+__global__ void __launch_bounds__(JAC_WARPS * 32, 8) k_jacobian_gate_small(Dev d, int cls, int per_group_doubles, int write_all) {
   extern __shared__ double smem[];
   constexpr int GPW = 32 / G;                       // groups per warp
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int grp = lane / G, tid = lane - grp * G, gbase = grp * G;
   const unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << gbase);
-  const int n = (int)d.stage_ctr[SC_NJAC_SMALL];
+  const int n = (int)d.stage_ctr[SC_NJAC_SMALL + cls];
+  const int2* wl = d.wl_jac_small + (size_t)cls * d.F * d.Fcap;
   double* base = smem + (size_t)(warp * GPW + grp) * per_group_doubles;
   const int stride = gridDim.x * JAC_WARPS * GPW;
   for (int w = (blockIdx.x * JAC_WARPS + warp) * GPW + grp; w < n; w += stride) {
-    const int2 it = d.wl_jac_small[w];
+    const int2 it = wl[w];
     const size_t ik = (size_t)it.x * d.Fcap + it.y;
     const unsigned long long lmask = logical_mask<G>(d, it.x, d.item_mask[ik], tid, gmask, gbase);
     const int M = __popcll(lmask);
@@ -412,33 +464,30 @@ __global__ void __launch_bounds__(JAC_BIG_T) k_jacobian_gate_big(Dev d, int smem
 __global__ void k_measurement_jacobian(Dev d, int f, int c, int slot, double* out) {
   if (threadIdx.x != 0) return;
   const size_t fs = (size_t)f * d.Fcap + slot;
-  const double* cs = d.cam + ((size_t)f * d.Nmax + c) * CAM_STRIDE;
+  const double* pre = d.cam_pre + ((size_t)f * d.Nmax + c) * CAM_PRE;
   const double* z = d.f_obs + (fs * d.Nmax + d.cam_phys[(size_t)f * d.Nmax + c]) * 4;
-  measurement_jacobian(cs, d.f_pos + fs * 3, z, d.imu + (size_t)f * IMU_STRIDE + MSCKF_IMU_GRAVITY, d.prm->R01, d.prm->t01,
-                       out, out + 24, out + 36);
+  const double* g = d.imu + (size_t)f * IMU_STRIDE + MSCKF_IMU_GRAVITY;
+  for (int h = 0; h < 2; ++h)
+    measurement_jacobian_half(pre, d.f_pos + fs * 3, z, g, d.prm->R01, h, out + 12 * h, out + 24 + 6 * h, out + 36 + 2 * h);
 }
 
-// dense (rows x n_state) view of item 0 of filter f (feature_jacobian's return value), expanded from the compact record
+// dense (rows x n_state) view of item 0 of filter f (feature_jacobian's return value), scattered from its record
 __global__ void k_export_item_dense(Dev d, int f, double* H, double* r, int n_state) {
   const size_t ik = (size_t)f * d.Fcap;
   const unsigned long long lmask = d.item_lmask[ik];
-  const int rows = d.item_rows[ik], M = (rows + 3) / 4, C6 = 6 * M;
+  const int rows = d.item_rows[ik], M = (rows + 3) / 4, C6 = 6 * M, ldr = C6 + 1;
   const double* rec = d.pool + d.item_off[ik];
-  const double *Hx = rec, *V = rec + 24 * M, *Zt = rec + 36 * M, *rq = rec + 54 * M;
   const int N = d.ncam[f];
   for (int e = threadIdx.x; e < rows * n_state; e += blockDim.x) H[e] = 0.0;
   __syncthreads();
   for (int e = threadIdx.x; e < rows * C6; e += blockDim.x) {
-    const int ii = e / C6, c = e - ii * C6, a = c / 6, e6 = c - 6 * a, i = ii + 3;
-    // logical camera of observation a
-    int cam = -1, seen = 0;
+    const int ii = e / C6, c = e - ii * C6, a = c / 6, e6 = c - 6 * a;
+    int cam = -1, seen = 0;           // logical camera of observation a
     for (int cc = 0; cc < N; ++cc)
       if ((lmask >> cc) & 1ull) { if (seen == a) { cam = cc; break; } ++seen; }
-    double v = (i >= 4 * a && i < 4 * a + 4) ? Hx[24 * a + 6 * (i - 4 * a) + e6] : 0.0;
-    v -= V[3 * i] * Zt[3 * c] + V[3 * i + 1] * Zt[3 * c + 1] + V[3 * i + 2] * Zt[3 * c + 2];
-    H[(size_t)ii * n_state + NI + 6 * cam + e6] = v;
+    H[(size_t)ii * n_state + NI + 6 * cam + e6] = rec[ii * ldr + c];
   }
-  for (int i = threadIdx.x; i < rows; i += blockDim.x) r[i] = rq[i + 3];
+  for (int i = threadIdx.x; i < rows; i += blockDim.x) r[i] = rec[i * ldr + C6];
 }
 
 // gating_test on a dense caller-supplied H (m x n), r (m).  scratch: m*n + m*m + m doubles.
@@ -506,34 +555,40 @@ int sm_count() {
 }
 
 template <int G>
-static void launch_small(const Dev& d, int max_small_M, int write_all, cudaStream_t st) {
+static void launch_small(const Dev& d, int cls, int write_all, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(k_jacobian_gate_small<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     attr_set = true;
   }
-  const int per_group = (jac_small_doubles(max_small_M) + 1) & ~1;
+  int per_group = (jac_small_doubles(jac_class_maxM(cls)) + 15) & ~15;
+  if (G < 32) per_group += 8;      // neighbouring groups of a warp land on different halves of the banks
   const size_t smem = (size_t)JAC_WARPS * (32 / G) * per_group * sizeof(double);
-  int per_sm = (int)std::min<size_t>(4, (200 * 1024) / std::max<size_t>(smem + 1024, 1));
+  int per_sm = (int)std::min<size_t>(8, (220 * 1024) / std::max<size_t>(smem + 1024, 1));
   per_sm = std::max(per_sm, 1);
-  KLAUNCH(d, KID_JACOBIAN_GATE, st, (k_jacobian_gate_small<G><<<sm_count() * per_sm, JAC_WARPS * 32, smem, st>>>(d, per_group, write_all)));
+  KLAUNCH(d, KID_JACOBIAN_GATE, st, (k_jacobian_gate_small<G><<<sm_count() * per_sm, JAC_WARPS * 32, smem, st>>>(d, cls, per_group, write_all)));
 }
 
-// max_small_M: largest M the group kernel can meet in this stage (2 for the pruning stage: 8 lanes per landmark).
-void launch_jacobian_gate(const Dev& d, int max_small_M, int write_all, cudaStream_t st) {
+// class_mask: which size classes of the group-per-landmark kernel can occur in this stage (bit c = class c; the
+// pruning stage only has M = 2).  Lanes per landmark grow with the class so that the shared-memory-limited number of
+// landmarks in flight still fills the SM with warps.
+void launch_jacobian_gate(const Dev& d, int class_mask, int with_big, int write_all, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(k_jacobian_gate_big, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     attr_set = true;
   }
-  if (max_small_M <= 2) launch_small<8>(d, max_small_M, write_all, st);
-  else launch_small<16>(d, max_small_M, write_all, st);
-  if (max_small_M >= JAC_SMALL_M) {     // the stage can contain long tracks
+  if (class_mask & 1) launch_small<8>(d, 0, write_all, st);
+  if (class_mask & 2) launch_small<16>(d, 1, write_all, st);
+  if (class_mask & 4) launch_small<32>(d, 2, write_all, st);
+  if (class_mask & 8) launch_small<32>(d, 3, write_all, st);
+  if (with_big) {
     const int smem_doubles = d.jac_big_smem_doubles;
     KLAUNCH(d, KID_JACOBIAN_BIG, st,
             (k_jacobian_gate_big<<<d.jac_big_grid, JAC_BIG_T, (size_t)smem_doubles * sizeof(double), st>>>(d, smem_doubles, write_all)));
   }
 }
+void launch_cam_prepare(const Dev& d, cudaStream_t st) { KLAUNCH(d, KID_CAM_PREPARE, st, (k_cam_prepare<<<d.F, 64, 0, st>>>(d))); }
 void launch_measurement_jacobian(const Dev& d, int filter, int cam_logical, int slot, double* out, cudaStream_t st) {
   KLAUNCH(d, KID_MISC, st, (k_measurement_jacobian<<<1, 32, 0, st>>>(d, filter, cam_logical, slot, out)));
 }

@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(ST) k_plan_items(Dev d, int stage) {
       if (stage == 1) d.f_mask[(size_t)f * d.Fcap + slot] = mask & ~rmm;
     }
     const int rows = 4 * M - 3;
-    const long long need = isitem ? (long long)58 * M : 0;      // compact record, see k_jacobian.cu
+    const long long need = isitem ? jac_record_doubles(M) : 0;  // projected rows, see k_jacobian.cu
     int tot;
     const int r = block_rank(isitem, s_warp, tot);
     long long tot_e;
@@ -342,7 +342,10 @@ __global__ void __launch_bounds__(ST) k_plan_items(Dev d, int stage) {
       d.item_pass[k] = 0;
       d.item_gamma[k] = 0.0;
       d.item_rowoff[k] = -1;
-      if (M <= JAC_SMALL_M) d.wl_jac_small[atomicAdd(d.stage_ctr + SC_NJAC_SMALL, 1ull)] = make_int2(f, ni + r);
+      if (M <= JAC_SMALL_M) {
+        const int cls = jac_class(M);
+        d.wl_jac_small[(size_t)cls * d.F * d.Fcap + atomicAdd(d.stage_ctr + SC_NJAC_SMALL + cls, 1ull)] = make_int2(f, ni + r);
+      }
       else d.wl_jac_big[atomicAdd(d.stage_ctr + SC_NJAC_BIG, 1ull)] = make_int2(f, ni + r);
       const long long Ml = M, R = rows, C6 = 6 * Ml;
       w_obs += Ml;
@@ -405,6 +408,10 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
     const long long ro = used_rows + block_scan_ll(used ? rows : 0, s_warp_ll, tot_u);
     if (valid) {
       d.item_rowoff[ik] = used ? (int)ro : -1;
+      if (used && ro + rows <= d.rowmap_cap) {
+        int* rm = d.rowmap + (size_t)f * d.rowmap_cap + ro;
+        for (int li = 0; li < rows; ++li) rm[li] = (k << 8) | li;
+      }
       cst[d.item_cand[ik]] = processed ? (pass ? MSCKF_FEAT_GATE_PASS : MSCKF_FEAT_GATE_FAIL) : MSCKF_FEAT_AFTER_CAP;
       if (used) atomicOr(&s_act, d.item_mask[ik]);
       if (processed) atomicAdd(&s_proc, 1);
@@ -440,14 +447,21 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
     for (int c = 0; c < N; ++c)
       if ((act >> d.cam_phys[(size_t)f * d.Nmax + c]) & 1ull)
         for (int e = 0; e < 6; ++e) cm[na++] = NI + 6 * c + e;
+    if (m > d.rowmap_cap) { atomicOr(d.err, ERRBIT_ROWS); m = 0; }
     const int kr = (m > na) ? na : m;
+    int qcls = -1;
+    if (m > 0) {
+      qcls = (m > na && na <= 12) ? 0 : ((m > na && na <= 24) ? 1 : 2);
+      if (qcls < QR_WARP_CLASSES) d.wl_qr[(size_t)qcls * d.F + atomicAdd(d.stage_ctr + SC_NQR + qcls, 1ull)] = f;
+    }
+    d.qr_cls[f] = qcls;
     d.m_rows[f] = m;
     d.m_pad[f] = max(4, ((kr + 3) / 4) * 4);
     d.n_act[f] = na;
     d.k_rows[f] = kr;
     int path = 0;
     if (kr > 0) {
-      path = (d.upd_small_ok && kr <= UPD_SMALL_K && na <= UPD_SMALL_NA) ? 1 : ((d.upd_med_ok && kr <= UPD_MED_K && na <= UPD_MED_NA) ? 3 : 2);
+      path = (d.upd_small_ok && kr <= UPD_TINY_K && na <= UPD_TINY_NA) ? 4 : (d.upd_small_ok && kr <= UPD_SMALL_K && na <= UPD_SMALL_NA) ? 1 : ((d.upd_med_ok && kr <= UPD_MED_K && na <= UPD_MED_NA) ? 3 : 2);
       if (path == 2) d.wl_upd_big[atomicAdd(d.stage_ctr + SC_NUPD_BIG, 1ull)] = f;
     }
     d.upd_path[f] = path;

@@ -82,7 +82,17 @@ __device__ __forceinline__ void initial_guess(const Views& V, int vl, double* p)
 
 // The solver proper.  Views 0..nv-1 are staged in V by the caller (all lanes, then __syncwarp).
 // Rf/tf = pose of the first cam0 (camera -> world).  Returns validity; writes world position.
-__device__ bool lm_solve(const Views& V, int nv, const TriCfg& cfg, const double* Rf, const double* tf, int lane,
+template <int G>
+__device__ __forceinline__ double grp_sum(double v, unsigned m) {
+#pragma unroll
+  for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(m, v, o);
+  return v;
+}
+
+// G lanes (a whole warp, or 8 lanes so that four landmarks share a warp) cooperate; gmask = their lane mask,
+// lane = index inside the group.
+template <int G>
+__device__ bool lm_solve(const Views& V, int nv, const TriCfg& cfg, const double* Rf, const double* tf, int lane, unsigned gmask,
                          double* pos_w, int* n_solves) {
   // ---- initial guess from the first and the last cam0 view (feature.py:99-122, 216-218)
   const int vl = nv - 2;
@@ -94,12 +104,12 @@ __device__ bool lm_solve(const Views& V, int nv, const TriCfg& cfg, const double
   }
   // ---- initial cost
   double total = 0;
-  for (int v = lane; v < nv; v += 32) total += view_cost(V, v, x);
-  total = warp_sum(total);
+  for (int v = lane; v < nv; v += G) total += view_cost(V, v, x);
+  total = grp_sum<G>(total, gmask);
   // ---- normal equations at x (the reference rebuilds them every outer iteration, but x only
   //      changes on the single accepted step, after which nothing else is observable)
   double A[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0};
-  for (int v = lane; v < nv; v += 32) {   // feature.py:57-97, 241-248
+  for (int v = lane; v < nv; v += G) {   // feature.py:57-97, 241-248
     const double h1 = V.at(0, v) * x[0] + V.at(1, v) * x[1] + V.at(2, v) + x[2] * V.at(9, v);
     const double h2 = V.at(3, v) * x[0] + V.at(4, v) * x[1] + V.at(5, v) + x[2] * V.at(10, v);
     const double h3 = V.at(6, v) * x[0] + V.at(7, v) * x[1] + V.at(8, v) + x[2] * V.at(11, v);
@@ -121,8 +131,8 @@ __device__ bool lm_solve(const Views& V, int nv, const TriCfg& cfg, const double
       b[i] += s0 * r0 + s1 * r1;
     }
   }
-  for (int i = 0; i < 9; ++i) A[i] = warp_sum(A[i]);
-  for (int i = 0; i < 3; ++i) b[i] = warp_sum(b[i]);
+  for (int i = 0; i < 9; ++i) A[i] = grp_sum<G>(A[i], gmask);
+  for (int i = 0; i < 3; ++i) b[i] = grp_sum<G>(b[i], gmask);
 
   // ---- damped steps (feature.py:220-276).  is_cost_reduced is never cleared after a success,
   //      so at most one step is accepted; failed attempts walk lambda up in groups of inner_max.
@@ -141,8 +151,8 @@ __device__ bool lm_solve(const Views& V, int nv, const TriCfg& cfg, const double
       const double xn[3] = {x[0] - delta[0], x[1] - delta[1], x[2] - delta[2]};
       delta_norm = sqrt(delta[0] * delta[0] + delta[1] * delta[1] + delta[2] * delta[2]);
       double nc = 0;
-      for (int v = lane; v < nv; v += 32) nc += view_cost(V, v, xn);
-      nc = warp_sum(nc);
+      for (int v = lane; v < nv; v += G) nc += view_cost(V, v, xn);
+      nc = grp_sum<G>(nc, gmask);
       if (nc < total) {
         reduced = true;
         x[0] = xn[0]; x[1] = xn[1]; x[2] = xn[2];
@@ -160,11 +170,11 @@ __device__ bool lm_solve(const Views& V, int nv, const TriCfg& cfg, const double
   // ---- back to Euclidean, cheirality in every view (feature.py:278-295)
   const double fp[3] = {x[0] / x[2], x[1] / x[2], 1.0 / x[2]};
   bool ok = true;
-  for (int v = lane; v < nv; v += 32) {
+  for (int v = lane; v < nv; v += G) {
     const double z = V.at(6, v) * fp[0] + V.at(7, v) * fp[1] + V.at(8, v) * fp[2] + V.at(11, v);
     if (z <= 0) ok = false;
   }
-  ok = __all_sync(0xffffffffu, ok);
+  ok = __all_sync(gmask, ok);
   mat3_vec(Rf, fp, pos_w);
   for (int i = 0; i < 3; ++i) pos_w[i] += tf[i];
   return ok;
@@ -199,6 +209,32 @@ __device__ __forceinline__ void stage_views(const Views& V, int a, const double*
   V.at(12, 2 * a + 1) = z[2]; V.at(13, 2 * a + 1) = z[3];
 }
 
+// Same with R0 = R(q) and R1^T' = R_01 R0 taken from the per-stage camera table (bitwise the products above).
+__device__ __forceinline__ void stage_views_pre(const Views& V, int a, const double* pre, const double* p, const double* z,
+                                                const double* Rf, const double* tf, const TriCfg& cfg) {
+  double R0[9], R1t[9];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) { R0[k] = pre[k]; R1t[k] = pre[9 + k]; }
+  double Rr[9], a1[3], a2[3];
+  mat3_mul(R0, Rf, Rr);
+  mat3_vec(R0, tf, a1);
+  mat3_vec(R0, p, a2);
+  for (int k = 0; k < 9; ++k) V.at(k, 2 * a) = Rr[k];
+  for (int k = 0; k < 3; ++k) V.at(9 + k, 2 * a) = a1[k] + (-a2[k]);
+  V.at(12, 2 * a) = z[0]; V.at(13, 2 * a) = z[1];
+  double c10[3], tmp[3], t1[3];
+  mat3t_vec(cfg.R01, cfg.t01, tmp);
+  for (int k = 0; k < 3; ++k) c10[k] = -tmp[k];
+  mat3t_vec(R0, c10, tmp);
+  for (int k = 0; k < 3; ++k) t1[k] = tmp[k] + p[k];
+  mat3_mul(R1t, Rf, Rr);
+  mat3_vec(R1t, tf, a1);
+  mat3_vec(R1t, t1, a2);
+  for (int k = 0; k < 9; ++k) V.at(k, 2 * a + 1) = Rr[k];
+  for (int k = 0; k < 3; ++k) V.at(9 + k, 2 * a + 1) = a1[k] + (-a2[k]);
+  V.at(12, 2 * a + 1) = z[2]; V.at(13, 2 * a + 1) = z[3];
+}
+
 // check_motion (feature.py:124-165)
 __device__ __forceinline__ bool check_motion(const TriCfg& cfg, const double* Rf, const double* tf, const double* z_first,
                                              const double* p_last) {
@@ -216,15 +252,20 @@ __device__ __forceinline__ bool check_motion(const TriCfg& cfg, const double* Rf
 
 // ------------------------------------------------------------------ store-driven kernel
 // Persistent grid over the work list wl_tri[0 .. n) of (filter, candidate) pairs that still need a position
-// (built by k_classify_lost / k_prune_select); one warp per landmark.
+// (built by k_classify_lost / k_prune_select).  Tracks are short (a handful of stereo observations), so eight lanes
+// work on one landmark and four landmarks share a warp.
+constexpr int TRI_G = 8;
 __global__ void __launch_bounds__(TRI_WPB * 32) k_triangulate_store(Dev d) {
   extern __shared__ double smem[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int GPW = 32 / TRI_G;
+  const int warp = threadIdx.x >> 5, wl = threadIdx.x & 31;
+  const int grp = wl / TRI_G, lane = wl - grp * TRI_G, gbase = grp * TRI_G;
+  const unsigned gmask = ((1u << TRI_G) - 1u) << gbase;
   const int n = (int)d.stage_ctr[SC_NTRI];
   const TriCfg cfg = load_tricfg(*d.prm);
   const int stride = 2 * d.Nmax;
-  Views V{smem + (size_t)warp * VIEW_DOUBLES * stride, stride};
-  for (int w = blockIdx.x * TRI_WPB + warp; w < n; w += gridDim.x * TRI_WPB) {
+  Views V{smem + (size_t)(warp * GPW + grp) * (VIEW_DOUBLES * stride + 8), stride};
+  for (int w = (blockIdx.x * TRI_WPB + warp) * GPW + grp; w < n; w += gridDim.x * TRI_WPB * GPW) {
     const int2 it = d.wl_tri[w];
     const int f = it.x, ci = it.y;
     const int slot = d.cand[(size_t)f * d.Fcap + ci];
@@ -233,37 +274,37 @@ __global__ void __launch_bounds__(TRI_WPB * 32) k_triangulate_store(Dev d) {
     const int N = d.ncam[f];
     // logical-order observation mask
     unsigned long long lmask = 0;
-    for (int c0 = 0; c0 < N; c0 += 32) {
+    for (int c0 = 0; c0 < N; c0 += TRI_G) {
       const int c = c0 + lane;
       const int bit = (c < N) ? (int)((mask >> d.cam_phys[(size_t)f * d.Nmax + c]) & 1ull) : 0;
-      lmask |= (unsigned long long)__ballot_sync(0xffffffffu, bit) << c0;
+      const unsigned b = (__ballot_sync(gmask, bit) >> gbase) & ((1u << TRI_G) - 1u);
+      lmask |= (unsigned long long)b << c0;
     }
     const int M = __popcll(lmask);
     const int c_first = __ffsll((long long)lmask) - 1;
     const int c_last = 63 - __clzll((long long)lmask);
-    const double* camf = d.cam + ((size_t)f * d.Nmax + c_first) * CAM_STRIDE;
+    const double* pref = d.cam_pre + ((size_t)f * d.Nmax + c_first) * CAM_PRE;
     const double* caml = d.cam + ((size_t)f * d.Nmax + c_last) * CAM_STRIDE;
-    double R0f[9], Rf[9], tf[3];
-    to_rotation(camf, R0f);
+    double Rf[9], tf[3];
     for (int i = 0; i < 3; ++i)
-      for (int j = 0; j < 3; ++j) Rf[3 * i + j] = R0f[3 * j + i];
-    for (int i = 0; i < 3; ++i) tf[i] = camf[4 + i];
+      for (int j = 0; j < 3; ++j) Rf[3 * i + j] = pref[3 * j + i];
+    for (int i = 0; i < 3; ++i) tf[i] = pref[18 + i];
     const double* obs_base = d.f_obs + fs * d.Nmax * 4;
     const double* zf = obs_base + (size_t)d.cam_phys[(size_t)f * d.Nmax + c_first] * 4;
     bool ok = check_motion(cfg, Rf, tf, zf, caml + 4);
     double pos[3] = {0, 0, 0};
-    __syncwarp();                       // the previous landmark's views are no longer read
+    __syncwarp(gmask);                  // the previous landmark's views are no longer read
     if (ok) {
-      for (int c = lane; c < N; c += 32) {
+      for (int c = lane; c < N; c += TRI_G) {
         if ((lmask >> c) & 1ull) {
           const int a = __popcll(lmask & ((1ull << c) - 1ull));
-          const double* cs = d.cam + ((size_t)f * d.Nmax + c) * CAM_STRIDE;
-          stage_views(V, a, cs, cs + 4, obs_base + (size_t)d.cam_phys[(size_t)f * d.Nmax + c] * 4, Rf, tf, cfg);
+          const double* pre = d.cam_pre + ((size_t)f * d.Nmax + c) * CAM_PRE;
+          stage_views_pre(V, a, pre, pre + 18, obs_base + (size_t)d.cam_phys[(size_t)f * d.Nmax + c] * 4, Rf, tf, cfg);
         }
       }
-      __syncwarp();
+      __syncwarp(gmask);
       int ns = 0;
-      ok = lm_solve(V, 2 * M, cfg, Rf, tf, lane, pos, &ns);
+      ok = lm_solve<TRI_G>(V, 2 * M, cfg, Rf, tf, lane, gmask, pos, &ns);
       if (lane == 0) {
         d.f_pos[fs * 3 + 0] = pos[0]; d.f_pos[fs * 3 + 1] = pos[1]; d.f_pos[fs * 3 + 2] = pos[2];
         unsigned long long* cnt = (unsigned long long*)(d.counters + (size_t)NCNT * f);
@@ -317,7 +358,7 @@ __global__ void __launch_bounds__(TRI_WPB * 32) k_triangulate_raw(Dev d, int n, 
       if (lane == 0) { pos_out[3 * (size_t)i + 0] = pos[0]; pos_out[3 * (size_t)i + 1] = pos[1]; pos_out[3 * (size_t)i + 2] = pos[2]; }
       return;
     }
-    ok = lm_solve(V, 2 * M, cfg, Rf, tf, lane, pos, &ns);
+    ok = lm_solve<32>(V, 2 * M, cfg, Rf, tf, lane, 0xffffffffu, pos, &ns);
   }
   if (lane == 0) {
     pos_out[3 * (size_t)i + 0] = pos[0]; pos_out[3 * (size_t)i + 1] = pos[1]; pos_out[3 * (size_t)i + 2] = pos[2];
@@ -327,7 +368,7 @@ __global__ void __launch_bounds__(TRI_WPB * 32) k_triangulate_raw(Dev d, int n, 
 }
 
 void launch_triangulate_store(const Dev& d, cudaStream_t st) {
-  const size_t smem = (size_t)TRI_WPB * VIEW_DOUBLES * 2 * d.Nmax * sizeof(double);
+  const size_t smem = (size_t)TRI_WPB * (32 / TRI_G) * (VIEW_DOUBLES * 2 * d.Nmax + 8) * sizeof(double);
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(k_triangulate_store, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);

@@ -8,8 +8,8 @@ namespace msckf {
 
 // Kernel ids for launch counting and optional per-kernel event timing (msckf_kernel_times).
 enum KernelId {
-  KID_PROPAGATE = 0, KID_AUGMENT, KID_OBSERVE, KID_CLASSIFY_LOST, KID_PRUNE_SELECT, KID_TRIANGULATE, KID_PLAN_ITEMS,
-  KID_JACOBIAN_GATE, KID_JACOBIAN_BIG, KID_PLAN_STACK, KID_QR, KID_UPD_SMALL, KID_UPD_MED, KID_UPD_T, KID_UPD_S, KID_UPD_CHOL, KID_UPD_TRSM, KID_UPD_INJECT,
+  KID_PROPAGATE = 0, KID_AUGMENT, KID_CAM_PREPARE, KID_OBSERVE, KID_CLASSIFY_LOST, KID_PRUNE_SELECT, KID_TRIANGULATE, KID_PLAN_ITEMS,
+  KID_JACOBIAN_GATE, KID_JACOBIAN_BIG, KID_PLAN_STACK, KID_QR, KID_QR_WARP, KID_QR_WARP1, KID_UPD_TINY, KID_UPD_SMALL, KID_UPD_MED, KID_UPD_T, KID_UPD_S, KID_UPD_CHOL, KID_UPD_TRSM, KID_UPD_INJECT,
   KID_UPD_DOWNDATE, KID_REMOVE_CAMS, KID_FINISH_FRAME, KID_RESET, KID_MISC, KID_COUNT
 };
 extern const char* const kKernelNames[KID_COUNT];
@@ -57,8 +57,9 @@ void launch_triangulate_raw(const Dev& d, int n, const int* obs_off, const doubl
                             double* pos, unsigned char* valid, int* solves, int max_obs, int mode, cudaStream_t st);
 
 // k_jacobian.cu
-void launch_jacobian_gate(const Dev& d, int max_small_M, int write_all, cudaStream_t st);
+void launch_jacobian_gate(const Dev& d, int class_mask, int with_big, int write_all, cudaStream_t st);
 int sm_count();
+void launch_cam_prepare(const Dev& d, cudaStream_t st);
 void launch_measurement_jacobian(const Dev& d, int filter, int cam_logical, int slot, double* out /*[4*6+4*3+4]*/, cudaStream_t st);
 void launch_export_item_dense(const Dev& d, int filter, double* H, double* r, int n_state, cudaStream_t st);
 void launch_gate_dense(const Dev& d, int filter, const double* H, const double* r, int m, int n_state, int dof,
@@ -66,6 +67,7 @@ void launch_gate_dense(const Dev& d, int filter, const double* H, const double* 
 
 // k_update.cu
 void launch_qr_build(const Dev& d, cudaStream_t st);
+void launch_qr_warp(const Dev& d, cudaStream_t st);
 void launch_qr_dense(const Dev& d, int filter, int mp_dense, cudaStream_t st);
 int qr_smem_doubles_for(int Nmax);
 size_t upd_small_smem_bytes(int nmax, int K, int NA);

@@ -10,6 +10,7 @@ namespace msckf {
 // ------------------------------------------------------------------ constants
 constexpr int IMU_STRIDE = MSCKF_IMU_STRIDE;
 constexpr int CAM_STRIDE = MSCKF_CAM_STRIDE;   // q[4] p[3] q_null[4] p_null[3] pad[2]
+constexpr int CAM_PRE = 32;                     // R0[9] R1[9] t0[3] t1[3] R(q_null) g [3] p_null[3] pad[2]
 constexpr int NI = 21;                          // IMU error-state size
 constexpr int NCNT = MSCKF_N_COUNTERS;
 
@@ -29,9 +30,15 @@ constexpr unsigned ERRBIT_NOT_SPD = 8u;
 constexpr unsigned ERRBIT_CAM_CAP = 16u;
 
 // per-stage device counters (one memset per stage): pool bump pointer and work-list lengths
-constexpr int SC_POOL = 0, SC_NTRI = 1, SC_NJAC_SMALL = 2, SC_NJAC_BIG = 3, SC_NUPD_BIG = 4, SC_COUNT = 8;
+constexpr int SC_POOL = 0, SC_NTRI = 1, SC_NJAC_BIG = 2, SC_NUPD_BIG = 3, SC_NJAC_SMALL = 4 /* .. 7: one per size class */, SC_NQR = 8 /* .. 9: warp-QR classes */, SC_COUNT = 16;
+// stacked-Jacobian compression classes: 0 = at most 12 active columns (pruning update), 1 = at most 24, 2 = general CTA kernel
+constexpr int QR_WARP_CLASSES = 2;
+// size classes of the group-per-landmark Jacobian kernel (shared memory is sized per class): M <= 2, M = 3, M = 4, M <= 6
+constexpr int JAC_CLASSES = 4;
+__host__ __device__ inline int jac_class(int M) { return M <= 2 ? 0 : (M == 3 ? 1 : (M == 4 ? 2 : 3)); }
+__host__ __device__ inline int jac_class_maxM(int c) { return c == 0 ? 2 : (c == 1 ? 3 : (c == 2 ? 4 : 6)); }
 // the fused single-CTA update handles compressed measurements of at most this many rows / active columns
-constexpr int UPD_SMALL_K = 32, UPD_SMALL_NA = 48, UPD_MED_K = 64, UPD_MED_NA = 72;
+constexpr int UPD_TINY_K = 16, UPD_TINY_NA = 24, UPD_SMALL_K = 32, UPD_SMALL_NA = 48, UPD_MED_K = 64, UPD_MED_NA = 72;
 // landmarks with at most this many observations go through the warp-per-landmark Jacobian kernel
 constexpr int JAC_SMALL_M = 6;
 
@@ -62,6 +69,7 @@ struct Dev {
   int* cam_phys;           // [F][Nmax]   physical observation slot of each camera state
   double* cam;             // [F][Nmax][CAM_STRIDE]
   int* ncam;               // [F]
+  double* cam_pre;         // [F][Nmax][CAM_PRE] per-stage derived camera quantities (k_cam_prepare)
   unsigned long long* phys_used;   // [F] bit mask of physical slots in use
   double* P;               // [F][ld*ld] row-major, logical layout, n = 21+6*ncam
   // ---- landmark store (map_server)
@@ -97,7 +105,7 @@ struct Dev {
   unsigned long long* stage_ctr;   // [SC_COUNT] pool bump pointer + work-list lengths, zeroed per stage
   long long pool_cap;      // elements
   int2* wl_tri;            // [F*Fcap] (filter, candidate) pairs that need triangulation
-  int2* wl_jac_small;      // [F*Fcap] (filter, item) pairs, M <= JAC_SMALL_M
+  int2* wl_jac_small;      // [JAC_CLASSES][F*Fcap] (filter, item) pairs, M <= JAC_SMALL_M, binned by size class
   int2* wl_jac_big;        // [F*Fcap] (filter, item) pairs, longer tracks
   double* jac_scratch;     // T1 / S of long tracks that do not fit shared memory, per CTA of the big kernel
   long long jac_scratch_stride;
@@ -113,7 +121,11 @@ struct Dev {
   int* n_act;              // [F] active columns (without r)
   int* k_rows;             // [F] rows of H_thin after compression
   int* colmap;             // [F][nmax] active column -> state index
-  int* upd_path;           // [F] 0 = no update, 1 / 3 = fused kernel (small / medium), 2 = tiled kernels (queued in wl_upd_big)
+  int* rowmap;             // [F][rowmap_cap] stacked row -> (item << 8 | row inside the item's record)
+  int rowmap_cap;
+  int* qr_cls;             // [F] compression class of this stage's stacked Jacobian (-1: nothing to do)
+  int* wl_qr;              // [QR_WARP_CLASSES][F] filters of the warp-QR classes
+  int* upd_path;           // [F] 0 = no update, 4 / 1 / 3 = fused kernel (tiny / small / medium), 2 = tiled kernels (queued in wl_upd_big)
   int upd_small_ok;
   int upd_med_ok;          // the medium fused kernel fits shared memory for this window size
   int* wl_upd_big;         // [F]
@@ -136,6 +148,9 @@ struct Dev {
 };
 
 __host__ __device__ inline int Tld(const Dev& d) { return d.ld + 8; }
+// Pool record of a landmark that passed the gate: its projected Jacobian rows, row-major [4M-3][6M+1]
+// (six columns per observation in logical camera order, last column = projected residual).
+__host__ __device__ inline long long jac_record_doubles(int M) { return (long long)(4 * M - 3) * (6 * M + 1); }
 
 // records where the first non-positive-definite innovation covariance was met (where: 1 gate, 2 dense gate, 3 tiled update,
 // 4 fused update), then raises the error bit

@@ -111,7 +111,7 @@ def run_pair(stream, max_cam, n_frames, feature_capacity=1024, row_cap=None):
     dcfg = ConfigEuRoC()
     dcfg._vio_max_cam_state_size__ = max_cam
     if row_cap is not None:
-        dcfg.row_cap = row_cap
+        dcfg.row_cap = row_cap if row_cap < 10 ** 8 else 0      # <= 0 lifts the cap in the library
     df = MSCKF(dcfg, feature_capacity=feature_capacity)
     worst = {'imu': 0.0, 'P': 0.0, 'cams': 0.0, 'extr': 0.0, 'pos_m': 0.0}
     counts = {'gates': 0, 'pass': 0, 'prunes': 0, 'updates': 0}
@@ -162,6 +162,32 @@ def test_stream_vs_oracle_window30():
     worst, counts = run_pair(stream, 30, n_frames, feature_capacity=2048)
     assert counts['gates'] > 2000 and counts['prunes'] >= 10 and 0 < counts['pass'] < counts['gates'], counts
     assert worst['imu'] < TOL and worst['P'] < TOL and worst['cams'] < TOL and worst['extr'] < TOL, worst
+    assert worst['pos_m'] < 1e-3, worst
+
+
+def test_stress_long_tracks_cap_lifted():
+    """configs[2] in small: a 30-state window, long tracks, the row cap lifted, and a final frame in which EVERY live
+    landmark is lost at once (its ids are replaced): long-track Jacobians (one CTA per landmark), the general
+    stacking + QR kernel with up to 174 active columns and the tiled update."""
+    n_frames = 44
+    st = synth.make_structure(n_frames, 120, structure_seed=3, mean_track_len=40.0)
+    st.frame_ids[-1] = st.frame_ids[-1] + 10 ** 6
+    stream = synth.realize(st, noise_seed=7)
+    worst, counts = run_pair(stream, 30, n_frames, feature_capacity=1024, row_cap=10 ** 9)
+    assert counts['gates'] > 500 and counts['updates'] > 20, counts
+    assert max(worst['imu'], worst['P'], worst['cams'], worst['extr']) < TOL, worst
+    assert worst['pos_m'] < 1e-3, worst
+
+
+def test_large_window_64():
+    """configs[4] in small: max_cam_state_size = 64 (state dimension 405): Jacobian scratch in global memory, the
+    QR fallback buffers and the tiled update on the full-size covariance."""
+    n_frames = 76
+    st = synth.make_structure(n_frames, 100, structure_seed=5, mean_track_len=30.0)
+    stream = synth.realize(st, noise_seed=9)
+    worst, counts = run_pair(stream, 64, n_frames, feature_capacity=1024)
+    assert counts['gates'] > 500 and counts['prunes'] >= 3, counts
+    assert max(worst['imu'], worst['P'], worst['cams'], worst['extr']) < TOL, worst
     assert worst['pos_m'] < 1e-3, worst
 
 

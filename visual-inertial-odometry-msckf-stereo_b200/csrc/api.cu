@@ -91,7 +91,8 @@ struct msckf_ctx {
     cudaError_t e_ = (call);                                                                       \
     if (e_ != cudaSuccess) {                                                                       \
       char buf_[512];                                                                              \
-      snprintf(buf_, sizeof buf_, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+      snprintf(buf_, sizeof buf_, "%s failed: %s (%s:%d)%s%s", #call, cudaGetErrorString(e_), __FILE__, __LINE__, \
+               ctx->kt.bad_launch >= 0 ? " first rejected launch: " : "", ctx->kt.bad_launch >= 0 ? kKernelNames[ctx->kt.bad_launch] : ""); \
       ctx->err = buf_;                                                                             \
       return MSCKF_ERR_CUDA;                                                                       \
     }                                                                                              \
@@ -241,8 +242,14 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   d.A_elems = (long long)((d.Tk + 3) / 4 * 4) * (d.nmax + 1);
   d.Adense_elems = (((long long)d.max_rows + 3) / 4 * 4) * (d.nmax + 1);
   // Jacobian records: (4M-3) x (6M+1) doubles per landmark that reaches the gate in one stage
-  long long pool = cfg->jacobian_pool_bytes > 0 ? cfg->jacobian_pool_bytes / 8
-                                                : (long long)d.F * ((long long)d.Fcap * 96 + 4 * jac_record_doubles(d.Nmax));
+  long long pool;
+  if (cfg->jacobian_pool_bytes > 0) {
+    pool = cfg->jacobian_pool_bytes / 8;
+  } else {    // typical tracks for every filter, and up to 2 GB towards the worst case (every landmark seen by the whole window)
+    const long long base = (long long)d.F * ((long long)d.Fcap * 96 + 4 * jac_record_doubles(d.Nmax));
+    const long long worst = (long long)d.F * d.Fcap * jac_record_doubles(d.Nmax);
+    pool = std::max(base, std::min<long long>(worst, 256LL << 20));
+  }
   d.pool_cap = pool;
   {
     const long long M = d.Nmax;

@@ -258,14 +258,14 @@ constexpr int TRI_G = 8;
 __global__ void __launch_bounds__(TRI_WPB * 32) k_triangulate_store(Dev d) {
   extern __shared__ double smem[];
   constexpr int GPW = 32 / TRI_G;
-  const int warp = threadIdx.x >> 5, wl = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5, wl = threadIdx.x & 31, wpb = blockDim.x >> 5;     // warps per CTA chosen by the launcher
   const int grp = wl / TRI_G, lane = wl - grp * TRI_G, gbase = grp * TRI_G;
   const unsigned gmask = ((1u << TRI_G) - 1u) << gbase;
   const int n = (int)d.stage_ctr[SC_NTRI];
   const TriCfg cfg = load_tricfg(*d.prm);
   const int stride = 2 * d.Nmax;
   Views V{smem + (size_t)(warp * GPW + grp) * (VIEW_DOUBLES * stride + 8), stride};
-  for (int w = (blockIdx.x * TRI_WPB + warp) * GPW + grp; w < n; w += gridDim.x * TRI_WPB * GPW) {
+  for (int w = (blockIdx.x * wpb + warp) * GPW + grp; w < n; w += gridDim.x * wpb * GPW) {
     const int2 it = d.wl_tri[w];
     const int f = it.x, ci = it.y;
     const int slot = d.cand[(size_t)f * d.Fcap + ci];
@@ -368,7 +368,9 @@ __global__ void __launch_bounds__(TRI_WPB * 32) k_triangulate_raw(Dev d, int n, 
 }
 
 void launch_triangulate_store(const Dev& d, cudaStream_t st) {
-  const size_t smem = (size_t)TRI_WPB * (32 / TRI_G) * (VIEW_DOUBLES * 2 * d.Nmax + 8) * sizeof(double);
+  int wpb = TRI_WPB;                     // fewer warps per CTA for wide windows so that the views fit shared memory
+  while (wpb > 1 && (size_t)wpb * (32 / TRI_G) * (VIEW_DOUBLES * 2 * d.Nmax + 8) * sizeof(double) > 96 * 1024) wpb >>= 1;
+  const size_t smem = (size_t)wpb * (32 / TRI_G) * (VIEW_DOUBLES * 2 * d.Nmax + 8) * sizeof(double);
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(k_triangulate_store, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
@@ -376,7 +378,7 @@ void launch_triangulate_store(const Dev& d, cudaStream_t st) {
     attr_set = true;
   }
   const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(12, (200 * 1024) / (smem + 1024)));
-  KLAUNCH(d, KID_TRIANGULATE, st, (k_triangulate_store<<<sm_count() * per_sm, TRI_WPB * 32, smem, st>>>(d)));
+  KLAUNCH(d, KID_TRIANGULATE, st, (k_triangulate_store<<<sm_count() * per_sm, wpb * 32, smem, st>>>(d)));
 }
 
 void launch_triangulate_raw(const Dev& d, int n, const int* obs_off, const double* uv, const double* cam_q, const double* cam_p,

@@ -18,6 +18,7 @@ extern const char* const kKernelNames[KID_COUNT];
 // `timing` is set (two events per launch on the launching stream, accumulated at flush()).
 struct KTimer {
   bool timing = false;
+  int bad_launch = -1;           // kernel id of the first launch the runtime rejected (reported with the error text)
   long long launches[KID_COUNT] = {};
   double ms[KID_COUNT] = {};
   long long timed[KID_COUNT] = {};
@@ -33,6 +34,7 @@ struct KTimer {
     KTimer* kt_ = static_cast<KTimer*>((d).host_timer); \
     if (kt_) kt_->begin((id), (st));                    \
     __VA_ARGS__;                                        \
+    if (kt_ && kt_->bad_launch < 0 && cudaPeekAtLastError() != cudaSuccess) kt_->bad_launch = (id); \
     if (kt_) kt_->end((st));                            \
   } while (0)
 

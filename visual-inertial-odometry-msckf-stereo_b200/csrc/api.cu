@@ -14,7 +14,7 @@ using namespace msckf;
 namespace msckf {
 const char* const kKernelNames[KID_COUNT] = {
     "k_propagate", "k_augment", "k_cam_prepare", "k_observe", "k_classify_lost", "k_prune_select", "k_triangulate", "k_plan_items",
-    "k_jacobian_gate", "k_jacobian_big", "k_plan_stack", "k_qr", "k_qr_warp", "k_qr_warp1", "k_upd_tiny", "k_upd_small", "k_upd_med", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
+    "k_jacobian_gate", "k_jacobian_big", "k_plan_stack", "k_qr", "k_qr_warp", "k_qr_warp1", "k_upd_dmma16", "k_upd_dmma64", "k_upd_tiny", "k_upd_small", "k_upd_med", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
     "k_upd_downdate", "k_remove_cams", "k_finish_frame", "k_reset", "misc"};
 
 void KTimer::begin(int id, cudaStream_t st) {
@@ -266,7 +266,9 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
     }
     d.upd_med_ok = upd_small_smem_bytes(d.nmax, UPD_MED_K, UPD_MED_NA) <= 200 * 1024 ? 1 : 0;
     d.upd_small_ok = getenv("MSCKF_NO_SMALL") ? 0 : 1;   // debugging knob: everything small goes through the medium kernel
-    if (getenv("MSCKF_NO_MED")) d.upd_med_ok = 0;      // debugging knob: route medium updates through the tiled kernels
+    if (getenv("MSCKF_NO_MED")) d.upd_med_ok = 0;
+    d.upd_dmma_ok[0] = (!getenv("MSCKF_NO_DMMA") && upd_dmma_smem_bytes(d.nmax, 16) <= 220 * 1024) ? 1 : 0;
+    d.upd_dmma_ok[1] = (!getenv("MSCKF_NO_DMMA") && upd_dmma_smem_bytes(d.nmax, 64) <= 220 * 1024) ? 1 : 0;      // debugging knob: route medium updates through the tiled kernels
     const long long na = 6 * M, worst = 640 + na * (na + 1) / 2 + na + 32 * (na + 1) + 64;
     d.qr_scratch_stride = worst > d.qr_smem_doubles ? na * (na + 1) / 2 + na + 256 * (na + 1) : 0;
   }
@@ -310,7 +312,7 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   DA(d.jac_scratch, (size_t)d.jac_big_grid * d.jac_scratch_stride);
   if (d.qr_scratch_stride) DA(d.qr_scratch, F * (size_t)d.qr_scratch_stride);
   DA(d.Adense, (size_t)d.Adense_elems);
-  DA(d.A, F * (size_t)d.A_elems); DA(d.m_rows, F); DA(d.m_pad, F); DA(d.n_act, F); DA(d.k_rows, F); DA(d.colmap, F * (size_t)d.nmax); DA(d.upd_path, F); DA(d.wl_upd_big, F);
+  DA(d.A, F * (size_t)d.A_elems); DA(d.m_rows, F); DA(d.m_pad, F); DA(d.n_act, F); DA(d.k_rows, F); DA(d.colmap, F * (size_t)d.nmax); DA(d.upd_path, F); DA(d.wl_upd_big, F); DA(d.wl_upd_dmma, 2 * F);
   DA(d.rowmap, F * (size_t)d.rowmap_cap); DA(d.qr_cls, F); DA(d.wl_qr, (size_t)QR_WARP_CLASSES * F);
   DA(d.T, F * (size_t)d.Tk * Tld(d)); DA(d.S, F * (size_t)d.Tk * d.Tk); DA(d.dx, F * (size_t)d.nmax);
   DA(d.log_id, 2 * F * Fc); DA(d.log_status, 2 * F * Fc); DA(d.log_gamma, 2 * F * Fc); DA(d.log_dof, 2 * F * Fc);

@@ -576,48 +576,7 @@ __global__ void __launch_bounds__(UT) k_upd_trsm(Dev d) {
   }
 }
 
-// dx = W^T y, state injection (msckf.py:565-595).  One CTA per filter.
-__device__ void inject_state(const Dev& d, int f, const double* dx, int tid, int nthreads) {
-  const int N = d.ncam[f];
-  if (tid == 0) {
-    double* imu = d.imu + (size_t)f * IMU_STRIDE;
-    double dq[4], q[4];
-    small_angle_quat(dx, dq);
-    quat_mul(dq, imu + MSCKF_IMU_Q, q);
-    for (int i = 0; i < 4; ++i) imu[MSCKF_IMU_Q + i] = q[i];
-    for (int i = 0; i < 3; ++i) {
-      imu[MSCKF_IMU_BG + i] += dx[3 + i];
-      imu[MSCKF_IMU_V + i] += dx[6 + i];
-      imu[MSCKF_IMU_BA + i] += dx[9 + i];
-      imu[MSCKF_IMU_P + i] += dx[12 + i];
-    }
-    if (imu[MSCKF_IMU_NULL_ALIASED] != 0.0) {       // the reference's "+=" moves the aliased null members too
-      for (int i = 0; i < 3; ++i) {
-        imu[MSCKF_IMU_V_NULL + i] = imu[MSCKF_IMU_V + i];
-        imu[MSCKF_IMU_P_NULL + i] = imu[MSCKF_IMU_P + i];
-      }
-    }
-    double dqe[4], Re[9], Rn[9];
-    small_angle_quat(dx + 15, dqe);
-    to_rotation(dqe, Re);
-    mat3_mul(Re, imu + MSCKF_IMU_R_IC, Rn);
-    for (int i = 0; i < 9; ++i) imu[MSCKF_IMU_R_IC + i] = Rn[i];
-    for (int i = 0; i < 3; ++i) imu[MSCKF_IMU_T_CI + i] += dx[18 + i];
-  }
-  for (int c = tid; c < N; c += nthreads) {
-    double* cs = d.cam + ((size_t)f * d.Nmax + c) * CAM_STRIDE;
-    const double* dc = dx + NI + 6 * c;
-    double dq[4], q[4];
-    small_angle_quat(dc, dq);
-    quat_mul(dq, cs, q);
-    for (int i = 0; i < 4; ++i) cs[i] = q[i];
-    for (int i = 0; i < 3; ++i) {
-      cs[4 + i] += dc[3 + i];
-      cs[11 + i] = cs[4 + i];      // position_null aliases _vio_position__ (msckf.py:400, 595)
-    }
-  }
-}
-
+// dx = W^T y, state injection (msckf.py:565-595): inject_state lives in msckf_dev.cuh.  One CTA per filter.
 __global__ void __launch_bounds__(UT) k_upd_inject(Dev d) {
   const int nbig = (int)d.stage_ctr[SC_NUPD_BIG];
   const int tid = threadIdx.x;
@@ -861,6 +820,7 @@ void launch_update(const Dev& d, int stage, cudaStream_t st) {
     cudaFuncSetAttribute(k_upd_small<UPD_TINY_K, UPD_TINY_NA, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
     attr_set = true;
   }
+  launch_update_dmma(d, st);
   KLAUNCH(d, KID_UPD_TINY, st,
           (k_upd_small<UPD_TINY_K, UPD_TINY_NA, 4><<<d.F, UT, upd_small_smem_bytes(d.nmax, UPD_TINY_K, UPD_TINY_NA), st>>>(d)));
   KLAUNCH(d, KID_UPD_SMALL, st,

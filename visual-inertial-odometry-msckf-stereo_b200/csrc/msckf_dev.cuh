@@ -30,7 +30,7 @@ constexpr unsigned ERRBIT_NOT_SPD = 8u;
 constexpr unsigned ERRBIT_CAM_CAP = 16u;
 
 // per-stage device counters (one memset per stage): pool bump pointer and work-list lengths
-constexpr int SC_POOL = 0, SC_NTRI = 1, SC_NJAC_BIG = 2, SC_NUPD_BIG = 3, SC_NJAC_SMALL = 4 /* .. 7: one per size class */, SC_NQR = 8 /* .. 9: warp-QR classes */, SC_COUNT = 16;
+constexpr int SC_POOL = 0, SC_NTRI = 1, SC_NJAC_BIG = 2, SC_NUPD_BIG = 3, SC_NJAC_SMALL = 4 /* .. 7: one per size class */, SC_NQR = 8 /* .. 9: warp-QR classes */, SC_NUPD_DMMA = 10 /* .. 11: tensor-pipe update classes */, SC_COUNT = 16;
 // stacked-Jacobian compression classes: 0 = at most 12 active columns (pruning update), 1 = at most 24, 2 = general CTA kernel
 constexpr int QR_WARP_CLASSES = 2;
 // size classes of the group-per-landmark Jacobian kernel (shared memory is sized per class): M <= 2, M = 3, M = 4, M <= 6
@@ -125,10 +125,12 @@ struct Dev {
   int rowmap_cap;
   int* qr_cls;             // [F] compression class of this stage's stacked Jacobian (-1: nothing to do)
   int* wl_qr;              // [QR_WARP_CLASSES][F] filters of the warp-QR classes
-  int* upd_path;           // [F] 0 = no update, 4 / 1 / 3 = fused kernel (tiny / small / medium), 2 = tiled kernels (queued in wl_upd_big)
+  int* upd_path;           // [F] 0 = no update, 4 / 1 / 3 = fused kernel (tiny / small / medium), 2 = tiled kernels (queued in wl_upd_big), 5 / 6 = DMMA kernel (k <= 16 / k <= 64)
   int upd_small_ok;
   int upd_med_ok;          // the medium fused kernel fits shared memory for this window size
   int* wl_upd_big;         // [F]
+  int* wl_upd_dmma;        // [2][F] filters of the tensor-pipe update classes (k <= 16, k <= 64)
+  int upd_dmma_ok[2];      // class fits shared memory for this window size
   double* T;               // [F][Tk][ld+8]  H_thin P | r  -> W | y
   double* S;               // [F][Tk][Tk]
   double* dx;              // [F][nmax]
@@ -272,6 +274,48 @@ __device__ __forceinline__ void small_angle_quat(const double* dtheta, double* q
   } else {
     const double n = sqrt(1 + s);
     q[0] = d[0] / n; q[1] = d[1] / n; q[2] = d[2] / n; q[3] = 1. / n;
+  }
+}
+
+// state injection of the correction dx (msckf.py:565-595), cooperatively by `nthreads` threads of one CTA
+__device__ __forceinline__ void inject_state(const Dev& d, int f, const double* dx, int tid, int nthreads) {
+  const int N = d.ncam[f];
+  if (tid == 0) {
+    double* imu = d.imu + (size_t)f * IMU_STRIDE;
+    double dq[4], q[4];
+    small_angle_quat(dx, dq);
+    quat_mul(dq, imu + MSCKF_IMU_Q, q);
+    for (int i = 0; i < 4; ++i) imu[MSCKF_IMU_Q + i] = q[i];
+    for (int i = 0; i < 3; ++i) {
+      imu[MSCKF_IMU_BG + i] += dx[3 + i];
+      imu[MSCKF_IMU_V + i] += dx[6 + i];
+      imu[MSCKF_IMU_BA + i] += dx[9 + i];
+      imu[MSCKF_IMU_P + i] += dx[12 + i];
+    }
+    if (imu[MSCKF_IMU_NULL_ALIASED] != 0.0) {       // the reference's "+=" moves the aliased null members too
+      for (int i = 0; i < 3; ++i) {
+        imu[MSCKF_IMU_V_NULL + i] = imu[MSCKF_IMU_V + i];
+        imu[MSCKF_IMU_P_NULL + i] = imu[MSCKF_IMU_P + i];
+      }
+    }
+    double dqe[4], Re[9], Rn[9];
+    small_angle_quat(dx + 15, dqe);
+    to_rotation(dqe, Re);
+    mat3_mul(Re, imu + MSCKF_IMU_R_IC, Rn);
+    for (int i = 0; i < 9; ++i) imu[MSCKF_IMU_R_IC + i] = Rn[i];
+    for (int i = 0; i < 3; ++i) imu[MSCKF_IMU_T_CI + i] += dx[18 + i];
+  }
+  for (int c = tid; c < N; c += nthreads) {
+    double* cs = d.cam + ((size_t)f * d.Nmax + c) * CAM_STRIDE;
+    const double* dc = dx + NI + 6 * c;
+    double dq[4], q[4];
+    small_angle_quat(dc, dq);
+    quat_mul(dq, cs, q);
+    for (int i = 0; i < 4; ++i) cs[i] = q[i];
+    for (int i = 0; i < 3; ++i) {
+      cs[4 + i] += dc[3 + i];
+      cs[11 + i] = cs[4 + i];      // position_null aliases _vio_position__ (msckf.py:400, 595)
+    }
   }
 }
 

@@ -461,9 +461,7 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
     d.k_rows[f] = kr;
     int path = 0;
     if (kr > 0) {
-      path = (d.upd_small_ok && kr <= UPD_TINY_K && na <= UPD_TINY_NA) ? 4 : (d.upd_small_ok && kr <= UPD_SMALL_K && na <= UPD_SMALL_NA) ? 1 : ((d.upd_med_ok && kr <= UPD_MED_K && na <= UPD_MED_NA) ? 3 : 2);
-      if (m > na && na <= 16 && d.upd_dmma_ok[0]) path = 5;           // compressed (H_thin = R, k = n_a): tensor-pipe kernel
-      else if (m > na && na <= 64 && d.upd_dmma_ok[1]) path = 6;
+      path = (kr <= 16 && na <= 16 && d.upd_dmma_ok[0]) ? 5 : ((kr <= 64 && na <= 64 && d.upd_dmma_ok[1]) ? 6 : 2);   // one-CTA tensor-pipe kernel, else tiled
       if (path == 2) d.wl_upd_big[atomicAdd(d.stage_ctr + SC_NUPD_BIG, 1ull)] = f;
       if (path >= 5) d.wl_upd_dmma[(size_t)(path - 5) * d.F + atomicAdd(d.stage_ctr + SC_NUPD_DMMA + (path - 5), 1ull)] = f;
     }

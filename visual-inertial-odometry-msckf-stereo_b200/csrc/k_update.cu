@@ -597,141 +597,6 @@ __global__ void __launch_bounds__(UT) k_upd_inject(Dev d) {
   }
 }
 
-// ------------------------------------------------------------------ fused update for small compressed measurements
-// One CTA per filter does the whole of msckf.py:555-604 when H_thin has at most UPD_SMALL_K rows and UPD_SMALL_NA
-// active columns (the common case: a pruning update has 12 active columns, a lost-landmark update a few cameras):
-// T = H_thin P[act,:] and W = L^-1 T stay in shared memory; P is read once for T and read-modified-written once.
-template <int USK, int USNA, int PATH>
-__global__ void __launch_bounds__(UT) k_upd_small(Dev d) {
-  extern __shared__ double us[];
-  const int f = blockIdx.x, tid = threadIdx.x;
-  const int k = d.k_rows[f];
-  if (k == 0 || d.upd_path[f] != PATH) return;
-  const int na = d.n_act[f], mp = d.m_pad[f], n = NI + 6 * d.ncam[f], ld = d.ld;
-  const int ldA = na + 1, ldT = (n + 2) & ~1;          // T has n + 1 columns (last = r_thin), even leading dimension
-  double* sA = us;                                      // [USK][ldA]   rows >= k are zero
-  double* sT = sA + USK * (USNA + 1);                  // [USK][ldT]
-  double* sS = sT + USK * (((d.nmax + 2) & ~1));       // [USK][USK+1]
-  double* sdx = sS + USK * (USK + 1);                   // [nmax]
-  int* scm = (int*)(sdx + d.nmax);                      // [na]
-  __shared__ int s_bad;
-  const double* A = d.A + (size_t)f * d.A_elems;
-  double* P = d.P + (size_t)f * ld * ld;
-  const int* cm = d.colmap + (size_t)f * d.nmax;
-  if (tid == 0) s_bad = 0;
-  for (int e = tid; e < USK * ldA; e += UT) {
-    const int i = e / ldA, c = e - i * ldA;
-    sA[e] = (i < k) ? A[(size_t)c * mp + i] : 0.0;
-  }
-  for (int c = tid; c < na; c += UT) scm[c] = cm[c];
-  __syncthreads();
-  // ---- T = H_thin P[act, :]  : work item = (column j, block of 8 rows)
-  const int nib = (k + 7) / 8;
-  for (int it = tid; it < n * nib; it += UT) {
-    const int ib = it / n, j = it - ib * n;
-    double acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    const double* a0 = sA + (8 * ib) * ldA;
-    for (int c = 0; c < na; ++c) {
-      const double pv = P[(size_t)scm[c] * ld + j];
-#pragma unroll
-      for (int t = 0; t < 8; ++t) acc[t] += a0[t * ldA + c] * pv;
-    }
-#pragma unroll
-    for (int t = 0; t < 8; ++t) sT[(8 * ib + t) * ldT + j] = acc[t];
-  }
-  for (int i = tid; i < 8 * nib; i += UT) sT[i * ldT + n] = sA[i * ldA + na];
-  __syncthreads();
-  // ---- S = T[:, act] H_thin^T + sigma^2 I   (lower triangle)
-  for (int e = tid; e < k * k; e += UT) {
-    const int i = e / k, j = e - i * k;
-    if (j > i) continue;
-    double s = 0;
-    for (int c = 0; c < na; ++c) s += sT[i * ldT + scm[c]] * sA[j * ldA + c];
-    if (i == j) s += d.prm->obs_noise;
-    sS[i * (USK + 1) + j] = s;
-  }
-  __syncthreads();
-  // ---- Cholesky (warp 0, lanes stride over rows)
-  if (tid < 32) {
-    for (int j = 0; j < k; ++j) {
-      const double dj = sS[j * (USK + 1) + j];
-      if (!(dj > 0.0)) { if (tid == 0) s_bad = 1; break; }
-      const double l = sqrt(dj);
-      __syncwarp();
-      if (tid == 0) sS[j * (USK + 1) + j] = l;
-      for (int i = j + 1 + tid; i < k; i += 32) {
-        const double lij = sS[i * (USK + 1) + j] / l;
-        sS[i * (USK + 1) + j] = lij;
-      }
-      __syncwarp();
-      for (int i = j + 1 + tid; i < k; i += 32) {
-        const double lij = sS[i * (USK + 1) + j];
-        for (int c = j + 1; c <= i; ++c) sS[i * (USK + 1) + c] -= lij * sS[c * (USK + 1) + j];
-      }
-      __syncwarp();
-    }
-  }
-  __syncthreads();
-  if (s_bad) {
-    if (tid == 0) raise_not_spd(d, 4, f, k, na, d.m_rows[f]);
-    return;
-  }
-  // ---- W = L^-1 [T | r_thin] : forward substitution, one column per thread
-  for (int j = tid; j <= n; j += UT) {
-    for (int i = 0; i < k; ++i) {
-      double x = sT[i * ldT + j];
-      for (int l = 0; l < i; ++l) x -= sS[i * (USK + 1) + l] * sT[l * ldT + j];
-      sT[i * ldT + j] = x / sS[i * (USK + 1) + i];
-    }
-  }
-  __syncthreads();
-  // ---- dx = W^T y, state injection
-  for (int j = tid; j < n; j += UT) {
-    double s = 0;
-    for (int i = 0; i < k; ++i) s += sT[i * ldT + j] * sT[i * ldT + n];
-    sdx[j] = s;
-  }
-  __syncthreads();
-  inject_state(d, f, sdx, tid, UT);
-  // ---- P <- P - W^T W : 4x4 register tiles over the upper triangle, mirrored
-  const int nt = (n + 3) / 4;
-  const int ntiles = nt * (nt + 1) / 2;
-  for (int t = tid; t < ntiles; t += UT) {
-    // (ta, tb), ta <= tb, enumerated row by row
-    int ta = (int)((2.0 * nt + 1.0 - sqrt((2.0 * nt + 1.0) * (2.0 * nt + 1.0) - 8.0 * t)) * 0.5);
-    while (ta > 0 && ta * nt - ta * (ta - 1) / 2 > t) --ta;
-    while ((ta + 1) * nt - (ta + 1) * ta / 2 <= t) ++ta;
-    const int tb = ta + (t - (ta * nt - ta * (ta - 1) / 2));
-    const int a0 = 4 * ta, b0 = 4 * tb;
-    double acc[4][4];
-#pragma unroll
-    for (int x = 0; x < 4; ++x)
-#pragma unroll
-      for (int y = 0; y < 4; ++y) acc[x][y] = 0.0;
-    for (int i = 0; i < k; ++i) {
-      const double* row = sT + i * ldT;
-      const double2 wa0 = *(const double2*)(row + a0), wa1 = *(const double2*)(row + a0 + 2);
-      const double2 wb0 = *(const double2*)(row + b0), wb1 = *(const double2*)(row + b0 + 2);
-      const double wa[4] = {wa0.x, wa0.y, wa1.x, wa1.y}, wb[4] = {wb0.x, wb0.y, wb1.x, wb1.y};
-#pragma unroll
-      for (int x = 0; x < 4; ++x)
-#pragma unroll
-        for (int y = 0; y < 4; ++y) acc[x][y] += wa[x] * wb[y];
-    }
-#pragma unroll
-    for (int x = 0; x < 4; ++x)
-#pragma unroll
-      for (int y = 0; y < 4; ++y) {
-        const int a = a0 + x, b = b0 + y;
-        if (a < n && b < n && b >= a) {
-          const double v = P[(size_t)a * ld + b] - acc[x][y];
-          P[(size_t)a * ld + b] = v;
-          P[(size_t)b * ld + a] = v;
-        }
-      }
-  }
-}
-
 // P <- P - W^T W.   grid (ceil(nmax/32), ceil(nmax/32), F); upper tiles only, mirrored.
 __device__ void k_upd_downdate_body(const Dev& d, int f, int bx, int by) {
   const int k = d.k_rows[f];
@@ -806,28 +671,9 @@ void launch_qr_dense(const Dev& d, int filter, int mp_dense, cudaStream_t st) {
   KLAUNCH(d, KID_QR, st, (k_qr_dense<<<1, UT, 0, st>>>(d, filter, mp_dense)));
 }
 
-size_t upd_small_smem_bytes(int nmax, int K, int NA) {
-  const size_t dbl = (size_t)K * (NA + 1) + (size_t)K * ((nmax + 2) & ~1) + (size_t)K * (K + 1) + nmax + (NA + 1) / 2 + 2;
-  return dbl * sizeof(double);
-}
-
 void launch_update(const Dev& d, int stage, cudaStream_t st) {
   (void)stage;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(k_upd_small<UPD_SMALL_K, UPD_SMALL_NA, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-    cudaFuncSetAttribute(k_upd_small<UPD_MED_K, UPD_MED_NA, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-    cudaFuncSetAttribute(k_upd_small<UPD_TINY_K, UPD_TINY_NA, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-    attr_set = true;
-  }
   launch_update_dmma(d, st);
-  KLAUNCH(d, KID_UPD_TINY, st,
-          (k_upd_small<UPD_TINY_K, UPD_TINY_NA, 4><<<d.F, UT, upd_small_smem_bytes(d.nmax, UPD_TINY_K, UPD_TINY_NA), st>>>(d)));
-  KLAUNCH(d, KID_UPD_SMALL, st,
-          (k_upd_small<UPD_SMALL_K, UPD_SMALL_NA, 1><<<d.F, UT, upd_small_smem_bytes(d.nmax, UPD_SMALL_K, UPD_SMALL_NA), st>>>(d)));
-  if (d.upd_med_ok)
-    KLAUNCH(d, KID_UPD_MED, st,
-            (k_upd_small<UPD_MED_K, UPD_MED_NA, 3><<<d.F, UT, upd_small_smem_bytes(d.nmax, UPD_MED_K, UPD_MED_NA), st>>>(d)));
   // tiled path for the filters k_plan_stack queued in wl_upd_big (none in the common case: the grids exit at once)
   const int tn = (d.nmax + 1 + 31) / 32, tk = (d.Tk + 31) / 32, tp = (d.nmax + 31) / 32;
   const int fz = d.F < 32 ? d.F : 32;

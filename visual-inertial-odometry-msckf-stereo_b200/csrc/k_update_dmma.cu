@@ -109,14 +109,16 @@ __global__ void __launch_bounds__(DT, 2) k_upd_dmma(Dev d, int cls) {
   for (int w = blockIdx.x; w < nlist; w += gridDim.x) {
     const int f = wl[w];
     const int k = d.k_rows[f], na = d.n_act[f], mp = d.m_pad[f], n = NI + 6 * d.ncam[f], ld = d.ld;
-    const int kp = (k + 7) & ~7, nkt = kp >> 3, nks = kp >> 2;
+    const int kp = (k + 7) & ~7, nkt = kp >> 3, nkk = kp >> 2;     // rows of H_thin: 8-row tiles, 4-deep steps over the rows
+    const int nks = ((na + 7) & ~7) >> 2;                          // 4-deep steps over the active columns
+    const bool tri = d.m_rows[f] > na;                             // compressed: H_thin = R is upper triangular (k = n_a)
     const int ntn = (n + 7) >> 3;                // column tiles of the state part
     const int nct = (n + 8) >> 3;                // column tiles including the residual column n
     const double* A = d.A + (size_t)f * d.A_elems;
     double* P = d.P + (size_t)f * ld * ld;
     const int* cm = d.colmap + (size_t)f * d.nmax;
 
-    // ---- stage R (upper triangle, zero elsewhere), r and the column map
+    // ---- stage H_thin (zero padded), r and the column map
     for (int e = tid; e < KC * LDX; e += DT) sX[e] = 0.0;
     for (int e = tid; e < kp * (nct * 8 - n); e += DT) {
       const int i = e / (nct * 8 - n), c = n + e - i * (nct * 8 - n);
@@ -127,7 +129,7 @@ __global__ void __launch_bounds__(DT, 2) k_upd_dmma(Dev d, int cls) {
     __syncthreads();
     for (int e = tid; e < k * na; e += DT) {
       const int c = e / k, i = e - c * k;
-      if (c >= i) sX[i * LDX + c] = A[(size_t)c * mp + i];
+      sX[i * LDX + c] = A[(size_t)c * mp + i];
     }
     __syncthreads();
 
@@ -146,8 +148,8 @@ __global__ void __launch_bounds__(DT, 2) k_upd_dmma(Dev d, int cls) {
           double c0 = 0.0, c1 = 0.0;
           const double* arow = sX + (8 * it + g) * LDX + tg;
 #pragma unroll
-          for (int ks = 2 * it; ks < KC / 4; ++ks)
-            if (ks < nks) dmma884(c0, c1, arow[4 * ks], bf[ks]);
+          for (int ks = 0; ks < KC / 4; ++ks)
+            if (ks < nks && (!tri || ks >= 2 * it)) dmma884(c0, c1, arow[4 * ks], bf[ks]);
           const int col = 8 * jt + 2 * tg;
           double* trow = sT + (8 * it + g) * ldT;
           if (col < n) trow[col] = c0;
@@ -169,7 +171,7 @@ __global__ void __launch_bounds__(DT, 2) k_upd_dmma(Dev d, int cls) {
         tri_decode(t, it, jt);
         const double* trow = sT + (8 * it + g) * ldT;
         const double* brow = sX + (8 * jt + g) * LDX + tg;
-        for (int ks = 2 * jt; ks < nks; ++ks) dmma884(sv0[q], sv1[q], trow[scm[4 * ks + tg]], brow[4 * ks]);
+        for (int ks = tri ? 2 * jt : 0; ks < nks; ++ks) dmma884(sv0[q], sv1[q], trow[scm[4 * ks + tg]], brow[4 * ks]);
       }
     }
     __syncthreads();
@@ -284,7 +286,7 @@ __global__ void __launch_bounds__(DT, 2) k_upd_dmma(Dev d, int cls) {
         }
       const double* wa = sT + tg * ldT + a0 + g;
       const double* wb = sT + tg * ldT + b0 + g;
-      for (int ks = 0; ks < nks; ++ks) {
+      for (int ks = 0; ks < nkk; ++ks) {
         const double fa0 = wa[0], fa1 = wa[8], fb0 = wb[0], fb1 = wb[8];
         dmma884(acc[0][0][0], acc[0][0][1], fa0, fb0);
         dmma884(acc[0][1][0], acc[0][1][1], fa0, fb1);

@@ -37,8 +37,6 @@ constexpr int QR_WARP_CLASSES = 2;
 constexpr int JAC_CLASSES = 4;
 __host__ __device__ inline int jac_class(int M) { return M <= 2 ? 0 : (M == 3 ? 1 : (M == 4 ? 2 : 3)); }
 __host__ __device__ inline int jac_class_maxM(int c) { return c == 0 ? 2 : (c == 1 ? 3 : (c == 2 ? 4 : 6)); }
-// the fused single-CTA update handles compressed measurements of at most this many rows / active columns
-constexpr int UPD_TINY_K = 16, UPD_TINY_NA = 24, UPD_SMALL_K = 32, UPD_SMALL_NA = 48, UPD_MED_K = 64, UPD_MED_NA = 72;
 // landmarks with at most this many observations go through the warp-per-landmark Jacobian kernel
 constexpr int JAC_SMALL_M = 6;
 
@@ -125,9 +123,7 @@ struct Dev {
   int rowmap_cap;
   int* qr_cls;             // [F] compression class of this stage's stacked Jacobian (-1: nothing to do)
   int* wl_qr;              // [QR_WARP_CLASSES][F] filters of the warp-QR classes
-  int* upd_path;           // [F] 0 = no update, 4 / 1 / 3 = fused kernel (tiny / small / medium), 2 = tiled kernels (queued in wl_upd_big), 5 / 6 = DMMA kernel (k <= 16 / k <= 64)
-  int upd_small_ok;
-  int upd_med_ok;          // the medium fused kernel fits shared memory for this window size
+  int* upd_path;           // [F] 0 = no update, 2 = tiled kernels (queued in wl_upd_big), 5 / 6 = DMMA kernel (k <= 16 / k <= 64)
   int* wl_upd_big;         // [F]
   int* wl_upd_dmma;        // [2][F] filters of the tensor-pipe update classes (k <= 16, k <= 64)
   int upd_dmma_ok[2];      // class fits shared memory for this window size

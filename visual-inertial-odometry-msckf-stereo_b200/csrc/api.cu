@@ -14,7 +14,7 @@ using namespace msckf;
 namespace msckf {
 const char* const kKernelNames[KID_COUNT] = {
     "k_propagate", "k_augment", "k_cam_prepare", "k_observe", "k_classify_lost", "k_prune_select", "k_triangulate", "k_plan_items",
-    "k_jacobian_gate", "k_jacobian_big", "k_plan_stack", "k_qr", "k_qr_warp", "k_qr_warp1", "k_upd_dmma16", "k_upd_dmma64", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
+    "k_jacobian_gate", "k_jacobian_big", "k_plan_stack", "k_qr", "k_qr_d16", "k_qr_d32", "k_qr_d48", "k_qr_d64", "k_upd_dmma16", "k_upd_dmma64", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
     "k_upd_downdate", "k_remove_cams", "k_finish_frame", "k_reset", "misc"};
 
 void KTimer::begin(int id, cudaStream_t st) {
@@ -310,7 +310,7 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   if (d.qr_scratch_stride) DA(d.qr_scratch, F * (size_t)d.qr_scratch_stride);
   DA(d.Adense, (size_t)d.Adense_elems);
   DA(d.A, F * (size_t)d.A_elems); DA(d.m_rows, F); DA(d.m_pad, F); DA(d.n_act, F); DA(d.k_rows, F); DA(d.colmap, F * (size_t)d.nmax); DA(d.upd_path, F); DA(d.wl_upd_big, F); DA(d.wl_upd_dmma, 2 * F);
-  DA(d.rowmap, F * (size_t)d.rowmap_cap); DA(d.qr_cls, F); DA(d.wl_qr, (size_t)QR_WARP_CLASSES * F);
+  DA(d.rowmap, F * (size_t)d.rowmap_cap); DA(d.qr_cls, F); DA(d.wl_qr, (size_t)QR_DMMA_CLASSES * F);
   DA(d.T, F * (size_t)d.Tk * Tld(d)); DA(d.S, F * (size_t)d.Tk * d.Tk); DA(d.dx, F * (size_t)d.nmax);
   DA(d.log_id, 2 * F * Fc); DA(d.log_status, 2 * F * Fc); DA(d.log_gamma, 2 * F * Fc); DA(d.log_dof, 2 * F * Fc);
   DA(d.log_n, 2 * F); DA(d.log_upd, 2 * F * 2); DA(d.log_rm, F * 2);
@@ -592,7 +592,7 @@ static void enqueue_lost_stage(msckf_ctx* ctx) {
   launch_plan_items(d, 0, ctx->st);
   launch_jacobian_gate(d, 0xE, 1, 0, ctx->st);            // lost landmarks have at least three observations
   launch_plan_stack(d, 0, ctx->st);
-  launch_qr_warp(d, ctx->st);
+  launch_qr_dmma(d, ctx->st);
   launch_qr_build(d, ctx->st);
   launch_update(d, 0, ctx->st);
 }
@@ -605,7 +605,7 @@ static void enqueue_prune_stage(msckf_ctx* ctx) {
   launch_plan_items(d, 1, ctx->st);
   launch_jacobian_gate(d, 0x1, 0, 0, ctx->st);            // the pruning update always involves exactly two camera states
   launch_plan_stack(d, 1, ctx->st);
-  launch_qr_warp(d, ctx->st);
+  launch_qr_dmma(d, ctx->st);
   launch_qr_build(d, ctx->st);
   launch_update(d, 1, ctx->st);
   launch_remove_cams(d, ctx->st);

@@ -101,34 +101,170 @@ __device__ __forceinline__ void qd_panel(double* sR, double* sC, double* sTm, in
 #pragma unroll
     for (int c = 0; c < 8; c += 2) *(double2*)(row + c) = make_double2(x[t][c], x[t][c + 1]);
   }
-  // T (8 x 8 upper): T(i,i) = tau_i, T(i,j) = -tau_j sum_{l=i}^{j-1} T(i,l) (v_l . v_j); lane i < 8 owns row i
-  double trow[8];
-  const int ri = lane & 7;
+  // T (8 x 8 upper): T(i,i) = tau_i, T(i,j) = -tau_j sum_{l=i}^{j-1} T(i,l) (v_l . v_j); lane i < 8 owns row i.
+  // All 28 dot products of V^T V go through one batched warp reduction.
+  double gm[8][8];
 #pragma unroll
-  for (int l = 0; l < 8; ++l) trow[l] = 0.0;
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    double gcol[8];
+  for (int j = 1; j < 8; ++j)
 #pragma unroll
     for (int l = 0; l < j; ++l) {
       double a = 0.0;
 #pragma unroll
       for (int t = 0; t < 4; ++t) a += x[t][l] * x[t][j];
-      gcol[l] = a;
+      gm[l][j] = a;
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
+  for (int o = 16; o > 0; o >>= 1) {
 #pragma unroll
-      for (int l = 0; l < j; ++l) gcol[l] += __shfl_xor_sync(QFULL, gcol[l], o);
-    }
+    for (int j = 1; j < 8; ++j)
+#pragma unroll
+      for (int l = 0; l < j; ++l) gm[l][j] += __shfl_xor_sync(QFULL, gm[l][j], o);
+  }
+  double trow[8];
+  const int ri = lane & 7;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
     double acc = 0.0;
 #pragma unroll
-    for (int l = 0; l < j; ++l) acc += trow[l] * gcol[l];
-    trow[j] = (ri == j) ? tau[j] : ((ri < j && j < nrefl) ? -tau[j] * acc : 0.0);
+    for (int l = 0; l < j; ++l) acc += trow[l] * gm[l][j];
+    trow[j] = (ri == j) ? tau[j] : ((ri < j) ? -tau[j] * acc : 0.0);
   }
   if (lane < 8) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) sTm[ri * QD_LDL + j] = trow[j];
+  }
+}
+
+
+__global__ void __launch_bounds__(QD_T, 2) k_qr_dmma(Dev d, int cls, int cap) {
+  extern __shared__ __align__(16) double qs[];
+  const int ldr = cap + 4;
+  double* sR = qs;                                   // [cap][ldr]
+  double* sC = sR + cap * ldr;                       // [QD_CR][ldr]
+  double* sTm = sC + QD_CR * ldr;                    // [8][QD_LDL]
+  double* sY = sTm + 8 * QD_LDL;                     // [8 warps][8][QD_LDL]
+  int* camcol = (int*)(sY + 8 * 8 * QD_LDL);         // [64] logical camera -> active column block
+  __shared__ int s_c0;
+  const int tid = threadIdx.x, nthr = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
+  const int g = lane >> 2, tg = lane & 3;
+  const int nlist = (int)d.stage_ctr[SC_NQR + cls];
+  const int* wl = d.wl_qr + (size_t)cls * d.F;
+  double* sYw = sY + warp * 8 * QD_LDL;
+
+  for (int w = blockIdx.x; w < nlist; w += gridDim.x) {
+    const int f = wl[w];
+    const int m = d.m_rows[f], na = d.n_act[f], nc = na + 1, mp = d.m_pad[f];
+    const int nct = (nc + 7) >> 3, npan = (na + 7) >> 3;
+    const size_t fb = (size_t)f * d.Fcap;
+    const int* cm = d.colmap + (size_t)f * d.nmax;
+    const int* rmap = d.rowmap + (size_t)f * d.rowmap_cap;
+    for (int e = tid; e < cap * ldr; e += nthr) sR[e] = 0.0;
+    for (int c = tid; c < 64; c += nthr) camcol[c] = -1;
+    __syncthreads();
+    for (int b = tid; b < na / 6; b += nthr) camcol[(cm[6 * b] - NI) / 6] = b;
+
+    for (int r0 = 0; r0 < m; r0 += QD_CR) {
+      const int cr = min(QD_CR, m - r0);
+      const int crk = (cr + 3) >> 2, crt = (cr + 7) >> 3;
+      // ---- expand the rows of this chunk (zero fill, then the 6-column blocks of every observation and the residual)
+      for (int e = tid; e < QD_CR * ldr / 2; e += nthr) ((double2*)sC)[e] = make_double2(0.0, 0.0);
+      if (tid == 0) s_c0 = na;
+      __syncthreads();
+      for (int i = tid; i < cr; i += nthr) {
+        const int rm = rmap[r0 + i];
+        const int kk = rm >> 8, li = rm & 255;
+        const int rows = d.item_rows[fb + kk], M = (rows + 3) / 4;
+        unsigned long long lmask = d.item_lmask[fb + kk];
+        const double* rec = d.pool + d.item_off[fb + kk] + (size_t)li * (6 * M + 1);
+        double* row = sC + i * ldr;
+        const int first = camcol[__ffsll((long long)lmask) - 1];
+        for (int a = 0; a < M; ++a) {
+          const int cam = __ffsll((long long)lmask) - 1;
+          lmask &= lmask - 1;
+          double* dst = row + 6 * camcol[cam];
+#pragma unroll
+          for (int e = 0; e < 6; ++e) dst[e] = rec[6 * a + e];
+        }
+        row[na] = rec[6 * M];
+        atomicMin(&s_c0, 6 * first);
+      }
+      __syncthreads();
+      const int pb0 = s_c0 >> 3;                      // columns before the chunk's first non-zero column need no elimination
+      for (int pb = pb0; pb < npan; ++pb) {
+        const int j0 = 8 * pb;
+        if (warp == 0) qd_panel(sR, sC, sTm, ldr, j0, min(8, na - j0), lane);
+        __syncthreads();
+        // ---- trailing tiles: one 8-column tile per warp
+        for (int ct = pb + 1 + warp; ct < nct; ct += nwarp) {
+          const int c0 = 8 * ct;
+          double* rp = sR + (j0 + g) * ldr + c0 + 2 * tg;
+          const double r_old0 = rp[0], r_old1 = rp[1];
+          double w0[4] = {r_old0, 0.0, 0.0, 0.0}, w1[4] = {r_old1, 0.0, 0.0, 0.0};
+          const double* va = sC + tg * ldr + j0 + g;
+          const double* cb = sC + tg * ldr + c0 + g;
+          int ks = 0;
+          for (; ks + 4 <= crk; ks += 4) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) qd_dmma(w0[u], w1[u], va[(4 * (ks + u)) * ldr], cb[(4 * (ks + u)) * ldr]);
+          }
+          for (; ks < crk; ++ks) qd_dmma(w0[0], w1[0], va[4 * ks * ldr], cb[4 * ks * ldr]);
+          const double ww0 = (w0[0] + w0[1]) + (w0[2] + w0[3]), ww1 = (w1[0] + w1[1]) + (w1[2] + w1[3]);
+          // Y = T^T W
+          sYw[g * QD_LDL + 2 * tg] = ww0;
+          sYw[g * QD_LDL + 2 * tg + 1] = ww1;
+          __syncwarp();
+          const double wb0 = sYw[tg * QD_LDL + g], wb1 = sYw[(4 + tg) * QD_LDL + g];
+          const double ta0 = sTm[tg * QD_LDL + g], ta1 = sTm[(4 + tg) * QD_LDL + g];
+          double y0 = 0.0, y1 = 0.0;
+          qd_dmma(y0, y1, ta0, wb0);
+          qd_dmma(y0, y1, ta1, wb1);
+          rp[0] = r_old0 - y0;
+          rp[1] = r_old1 - y1;
+          __syncwarp();
+          sYw[g * QD_LDL + 2 * tg] = y0;
+          sYw[g * QD_LDL + 2 * tg + 1] = y1;
+          __syncwarp();
+          const double yb0 = sYw[tg * QD_LDL + g], yb1 = sYw[(4 + tg) * QD_LDL + g];
+          // C(:, tile) -= V Y
+          for (int rt = 0; rt < crt; ++rt) {
+            const double* vr = sC + (8 * rt + g) * ldr + j0 + tg;
+            double2* cp = (double2*)(sC + (8 * rt + g) * ldr + c0 + 2 * tg);
+            double2 cv = *cp;
+            qd_dmma(cv.x, cv.y, -vr[0], yb0);
+            qd_dmma(cv.x, cv.y, -vr[4], yb1);
+            *cp = cv;
+          }
+          __syncwarp();
+        }
+        __syncthreads();
+      }
+    }
+    // ---- H_thin = R (k = n_a rows), r_thin = first n_a entries of Q^T r
+    double* A = d.A + (size_t)f * d.A_elems;
+    for (int e = tid; e < na * nc; e += nthr) {
+      const int i = e % na, c = e / na;
+      A[(size_t)c * mp + i] = (c >= i) ? sR[i * ldr + c] : 0.0;
+    }
+    __syncthreads();
+  }
+}
+
+void launch_qr_dmma(const Dev& d, cudaStream_t st) {
+  static bool attr_set = false;
+  static int sms = 0;
+  if (!attr_set) {
+    cudaFuncSetAttribute(k_qr_dmma, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    sms = sm_count();
+    attr_set = true;
+  }
+  const int caps[QR_DMMA_CLASSES] = {16, 32, 48, 64};
+  const int thr[QR_DMMA_CLASSES] = {64, 128, 128, 256};
+  const int kid[QR_DMMA_CLASSES] = {KID_QR_D16, KID_QR_D32, KID_QR_D48, KID_QR_D64};
+  for (int c = 0; c < QR_DMMA_CLASSES; ++c) {
+    const size_t sm = qr_dmma_smem_bytes(caps[c]);
+    int per_sm = (int)std::min<size_t>((224 * 1024) / (sm + 1024), 512 / thr[c]);   // 128 registers per thread
+    per_sm = std::max(1, per_sm);
+    KLAUNCH(d, kid[c], st, (k_qr_dmma<<<std::min(d.F, sms * per_sm), thr[c], sm, st>>>(d, c, caps[c])));
   }
 }
 

@@ -451,8 +451,8 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
     const int kr = (m > na) ? na : m;
     int qcls = -1;
     if (m > 0) {
-      qcls = (m > na && na <= 12) ? 0 : ((m > na && na <= 24) ? 1 : 2);
-      if (qcls < QR_WARP_CLASSES) d.wl_qr[(size_t)qcls * d.F + atomicAdd(d.stage_ctr + SC_NQR + qcls, 1ull)] = f;
+      qcls = (m <= na || na + 1 > 64) ? QR_DMMA_CLASSES : (na + 1 <= 16 ? 0 : (na + 1 <= 32 ? 1 : (na + 1 <= 48 ? 2 : 3)));
+      if (qcls < QR_DMMA_CLASSES) d.wl_qr[(size_t)qcls * d.F + atomicAdd(d.stage_ctr + SC_NQR + qcls, 1ull)] = f;
     }
     d.qr_cls[f] = qcls;
     d.m_rows[f] = m;

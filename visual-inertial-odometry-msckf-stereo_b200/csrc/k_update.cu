@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(QT) k_qr_build(Dev d, int smem_doubles) {
   extern __shared__ double sm[];
   const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int m = d.m_rows[f];
-  if (m == 0 || d.qr_cls[f] != 2) return;              // the narrow cases go through k_qr_warp
+  if (m == 0 || d.qr_cls[f] != QR_DMMA_CLASSES) return;   // compressed updates of up to 64 columns go through k_qr_dmma
   const int na = d.n_act[f], nc = na + 1, k = d.k_rows[f], mp = d.m_pad[f], ni = d.nitem[f];
   const bool do_qr = m > na;
   double* A = d.A + (size_t)f * d.A_elems;
@@ -188,136 +188,6 @@ __global__ void __launch_bounds__(QT) k_qr_build(Dev d, int smem_doubles) {
     const int i = e % na, c = e / na;
     A[(size_t)c * mp + i] = (c >= i) ? Rp[qr_row_off(i, na) + c - i] : 0.0;
   }
-}
-
-// ------------------------------------------------------------------ warp-level QR for narrow stacked Jacobians
-// When only a few camera states are involved (the pruning update: 12 columns, ~1000 rows; short lost tracks) the
-// stacked Jacobian is tall and skinny.  Rows live in REGISTERS, one or two per lane; a warp folds its rows into a packed
-// triangular factor R (shared memory, residual as the last column) with warp-shuffle reductions only -- no block
-// barrier in the elimination.  PARTS warps split the rows of one filter (TSQR) and warp 0 folds their factors.
-template <int NA, int RPL>
-__device__ __forceinline__ void wq_fold(double (&x)[RPL][NA + 1], double* Rp, int lane) {
-#pragma unroll
-  for (int j = 0; j < NA; ++j) {
-    double s = 0;
-#pragma unroll
-    for (int r = 0; r < RPL; ++r) s += x[r][j] * x[r][j];
-    s = warp_sum(s);
-    if (s == 0.0) continue;                               // warp-uniform
-    const int ro = j * (NA + 1) - j * (j - 1) / 2;
-    const double alpha = Rp[ro];
-    const double nrm = sqrt(alpha * alpha + s);
-    const double beta = (alpha >= 0) ? -nrm : nrm;
-    const double tau = (beta - alpha) / beta, sc = 1.0 / (alpha - beta);
-    double v[RPL];
-#pragma unroll
-    for (int r = 0; r < RPL; ++r) v[r] = x[r][j] * sc;
-#pragma unroll
-    for (int c = j + 1; c <= NA; ++c) {
-      double dot = 0;
-#pragma unroll
-      for (int r = 0; r < RPL; ++r) dot += v[r] * x[r][c];
-      dot = warp_sum(dot);
-      const double rjc = Rp[ro + c - j];
-      const double w = tau * (rjc + dot);
-      if (lane == 0) Rp[ro + c - j] = rjc - w;
-#pragma unroll
-      for (int r = 0; r < RPL; ++r) x[r][c] -= w * v[r];
-    }
-    if (lane == 0) Rp[ro] = beta;
-    __syncwarp();
-  }
-}
-
-constexpr int WQ_WARPS = 4;
-template <int NA, int RPL, int PARTS>
-__global__ void __launch_bounds__(WQ_WARPS * 32) k_qr_warp(Dev d, int cls) {
-  constexpr int NC = NA + 1, RSZ = NA * (NA + 1) / 2 + NA, FPC = WQ_WARPS / PARTS;    // filters per CTA
-  __shared__ double sR[WQ_WARPS][RSZ + 1];
-  __shared__ int sCam[FPC][NA / 6];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int slot = warp / PARTS, part = warp - slot * PARTS;
-  const int nlist = (int)d.stage_ctr[SC_NQR + cls];
-  const int* wl = d.wl_qr + (size_t)cls * d.F;
-  double* Rp = sR[warp];
-  for (int w0 = blockIdx.x * FPC; w0 < nlist; w0 += gridDim.x * FPC) {
-    const int w = w0 + slot;
-    const bool live = w < nlist;
-    const int f = live ? wl[w] : 0;
-    const int m = live ? d.m_rows[f] : 0, na = live ? d.n_act[f] : 0, mp = live ? d.m_pad[f] : 4;
-    const size_t fb = (size_t)f * d.Fcap;
-    const int* cm = d.colmap + (size_t)f * d.nmax;
-    if (live && part == 0 && lane < na / 6) sCam[slot][lane] = (cm[6 * lane] - NI) / 6;
-    for (int e = lane; e < RSZ; e += 32) Rp[e] = 0.0;
-    if (PARTS > 1) __syncthreads(); else __syncwarp();
-    // rows of this part, in chunks of 32 * RPL
-    const int per = ((m + PARTS - 1) / PARTS + 32 * RPL - 1) / (32 * RPL) * (32 * RPL);
-    const int r_begin = part * per, r_end = min(m, r_begin + per);
-    const int* rmap = d.rowmap + (size_t)f * d.rowmap_cap;
-    for (int r0 = r_begin; r0 < r_end; r0 += 32 * RPL) {
-      double x[RPL][NC];
-#pragma unroll
-      for (int r = 0; r < RPL; ++r) {
-        const int g = r0 + lane + 32 * r;
-        if (g < r_end) {
-          const int rm = rmap[g];
-          const int kk = rm >> 8, li = rm & 255;
-          const int rows = d.item_rows[fb + kk], M = (rows + 3) / 4, ldr = 6 * M + 1;
-          const unsigned long long lmask = d.item_lmask[fb + kk];
-          const double* rec = d.pool + d.item_off[fb + kk] + (size_t)li * ldr;
-#pragma unroll
-          for (int b = 0; b < NA / 6; ++b) {
-            const int cam = (6 * b < na) ? sCam[slot][b] : 0;
-            const bool on = (6 * b < na) && ((lmask >> cam) & 1ull);
-            const int a = __popcll(lmask & ((1ull << cam) - 1ull));
-#pragma unroll
-            for (int e = 0; e < 6; ++e) x[r][6 * b + e] = on ? rec[6 * a + e] : 0.0;
-          }
-          x[r][NA] = rec[6 * M];
-        } else {
-#pragma unroll
-          for (int c = 0; c < NC; ++c) x[r][c] = 0.0;
-        }
-      }
-      wq_fold<NA, RPL>(x, Rp, lane);
-    }
-    if (PARTS > 1) {
-      __syncthreads();
-      if (part == 0) {                                    // fold the other parts' factors: NA rows each, staircase
-        constexpr int TOT = (PARTS - 1) * NA;
-        for (int t0 = 0; t0 < TOT; t0 += 32 * RPL) {
-          double x[RPL][NC];
-#pragma unroll
-          for (int r = 0; r < RPL; ++r) {
-            const int t = t0 + lane + 32 * r;
-            const int pp = 1 + t / NA, i = t - (pp - 1) * NA;
-            const double* Rq = sR[warp + (t < TOT ? pp : 0)];
-            const int ro = i * (NA + 1) - i * (i - 1) / 2;
-#pragma unroll
-            for (int c = 0; c < NC; ++c) x[r][c] = (t < TOT && c >= i) ? Rq[ro + c - i] : 0.0;
-          }
-          wq_fold<NA, RPL>(x, Rp, lane);
-        }
-      }
-    }
-    // H_thin = R (k = n_a rows) in the active columns, r_thin = Q^T r
-    if (live && part == 0) {
-      double* A = d.A + (size_t)f * d.A_elems;
-      for (int e = lane; e < na * (na + 1); e += 32) {
-        const int i = e % na, c = e / na;                 // c == na: residual, stored at packed column NA
-        const int ro = i * (NA + 1) - i * (i - 1) / 2;
-        const int cc = (c == na) ? NA : c;
-        A[(size_t)c * mp + i] = (cc >= i) ? Rp[ro + cc - i] : 0.0;
-      }
-    }
-    if (PARTS > 1) __syncthreads(); else __syncwarp();
-  }
-}
-
-void launch_qr_warp(const Dev& d, cudaStream_t st) {
-  const int grid = std::min(d.F, sm_count() * 8);
-  KLAUNCH(d, KID_QR_WARP, st, (k_qr_warp<12, 2, 4><<<grid, WQ_WARPS * 32, 0, st>>>(d, 0)));
-  KLAUNCH(d, KID_QR_WARP1, st, (k_qr_warp<24, 1, 1><<<std::min((d.F + 3) / 4, sm_count() * 8), WQ_WARPS * 32, 0, st>>>(d, 1)));
 }
 
 int qr_smem_doubles_for(int Nmax) {

@@ -30,9 +30,9 @@ constexpr unsigned ERRBIT_NOT_SPD = 8u;
 constexpr unsigned ERRBIT_CAM_CAP = 16u;
 
 // per-stage device counters (one memset per stage): pool bump pointer and work-list lengths
-constexpr int SC_POOL = 0, SC_NTRI = 1, SC_NJAC_BIG = 2, SC_NUPD_BIG = 3, SC_NJAC_SMALL = 4 /* .. 7: one per size class */, SC_NQR = 8 /* .. 9: warp-QR classes */, SC_NUPD_DMMA = 10 /* .. 11: tensor-pipe update classes */, SC_COUNT = 16;
-// stacked-Jacobian compression classes: 0 = at most 12 active columns (pruning update), 1 = at most 24, 2 = general CTA kernel
-constexpr int QR_WARP_CLASSES = 2;
+constexpr int SC_POOL = 0, SC_NTRI = 1, SC_NJAC_BIG = 2, SC_NUPD_BIG = 3, SC_NJAC_SMALL = 4 /* .. 7: one per size class */, SC_NUPD_DMMA = 10 /* .. 11: tensor-pipe update classes */, SC_NQR = 12 /* .. 15: tensor-pipe QR classes */, SC_COUNT = 16;
+// stacked-Jacobian compression classes: 0..3 = compressed (m > n_a) with n_a + 1 <= 16 / 32 / 48 / 64 columns (k_qr_dmma), 4 = general CTA kernel
+constexpr int QR_DMMA_CLASSES = 4;
 // size classes of the group-per-landmark Jacobian kernel (shared memory is sized per class): M <= 2, M = 3, M = 4, M <= 6
 constexpr int JAC_CLASSES = 4;
 __host__ __device__ inline int jac_class(int M) { return M <= 2 ? 0 : (M == 3 ? 1 : (M == 4 ? 2 : 3)); }
@@ -122,7 +122,7 @@ struct Dev {
   int* rowmap;             // [F][rowmap_cap] stacked row -> (item << 8 | row inside the item's record)
   int rowmap_cap;
   int* qr_cls;             // [F] compression class of this stage's stacked Jacobian (-1: nothing to do)
-  int* wl_qr;              // [QR_WARP_CLASSES][F] filters of the warp-QR classes
+  int* wl_qr;              // [QR_DMMA_CLASSES][F] filters of the tensor-pipe QR classes
   int* upd_path;           // [F] 0 = no update, 2 = tiled kernels (queued in wl_upd_big), 5 / 6 = DMMA kernel (k <= 16 / k <= 64)
   int* wl_upd_big;         // [F]
   int* wl_upd_dmma;        // [2][F] filters of the tensor-pipe update classes (k <= 16, k <= 64)

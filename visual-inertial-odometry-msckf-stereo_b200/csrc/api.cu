@@ -84,6 +84,7 @@ struct msckf_ctx {
   float last_ms[5] = {0, 0, 0, 0, 0};
   bool frame_pending = false;
   KTimer kt;                        // launch counts / optional per-kernel event timing
+  Lanes lanes;                      // auxiliary streams for the independent launches of one step
 };
 
 #define CK(call)                                                                                   \
@@ -224,10 +225,15 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   for (auto& s : ctx->stg) CKC(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
   for (auto& evn : ctx->ev) CKC(cudaEventCreate(&evn));
   for (auto& evn : ctx->mark) CKC(cudaEventCreate(&evn));
+  for (auto& s : ctx->lanes.aux) CKC(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+  for (auto& evn : ctx->lanes.join) CKC(cudaEventCreateWithFlags(&evn, cudaEventDisableTiming));
+  CKC(cudaEventCreateWithFlags(&ctx->lanes.fork, cudaEventDisableTiming));
+  ctx->lanes.enabled = getenv("MSCKF_NO_LANES") == nullptr;
 
   Dev& d = ctx->d;
   memset(&d, 0, sizeof d);
   d.host_timer = &ctx->kt;
+  d.host_lanes = &ctx->lanes;
   d.F = cfg->n_filters;
   d.Nmax = cfg->max_cam_states;
   d.nmax = NI + 6 * d.Nmax;
@@ -353,6 +359,9 @@ void msckf_destroy(msckf_ctx* ctx) {
   for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
   ctx->kt.release();
   for (auto& e : ctx->mark) if (e) cudaEventDestroy(e);
+  for (auto& s : ctx->lanes.aux) if (s) { cudaStreamSynchronize(s); cudaStreamDestroy(s); }
+  for (auto& e : ctx->lanes.join) if (e) cudaEventDestroy(e);
+  if (ctx->lanes.fork) cudaEventDestroy(ctx->lanes.fork);
   if (ctx->h_pub) cudaFreeHost(ctx->h_pub);
   if (ctx->h_reset) cudaFreeHost(ctx->h_reset);
   if (ctx->h_err) cudaFreeHost(ctx->h_err);
@@ -592,8 +601,7 @@ static void enqueue_lost_stage(msckf_ctx* ctx) {
   launch_plan_items(d, 0, ctx->st);
   launch_jacobian_gate(d, 0xE, 1, 0, ctx->st);            // lost landmarks have at least three observations
   launch_plan_stack(d, 0, ctx->st);
-  launch_qr_dmma(d, ctx->st);
-  launch_qr_build(d, ctx->st);
+  launch_qr_all(d, ctx->st);
   launch_update(d, 0, ctx->st);
 }
 static void enqueue_prune_stage(msckf_ctx* ctx) {
@@ -605,8 +613,7 @@ static void enqueue_prune_stage(msckf_ctx* ctx) {
   launch_plan_items(d, 1, ctx->st);
   launch_jacobian_gate(d, 0x1, 0, 0, ctx->st);            // the pruning update always involves exactly two camera states
   launch_plan_stack(d, 1, ctx->st);
-  launch_qr_dmma(d, ctx->st);
-  launch_qr_build(d, ctx->st);
+  launch_qr_all(d, ctx->st);
   launch_update(d, 1, ctx->st);
   launch_remove_cams(d, ctx->st);
 }

@@ -578,11 +578,13 @@ void launch_jacobian_gate(const Dev& d, int class_mask, int with_big, int write_
     cudaFuncSetAttribute(k_jacobian_gate_big, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     attr_set = true;
   }
-  if (class_mask & 1) launch_small<8>(d, 0, write_all, st);
-  if (class_mask & 2) launch_small<16>(d, 1, write_all, st);
-  if (class_mask & 4) launch_small<32>(d, 2, write_all, st);
-  if (class_mask & 8) launch_small<32>(d, 3, write_all, st);
+  Fork fk(d, st);
+  if (class_mask & 1) launch_small<8>(d, 0, write_all, fk.lane(0));
+  if (class_mask & 2) launch_small<16>(d, 1, write_all, fk.lane(1));
+  if (class_mask & 4) launch_small<32>(d, 2, write_all, fk.lane(2));
+  if (class_mask & 8) launch_small<32>(d, 3, write_all, fk.lane(3));
   if (with_big) {
+    st = fk.lane(4);
     const int smem_doubles = d.jac_big_smem_doubles;
     KLAUNCH(d, KID_JACOBIAN_BIG, st,
             (k_jacobian_gate_big<<<d.jac_big_grid, JAC_BIG_T, (size_t)smem_doubles * sizeof(double), st>>>(d, smem_doubles, write_all)));

@@ -249,7 +249,7 @@ __global__ void __launch_bounds__(QD_T, 2) k_qr_dmma(Dev d, int cls, int cap) {
   }
 }
 
-void launch_qr_dmma(const Dev& d, cudaStream_t st) {
+void launch_qr_dmma(const Dev& d, Fork& fk) {
   static bool attr_set = false;
   static int sms = 0;
   if (!attr_set) {
@@ -264,6 +264,7 @@ void launch_qr_dmma(const Dev& d, cudaStream_t st) {
     const size_t sm = qr_dmma_smem_bytes(caps[c]);
     int per_sm = (int)std::min<size_t>((224 * 1024) / (sm + 1024), 512 / thr[c]);   // 128 registers per thread
     per_sm = std::max(1, per_sm);
+    cudaStream_t st = fk.lane(c);
     KLAUNCH(d, kid[c], st, (k_qr_dmma<<<std::min(d.F, sms * per_sm), thr[c], sm, st>>>(d, c, caps[c])));
   }
 }

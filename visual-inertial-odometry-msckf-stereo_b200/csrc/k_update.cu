@@ -537,13 +537,20 @@ void launch_qr_build(const Dev& d, cudaStream_t st) {
   }
   KLAUNCH(d, KID_QR, st, (k_qr_build<<<d.F, QT, (size_t)d.qr_smem_doubles * sizeof(double), st>>>(d, d.qr_smem_doubles)));
 }
+void launch_qr_all(const Dev& d, cudaStream_t st) {
+  Fork fk(d, st);
+  launch_qr_dmma(d, fk);
+  launch_qr_build(d, fk.lane(4));
+}
 void launch_qr_dense(const Dev& d, int filter, int mp_dense, cudaStream_t st) {
   KLAUNCH(d, KID_QR, st, (k_qr_dense<<<1, UT, 0, st>>>(d, filter, mp_dense)));
 }
 
 void launch_update(const Dev& d, int stage, cudaStream_t st) {
   (void)stage;
-  launch_update_dmma(d, st);
+  Fork fk(d, st);
+  launch_update_dmma(d, fk);
+  st = fk.lane(2);
   // tiled path for the filters k_plan_stack queued in wl_upd_big (none in the common case: the grids exit at once)
   const int tn = (d.nmax + 1 + 31) / 32, tk = (d.Tk + 31) / 32, tp = (d.nmax + 31) / 32;
   const int fz = d.F < 32 ? d.F : 32;

@@ -316,7 +316,7 @@ __global__ void __launch_bounds__(DT, 2) k_upd_dmma(Dev d, int cls) {
 }
 
 static int g_sm_count_dmma = 0;
-void launch_update_dmma(const Dev& d, cudaStream_t st) {
+void launch_update_dmma(const Dev& d, Fork& fk) {
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(k_upd_dmma<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
@@ -325,11 +325,13 @@ void launch_update_dmma(const Dev& d, cudaStream_t st) {
     attr_set = true;
   }
   if (d.upd_dmma_ok[0]) {
+    cudaStream_t st = fk.lane(1);
     const size_t sm = upd_dmma_smem_bytes(d.nmax, 16);
     const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (224 * 1024) / (sm + 1024)));
     KLAUNCH(d, KID_UPD_DMMA16, st, (k_upd_dmma<16><<<std::min(d.F, g_sm_count_dmma * per_sm), DT, sm, st>>>(d, 0)));
   }
   if (d.upd_dmma_ok[1]) {
+    cudaStream_t st = fk.lane(0);
     const size_t sm = upd_dmma_smem_bytes(d.nmax, 64);
     const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(2, (224 * 1024) / (sm + 1024)));
     KLAUNCH(d, KID_UPD_DMMA64, st, (k_upd_dmma<64><<<std::min(d.F, g_sm_count_dmma * per_sm), DT, sm, st>>>(d, 1)));

@@ -38,6 +38,43 @@ struct KTimer {
     if (kt_) kt_->end((st));                            \
   } while (0)
 
+// Independent launches of one step (the size classes of the Jacobian, QR and update kernels work on disjoint
+// landmarks / filters) are spread over auxiliary streams of the context and joined back into its main stream.
+constexpr int N_AUX = 4;
+struct Lanes {
+  cudaStream_t aux[N_AUX] = {};
+  cudaEvent_t fork = nullptr, join[N_AUX] = {};
+  bool enabled = false;
+};
+struct Fork {
+  cudaStream_t main;
+  Lanes* L;
+  bool on;
+  unsigned used = 0;
+  Fork(const Dev& d, cudaStream_t st) : main(st), L(static_cast<Lanes*>(d.host_lanes)) {
+    const KTimer* kt = static_cast<const KTimer*>(d.host_timer);
+    on = L && L->enabled && !(kt && kt->timing);          // the per-kernel event pass runs everything in order
+    if (on) cudaEventRecord(L->fork, main);
+  }
+  cudaStream_t lane(int i) {                               // lane 0 is the main stream
+    if (!on || i <= 0) return main;
+    i = (i - 1) % N_AUX;
+    if (!((used >> i) & 1u)) {
+      cudaStreamWaitEvent(L->aux[i], L->fork, 0);
+      used |= 1u << i;
+    }
+    return L->aux[i];
+  }
+  ~Fork() {
+    if (!on) return;
+    for (int i = 0; i < N_AUX; ++i)
+      if ((used >> i) & 1u) {
+        cudaEventRecord(L->join[i], L->aux[i]);
+        cudaStreamWaitEvent(main, L->join[i], 0);
+      }
+  }
+};
+
 // k_propagate.cu
 void launch_propagate(const Dev& d, const int* imu_off, const double* ts, const double* gyro, const double* acc, cudaStream_t st);
 void launch_augment(const Dev& d, const long long* ids, cudaStream_t st);
@@ -69,11 +106,12 @@ void launch_gate_dense(const Dev& d, int filter, const double* H, const double* 
 
 // k_update.cu
 void launch_qr_build(const Dev& d, cudaStream_t st);
-void launch_qr_dmma(const Dev& d, cudaStream_t st);        // k_qr_dmma.cu
+void launch_qr_all(const Dev& d, cudaStream_t st);         // every compression class of a stage, concurrently
+void launch_qr_dmma(const Dev& d, Fork& fk);               // k_qr_dmma.cu
 void launch_qr_dense(const Dev& d, int filter, int mp_dense, cudaStream_t st);
 int qr_smem_doubles_for(int Nmax);
 void launch_update(const Dev& d, int stage, cudaStream_t st);
-void launch_update_dmma(const Dev& d, cudaStream_t st);      // k_update_dmma.cu
+void launch_update_dmma(const Dev& d, Fork& fk);             // k_update_dmma.cu
 size_t upd_dmma_smem_bytes(int nmax, int KC);
 void launch_load_dense_H(const Dev& d, int filter, const double* H, const double* r, int m, int n_state, cudaStream_t st);
 

@@ -143,6 +143,7 @@ struct Dev {
   unsigned char* did_reset;        // [F]
   double* imu_pub;         // [F][IMU_STRIDE] snapshot for publish()
   void* host_timer;        // KTimer* of the owning context (host only; never dereferenced on the device)
+  void* host_lanes;        // Lanes* of the owning context (host only): auxiliary streams for independent launches of one step
 };
 
 __host__ __device__ inline int Tld(const Dev& d) { return d.ld + 8; }

@@ -117,6 +117,12 @@ void msckf_destroy(msckf_ctx* ctx);
 const char* msckf_last_error(const msckf_ctx* ctx);   /* ctx may be NULL for create errors */
 int msckf_sync(msckf_ctx* ctx);                       /* waits for the stream; surfaces device-side errors */
 
+/* Page-locked host memory for message buffers.  Arrays passed to msckf_feature_callback* that lie in page-locked
+ * memory (from here, cudaHostRegister or torch pin_memory) are copied to the device directly, without the
+ * intermediate copy into the library's own staging arena. */
+int msckf_host_alloc(size_t bytes, void** out);
+int msckf_host_free(void* p);
+
 /* ---- whole-filter state I/O (snapshots for parity harnesses; StateServer msckf.py:89-100) */
 int msckf_set_imu_state(msckf_ctx* ctx, int32_t filter, const double* imu /*[MSCKF_IMU_STRIDE]*/);
 int msckf_get_imu_state(msckf_ctx* ctx, int32_t filter, double* imu /*[MSCKF_IMU_STRIDE]*/);
@@ -176,8 +182,10 @@ int msckf_feature_callback(msckf_ctx* ctx, const int32_t* imu_off, const double*
                            const double* acc, const int64_t* cam_ids, const int32_t* feat_off,
                            const int64_t* ids, const double* uv, double* imu_out /*[F][MSCKF_IMU_STRIDE]*/,
                            uint8_t* did_reset /*[F]*/);
-/* Same, but only enqueues the work (inputs are copied to pinned staging before returning);
- * msckf_collect waits and fetches.  Lets a host thread prepare frame k+1 while frame k runs. */
+/* Same, but only enqueues the work; msckf_collect waits for the OLDEST frame in flight and fetches its results.
+ * Up to two frames may be in flight: the host->device copy of frame k+1 (on a copy stream) overlaps the kernels
+ * of frame k.  Pageable inputs are copied to pinned staging before returning; page-locked inputs are read by the
+ * DMA engine and must stay untouched until that frame has been collected. */
 int msckf_feature_callback_async(msckf_ctx* ctx, const int32_t* imu_off, const double* ts, const double* gyro,
                                  const double* acc, const int64_t* cam_ids, const int32_t* feat_off,
                                  const int64_t* ids, const double* uv);

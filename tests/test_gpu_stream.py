@@ -236,3 +236,51 @@ def test_batch_of_filters_vs_oracle():
         assert rel_err(Ps[k], so['P']) < TOL
         assert np.array_equal(cams[k][0], so['cam_ids'])
         assert np.array_equal(feats[k], so['map_ids'])
+
+
+def test_two_frames_in_flight_equal_sequential():
+    """msckf_feature_callback_async with two frames in flight (inputs in page-locked memory, copied on the copy stream)
+    returns, frame by frame, exactly what the blocking call returns."""
+    F, n_frames, max_cam = 4, 24, 6
+    st = synth.make_structure(n_frames, 60, structure_seed=5)
+    streams = [synth.realize(st, noise_seed=200 + k) for k in range(F)]
+    dcfg = ConfigEuRoC()
+    dcfg._vio_max_cam_state_size__ = max_cam
+    s0 = streams[0]
+
+    def frame_args(batch, f, pinned):
+        a, b = s0.imu_range_for_frame(f)
+        take = batch.select_imu(float(s0.frame_ts[f]), s0.imu_ts[a:b])
+        ts = s0.imu_ts[a:b][take]
+        K, n = len(ts), len(s0.frame_ids[f])
+        cam_id = batch.next_imu_id
+        batch.next_imu_id += 1
+        args = [(np.arange(F + 1) * K).astype(np.int32), np.tile(ts, F),
+                np.ascontiguousarray(np.stack([s.gyro[a:b][take] for s in streams])),
+                np.ascontiguousarray(np.stack([s.acc[a:b][take] for s in streams])),
+                np.full(F, cam_id, dtype=np.int64), (np.arange(F + 1) * n).astype(np.int32),
+                np.tile(s0.frame_ids[f].astype(np.int64), F), np.ascontiguousarray(np.stack([s.frame_uv[f] for s in streams]))]
+        return [capi.pinned_copy(x) for x in args] if pinned else args
+
+    outs = {}
+    for mode in ('blocking', 'pipelined'):
+        batch = MSCKFBatch(dcfg, F, feature_capacity=256)
+        try:
+            batch.initialize_gravity_and_bias(np.stack([s.gyro[:200] for s in streams]), np.stack([s.acc[:200] for s in streams]))
+            res = []
+            if mode == 'blocking':
+                for f in range(n_frames):
+                    res.append(batch.ctx.feature_callback(*frame_args(batch, f, False))[0])
+            else:
+                args = [frame_args(batch, f, True) for f in range(n_frames)]
+                batch.ctx.feature_callback_async(*args[0])
+                for f in range(1, n_frames):
+                    batch.ctx.feature_callback_async(*args[f])
+                    res.append(batch.ctx.collect()[0])
+                res.append(batch.ctx.collect()[0])
+            outs[mode] = (np.array(res), [batch.ctx.get_cov(k) for k in range(F)])
+        finally:
+            batch.close()
+    assert np.array_equal(outs['blocking'][0], outs['pipelined'][0])
+    for k in range(F):
+        assert np.array_equal(outs['blocking'][1][k], outs['pipelined'][1][k])

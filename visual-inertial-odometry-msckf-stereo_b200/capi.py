@@ -112,6 +112,8 @@ SIGNATURES = {
     'msckf_mark': [_P, _I],
     'msckf_mark_elapsed': [_P, _P],
     'msckf_version': [],
+    'msckf_host_alloc': [C.c_size_t, _P],
+    'msckf_host_free': [_P],
 }
 _RESTYPE = {'msckf_destroy': None, 'msckf_last_error': C.c_char_p, 'msckf_version': C.c_char_p,
             'msckf_kernel_name': C.c_char_p}
@@ -134,6 +136,30 @@ def load_library():
         fn.restype = _RESTYPE.get(name, C.c_int)
     _lib = lib
     return lib
+
+
+def pinned_empty(shape, dtype=np.float64):
+    """numpy array in page-locked host memory (msckf_host_alloc): message buffers built here go to the
+    device without the extra copy through the library's staging arena.  Freed when the array is collected."""
+    import weakref
+    lib = load_library()
+    dtype = np.dtype(dtype)
+    shape = (shape,) if np.isscalar(shape) else tuple(shape)
+    nbytes = int(np.prod(shape, dtype=np.int64)) * dtype.itemsize
+    p = C.c_void_p(0)
+    rc = lib.msckf_host_alloc(max(nbytes, 1), C.addressof(p))
+    if rc != 0 or not p.value:
+        raise MsckfCudaError(rc, 'msckf_host_alloc(%d bytes) failed' % nbytes)
+    buf = (C.c_char * max(nbytes, 1)).from_address(p.value)
+    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape, dtype=np.int64))).reshape(shape)
+    weakref.finalize(buf, lib.msckf_host_free, p.value)
+    return arr
+
+
+def pinned_copy(a):
+    out = pinned_empty(np.shape(a), np.asarray(a).dtype)
+    out[...] = a
+    return out
 
 
 def _ptr(a):

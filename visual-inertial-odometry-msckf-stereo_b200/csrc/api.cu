@@ -82,7 +82,11 @@ struct msckf_ctx {
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t mark[2] = {nullptr, nullptr};
   float last_ms[5] = {0, 0, 0, 0, 0};
-  bool frame_pending = false;
+  // frames enqueued by msckf_feature_callback_async and not collected yet (at most two): results land in per-slot pinned buffers
+  struct FrameSlot { double* pub = nullptr; unsigned char* reset = nullptr; unsigned* err = nullptr; cudaEvent_t done = nullptr; } slot[2];
+  int n_pending = 0, head = 0;
+  cudaStream_t copy_st = nullptr;    // H2D of the next frame's inputs overlaps the kernels of the current one
+  cudaEvent_t h2d_done = nullptr;
   KTimer kt;                        // launch counts / optional per-kernel event timing
   Lanes lanes;                      // auxiliary streams for the independent launches of one step
 };
@@ -117,16 +121,17 @@ static int dalloc(msckf_ctx* ctx, T** p, size_t count) {
   return 0;
 }
 
-static int check_device_errors(msckf_ctx* ctx) {
+static int check_device_errors(msckf_ctx* ctx, unsigned* h_err = nullptr) {
   // caller has synchronised the stream after copying d.err to h_err
-  const unsigned e = *ctx->h_err;
+  if (!h_err) h_err = ctx->h_err;
+  const unsigned e = *h_err;
   if (!e) return MSCKF_OK;
   cudaMemsetAsync(ctx->d.err, 0, 8 * sizeof(unsigned), ctx->st);
-  const unsigned* info = ctx->h_err;
+  const unsigned* info = h_err;
   char detail[160];
   snprintf(detail, sizeof detail, " [first at kernel class %u, filter %u, sizes %u %u %u]", info[1], info[2], info[3], info[4], info[5]);
   const std::string det = detail;
-  *ctx->h_err = 0;
+  *h_err = 0;
   std::string s = "device reported:";
   int rc = MSCKF_ERR_CAPACITY;
   if (e & ERRBIT_FEATURE_CAP) s += " feature_capacity exceeded;";
@@ -166,7 +171,14 @@ static int stage_begin(msckf_ctx* ctx, Packer& p) {
   return 0;
 }
 
-static int stage_commit(msckf_ctx* ctx, Packer& p) {
+// Caller memory that is already page-locked (msckf_host_alloc, cudaHostRegister, torch pin_memory) is copied to the
+// device straight from where it lies; everything else goes through the pinned arena first.
+static bool is_pinned(const void* p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeHost;
+}
+static int stage_commit(msckf_ctx* ctx, Packer& p, bool overlap = false) {
   Staging* s = p.s;
   CK(cudaEventSynchronize(s->done));       // previous user of this arena has finished
   if (p.off > s->cap) {
@@ -176,9 +188,22 @@ static int stage_commit(msckf_ctx* ctx, Packer& p) {
     CK(cudaMallocHost((void**)&s->h, s->cap));
     CK(cudaMalloc((void**)&s->d, s->cap));
   }
-  for (auto& part : p.parts)
-    if (part.second.second) memcpy(s->h + part.first, part.second.first, part.second.second);
-  if (p.off) CK(cudaMemcpyAsync(s->d, s->h, p.off, cudaMemcpyHostToDevice, ctx->st));
+  cudaStream_t cs = overlap ? ctx->copy_st : ctx->st;
+  for (auto& part : p.parts) {
+    const size_t bytes = part.second.second;
+    if (!bytes) continue;
+    const void* src = part.second.first;
+    if (bytes >= (64u << 10) && is_pinned(src)) {
+      CK(cudaMemcpyAsync(s->d + part.first, src, bytes, cudaMemcpyHostToDevice, cs));
+    } else {
+      memcpy(s->h + part.first, src, bytes);
+      CK(cudaMemcpyAsync(s->d + part.first, s->h + part.first, bytes, cudaMemcpyHostToDevice, cs));
+    }
+  }
+  if (overlap) {
+    CK(cudaEventRecord(ctx->h2d_done, cs));
+    CK(cudaStreamWaitEvent(ctx->st, ctx->h2d_done, 0));
+  }
   return 0;
 }
 static int stage_end(msckf_ctx* ctx, Packer& p) {
@@ -326,6 +351,15 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   CKC(cudaMallocHost((void**)&ctx->h_reset, F));
   CKC(cudaMallocHost((void**)&ctx->h_err, 8 * sizeof(unsigned)));
   memset(ctx->h_err, 0, 8 * sizeof(unsigned));
+  for (auto& s : ctx->slot) {
+    CKC(cudaMallocHost((void**)&s.pub, F * IMU_STRIDE * sizeof(double)));
+    CKC(cudaMallocHost((void**)&s.reset, F));
+    CKC(cudaMallocHost((void**)&s.err, 8 * sizeof(unsigned)));
+    memset(s.err, 0, 8 * sizeof(unsigned));
+    CKC(cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming));
+  }
+  CKC(cudaStreamCreateWithFlags(&ctx->copy_st, cudaStreamNonBlocking));
+  CKC(cudaEventCreateWithFlags(&ctx->h2d_done, cudaEventDisableTiming));
   // initial state: identity orientation, gravity from the caller later (set_imu_state), reset covariance
   {
     std::vector<double> imu0(F * IMU_STRIDE, 0.0);
@@ -365,8 +399,26 @@ void msckf_destroy(msckf_ctx* ctx) {
   if (ctx->h_pub) cudaFreeHost(ctx->h_pub);
   if (ctx->h_reset) cudaFreeHost(ctx->h_reset);
   if (ctx->h_err) cudaFreeHost(ctx->h_err);
+  for (auto& s : ctx->slot) {
+    if (s.pub) cudaFreeHost(s.pub);
+    if (s.reset) cudaFreeHost(s.reset);
+    if (s.err) cudaFreeHost(s.err);
+    if (s.done) cudaEventDestroy(s.done);
+  }
+  if (ctx->copy_st) { cudaStreamSynchronize(ctx->copy_st); cudaStreamDestroy(ctx->copy_st); }
+  if (ctx->h2d_done) cudaEventDestroy(ctx->h2d_done);
   if (ctx->st) cudaStreamDestroy(ctx->st);
   delete ctx;
+}
+
+int msckf_host_alloc(size_t bytes, void** out) {
+  if (!out) return MSCKF_ERR_ARG;
+  *out = nullptr;
+  return cudaMallocHost(out, bytes ? bytes : 1) == cudaSuccess ? MSCKF_OK : MSCKF_ERR_CUDA;
+}
+int msckf_host_free(void* p) {
+  if (!p) return MSCKF_OK;
+  return cudaFreeHost(p) == cudaSuccess ? MSCKF_OK : MSCKF_ERR_CUDA;
 }
 
 int msckf_sync(msckf_ctx* ctx) {
@@ -710,7 +762,7 @@ int msckf_feature_callback_async(msckf_ctx* ctx, const int32_t* imu_off, const d
                                  const int64_t* cam_ids, const int32_t* feat_off, const int64_t* ids, const double* uv) {
   if (!ctx) return MSCKF_ERR_ARG;
   ARG(imu_off && cam_ids && feat_off, "offset / id pointers");
-  ARG(!ctx->frame_pending, "previous frame not collected");
+  ARG(ctx->n_pending < 2, "two frames already in flight: collect one first");
   CK(cudaSetDevice(ctx->device));
   const Dev& d = ctx->d;
   const int F = d.F, ni = imu_off[F], nf = feat_off[F];
@@ -721,7 +773,7 @@ int msckf_feature_callback_async(msckf_ctx* ctx, const int32_t* imu_off, const d
   const size_t o2 = p.add(gyro, (size_t)ni * 3 * sizeof(double)), o3 = p.add(acc, (size_t)ni * 3 * sizeof(double));
   const size_t o4 = p.add(cam_ids, F * sizeof(int64_t)), o5 = p.add(feat_off, (F + 1) * sizeof(int));
   const size_t o6 = p.add(ids, nf * sizeof(int64_t)), o7 = p.add(uv, (size_t)nf * 4 * sizeof(double));
-  int rc = stage_commit(ctx, p);
+  int rc = stage_commit(ctx, p, true);
   if (rc) return rc;
   char* b = p.s->d;
   const bool tm = ctx->timing;
@@ -738,11 +790,13 @@ int msckf_feature_callback_async(msckf_ctx* ctx, const int32_t* imu_off, const d
   launch_finish_frame(d, 1, ctx->st);
   if (tm) cudaEventRecord(ctx->ev[5], ctx->st);
   stage_end(ctx, p);
-  CK(cudaMemcpyAsync(ctx->h_pub, d.imu_pub, (size_t)F * IMU_STRIDE * sizeof(double), cudaMemcpyDeviceToHost, ctx->st));
-  CK(cudaMemcpyAsync(ctx->h_reset, d.did_reset, F, cudaMemcpyDeviceToHost, ctx->st));
-  CK(cudaMemcpyAsync(ctx->h_err, d.err, 8 * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->st));
+  msckf_ctx::FrameSlot& fs = ctx->slot[(ctx->head + ctx->n_pending) & 1];
+  CK(cudaMemcpyAsync(fs.pub, d.imu_pub, (size_t)F * IMU_STRIDE * sizeof(double), cudaMemcpyDeviceToHost, ctx->st));
+  CK(cudaMemcpyAsync(fs.reset, d.did_reset, F, cudaMemcpyDeviceToHost, ctx->st));
+  CK(cudaMemcpyAsync(fs.err, d.err, 8 * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->st));
+  CK(cudaEventRecord(fs.done, ctx->st));
   CK(cudaGetLastError());
-  ctx->frame_pending = true;
+  ctx->n_pending += 1;
   return MSCKF_OK;
 }
 
@@ -751,7 +805,7 @@ int msckf_feature_callback_dev(msckf_ctx* ctx, const int32_t* imu_off, const dou
                                double* imu_out_dev) {
   if (!ctx) return MSCKF_ERR_ARG;
   ARG(imu_off && cam_ids && feat_off, "offset / id pointers");
-  ARG(!ctx->frame_pending, "previous frame not collected");
+  ARG(ctx->n_pending == 0, "previous frame not collected");
   CK(cudaSetDevice(ctx->device));
   const Dev& d = ctx->d;
   launch_propagate(d, imu_off, ts, gyro, acc, ctx->st);
@@ -768,15 +822,17 @@ int msckf_feature_callback_dev(msckf_ctx* ctx, const int32_t* imu_off, const dou
 
 int msckf_collect(msckf_ctx* ctx, double* imu_out, uint8_t* did_reset) {
   if (!ctx) return MSCKF_ERR_ARG;
-  ARG(ctx->frame_pending, "no frame in flight");
+  ARG(ctx->n_pending > 0, "no frame in flight");
   CK(cudaSetDevice(ctx->device));
-  ctx->frame_pending = false;
-  CK(cudaStreamSynchronize(ctx->st));
+  msckf_ctx::FrameSlot& fs = ctx->slot[ctx->head];
+  ctx->head ^= 1;
+  ctx->n_pending -= 1;
+  CK(cudaEventSynchronize(fs.done));         // the oldest frame in flight; a younger one keeps running
   CK(cudaGetLastError());
-  int rc = check_device_errors(ctx);
+  int rc = check_device_errors(ctx, fs.err);
   if (rc) return rc;
-  if (imu_out) memcpy(imu_out, ctx->h_pub, (size_t)ctx->d.F * IMU_STRIDE * sizeof(double));
-  if (did_reset) memcpy(did_reset, ctx->h_reset, ctx->d.F);
+  if (imu_out) memcpy(imu_out, fs.pub, (size_t)ctx->d.F * IMU_STRIDE * sizeof(double));
+  if (did_reset) memcpy(did_reset, fs.reset, ctx->d.F);
   if (ctx->timing) {
     for (int i = 0; i < 4; ++i) cudaEventElapsedTime(&ctx->last_ms[i], ctx->ev[i], ctx->ev[i + 1]);
     float fin = 0;

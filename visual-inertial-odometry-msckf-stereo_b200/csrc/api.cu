@@ -14,7 +14,7 @@ using namespace msckf;
 namespace msckf {
 const char* const kKernelNames[KID_COUNT] = {
     "k_propagate", "k_augment", "k_cam_prepare", "k_observe", "k_classify_lost", "k_prune_select", "k_triangulate", "k_plan_items",
-    "k_jacobian_gate", "k_jacobian_big", "k_plan_stack", "k_qr", "k_qr_d16", "k_qr_d32", "k_qr_d48", "k_qr_d64", "k_upd_dmma16", "k_upd_dmma64", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
+    "k_jacobian_gate", "k_jacobian_rows", "k_jacobian_big", "k_plan_stack", "k_qr", "k_qr_d16", "k_qr_d32", "k_qr_d48", "k_qr_d64", "k_upd_dmma16", "k_upd_dmma64", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
     "k_upd_downdate", "k_remove_cams", "k_finish_frame", "k_reset", "misc"};
 
 void KTimer::begin(int id, cudaStream_t st) {
@@ -295,6 +295,7 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
       const long long capped = std::max<long long>(d.max_rows, 5LL * d.Fcap + 8);
       d.rowmap_cap = (int)(row_cap > 0 ? std::min(all, capped) : all);
     }
+    d.jac_rows_ok = getenv("MSCKF_NO_JAC_ROWS") ? 0 : 1;
     d.upd_dmma_ok[0] = (!getenv("MSCKF_NO_DMMA") && upd_dmma_smem_bytes(d.nmax, 16) <= 220 * 1024) ? 1 : 0;
     d.upd_dmma_ok[1] = (!getenv("MSCKF_NO_DMMA") && upd_dmma_smem_bytes(d.nmax, 64) <= 220 * 1024) ? 1 : 0;      // debugging knob: route medium updates through the tiled kernels
     const long long na = 6 * M, worst = 640 + na * (na + 1) / 2 + na + 32 * (na + 1) + 64;

@@ -9,7 +9,7 @@ namespace msckf {
 // Kernel ids for launch counting and optional per-kernel event timing (msckf_kernel_times).
 enum KernelId {
   KID_PROPAGATE = 0, KID_AUGMENT, KID_CAM_PREPARE, KID_OBSERVE, KID_CLASSIFY_LOST, KID_PRUNE_SELECT, KID_TRIANGULATE, KID_PLAN_ITEMS,
-  KID_JACOBIAN_GATE, KID_JACOBIAN_BIG, KID_PLAN_STACK, KID_QR, KID_QR_D16, KID_QR_D32, KID_QR_D48, KID_QR_D64, KID_UPD_DMMA16, KID_UPD_DMMA64, KID_UPD_T, KID_UPD_S, KID_UPD_CHOL, KID_UPD_TRSM, KID_UPD_INJECT,
+  KID_JACOBIAN_GATE, KID_JACOBIAN_ROWS, KID_JACOBIAN_BIG, KID_PLAN_STACK, KID_QR, KID_QR_D16, KID_QR_D32, KID_QR_D48, KID_QR_D64, KID_UPD_DMMA16, KID_UPD_DMMA64, KID_UPD_T, KID_UPD_S, KID_UPD_CHOL, KID_UPD_TRSM, KID_UPD_INJECT,
   KID_UPD_DOWNDATE, KID_REMOVE_CAMS, KID_FINISH_FRAME, KID_RESET, KID_MISC, KID_COUNT
 };
 extern const char* const kKernelNames[KID_COUNT];
@@ -98,6 +98,7 @@ void launch_triangulate_raw(const Dev& d, int n, const int* obs_off, const doubl
 // k_jacobian.cu
 void launch_jacobian_gate(const Dev& d, int class_mask, int with_big, int write_all, cudaStream_t st);
 int sm_count();
+void launch_jacobian_rows(const Dev& d, int cls, int write_all, cudaStream_t st);   // k_jacobian_rows.cu (lane-per-row kernel, short tracks)
 void launch_cam_prepare(const Dev& d, cudaStream_t st);
 void launch_measurement_jacobian(const Dev& d, int filter, int cam_logical, int slot, double* out /*[4*6+4*3+4]*/, cudaStream_t st);
 void launch_export_item_dense(const Dev& d, int filter, double* H, double* r, int n_state, cudaStream_t st);

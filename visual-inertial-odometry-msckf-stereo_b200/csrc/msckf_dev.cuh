@@ -108,6 +108,7 @@ struct Dev {
   double* jac_scratch;     // T1 / S of long tracks that do not fit shared memory, per CTA of the big kernel
   long long jac_scratch_stride;
   int jac_big_smem_doubles, jac_big_grid;
+  int jac_rows_ok;         // short tracks go through the lane-per-row kernel (debug knob MSCKF_NO_JAC_ROWS)
   int qr_smem_doubles;     // dynamic shared memory of k_qr_build
   double* qr_scratch;      // [F][qr_scratch_stride] fallback for R + row chunk when they exceed shared memory (may be null)
   long long qr_scratch_stride;

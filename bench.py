@@ -436,8 +436,12 @@ def run_b200(args):
         dom = max(kernels, key=lambda k: kernels[k]['ms'])
         dk = kernels[dom]
         peak = dmma if dom == 'gain_update' else dfma
+        traffic = None
+        tpath = os.path.join(REPO, 'profiles', 'traffic_r1.json')
+        if os.path.exists(tpath):       # dram bytes per launch of each family, from the committed ncu --set full capture of this workload
+            traffic = json.load(open(tpath)).get('dram_bytes_per_launch', {}).get(dom)
         roofline = {'kernel': dom, 'bound': 'tensor', 'achieved': dk['gflops'] / 1e3, 'peak': peak, 'unit': 'TFLOP/s',
-                    'frac': (dk['gflops'] / 1e3) / peak if peak else None, 'traffic': None,
+                    'frac': (dk['gflops'] / 1e3) / peak if peak else None, 'traffic': traffic,
                     'peak_source': 'FP64 %s peak measured on this GPU by msckf_fp64_peak (MEASURED_PEAKS.json carries no FP64 figure); '
                                    'DFMA %.1f / DMMA %.1f TFLOP/s' % ('DMMA' if dom == 'gain_update' else 'DFMA', dfma, dmma),
                     'avg_launch_ms': dk['ms'] / dk['launches'] if dk['launches'] else None,

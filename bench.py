@@ -332,6 +332,8 @@ def run_b200(args):
         run_dev(f)
     ctx.sync()
     # bring the SM clocks up from idle before anything is timed (the first ~0.3 s after idle run at reduced clocks)
+    sampler = ClockSampler(local)      # samples every 100 ms from the clock warm-up to the end of the e2e leg: all of it is under load
+    sampler.start()
     wa = torch.randn((4096, 4096), device=dev, dtype=torch.bfloat16)
     t_spin = time.perf_counter()
     while time.perf_counter() - t_spin < 1.0:
@@ -343,8 +345,6 @@ def run_b200(args):
     ctx.sync()
     c0 = ctx.counters().sum(axis=0)
     l0 = ctx.kernel_launches()
-    sampler = ClockSampler(local)
-    sampler.start()
     barrier()
     t0 = time.perf_counter()
     ctx.mark(0)
@@ -356,7 +356,6 @@ def run_b200(args):
     torch.cuda.synchronize()
     wall_ms = (time.perf_counter() - t0) * 1e3
     barrier()
-    clocks = sampler.stop()
     c1 = ctx.counters().sum(axis=0)
     l1 = ctx.kernel_launches()
     upd_dev = float(c1[capi.CNT_FEATURE_UPDATES] - c0[capi.CNT_FEATURE_UPDATES])
@@ -387,6 +386,7 @@ def run_b200(args):
     imu_last, _ = e2e_run(first_e2e + W2, K)
     e2e_s = time.perf_counter() - t0
     assert np.isfinite(imu_last).all()
+    clocks = sampler.stop()
     barrier()
     c3 = ctx.counters().sum(axis=0)
     upd_e2e = reduce_sum(float(c3[capi.CNT_FEATURE_UPDATES] - c2[capi.CNT_FEATURE_UPDATES]))

@@ -252,6 +252,20 @@ int msckf_measurement_update(msckf_ctx* ctx, int32_t filter, const double* H, co
 /* find_redundant_cam_states (msckf.py:691-727): the two camera-state ids that would be removed. */
 int msckf_find_redundant_cam_states(msckf_ctx* ctx, int32_t filter, int64_t* cam_ids /*[2]*/);
 
+/* ---- the step in front of the filter: point undistortion of the feature message (context free) ---- */
+/* undistort_points (image.py:640-674; cv2.undistortPoints / cv2.fisheye.undistortPoints): pts_in [n][2] pixel
+ * coordinates -> pts_out [n][2].  intrinsics = fx fy cx cy; model 0 = radtan (k1 k2 p1 p2), 1 = equidistant (k1..k4);
+ * rectification [9] row-major or NULL (identity); new_intrinsics [4] or NULL (1 1 0 0: normalised coordinates).
+ * As in the reference's positional cv2.fisheye call, the equidistant model ignores the rectification. */
+int msckf_undistort_points(int32_t device, int32_t n, const double* pts_in, const double* intrinsics, int32_t model,
+                           const double* dist, const double* rectification, const double* new_intrinsics,
+                           double* pts_out);
+/* publish (image.py:406-438): raw pixel tracks of both cameras -> the rows [u0 v0 u1 v1] of the feature message,
+ * uv_out [n][4], in the layout msckf_add_observations / msckf_feature_callback take. */
+int msckf_undistort_stereo(int32_t device, int32_t n, const double* cam0_pts, const double* cam1_pts,
+                           const double* intr0, int32_t model0, const double* dist0, const double* intr1,
+                           int32_t model1, const double* dist1, double* uv_out);
+
 /* Timing of the last msckf_feature_callback*: device milliseconds per stage (CUDA events on the
  * context's stream): [0] propagate+augment [1] observe [2] remove_lost [3] prune [4] total. */
 int msckf_last_timing(msckf_ctx* ctx, float* ms /*[5]*/);

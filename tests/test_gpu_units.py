@@ -350,3 +350,31 @@ def test_errors_are_loud(units):
             dev.measurement_update(H, np.ones(3))
     finally:
         dev.close()
+
+
+@pytest.mark.gpu
+def test_undistort_points_vs_golden_and_oracle():
+    """k_undistort through the C ABI (msckf_undistort_points / msckf_undistort_stereo) against the reference's
+    recorded outputs and the oracle: FP64, 1e-12 relative (tan / division orders differ in the last bit)."""
+    from oracle import image_oracle as io
+    from msckf_b200 import image as gimg
+    from msckf_b200.config import ConfigEuRoC
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden', 'undistort.npz'))
+    for name in ['radtan_cam0', 'radtan_cam1', 'radtan_rect', 'equi_a', 'equi_rect']:
+        model = 'equidistant' if name.startswith('equi') else 'radtan'
+        out = gimg.undistort_points(g[name + '_in'], g[name + '_intr'], model, g[name + '_dist'], g[name + '_R'], g[name + '_newK'])
+        ref = g[name + '_out']
+        assert np.max(np.abs(out - ref) / (1.0 + np.abs(ref))) < 1e-12, name
+    assert gimg.undistort_points([], g['radtan_cam0_intr'], 'radtan', g['radtan_cam0_dist']) == []
+    cfg = ConfigEuRoC()
+    rng = np.random.default_rng(3)
+    n = 100003                                           # ragged tail, more points than one grid pass
+    p0 = np.stack([rng.uniform(0, 752, n), rng.uniform(0, 480, n)], axis=1)
+    p1 = p0 + rng.normal(0, 3.0, p0.shape)
+    uv = gimg.undistort_stereo(p0, p1, cfg)
+    sel = rng.choice(n, 500, replace=False)
+    ref = io.publish_measurements(p0[sel], p1[sel], cfg)
+    assert np.max(np.abs(uv[sel] - ref)) < 1e-12
+    msg = gimg.publish(1.5, np.arange(5), p0[:5], p1[:5], cfg)
+    assert msg.timestamp == 1.5 and [f.id for f in msg.vio_features] == [0, 1, 2, 3, 4]
+    assert np.allclose([[f.u0, f.v0, f.u1, f.v1] for f in msg.vio_features], uv[:5], rtol=0, atol=0)

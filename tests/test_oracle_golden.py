@@ -156,3 +156,17 @@ def test_stream_golden(stream_gold):
     assert np.all(np.abs(gam - g['gate'][:, 2]) <= 1e-8 * np.abs(g['gate'][:, 2]))
     rm = np.array(filt.log['rm_cam_ids'], dtype=np.int64)
     assert np.array_equal(rm, g['rm'][:, 1:])
+
+
+def test_image_oracle_undistort_vs_reference_golden():
+    """oracle/image_oracle.py against the reference's ImageProcessor.undistort_points (cv2 4.13 underneath), recorded by
+    tests/golden/make_golden_image.py: radtan (both EuRoC cameras, with and without rectification / new camera matrix)
+    and equidistant (including the reference's positional-argument quirk).  FP64 in, FP64 out: 1e-12 relative."""
+    from oracle import image_oracle as io
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden', 'undistort.npz'))
+    for name in ['radtan_cam0', 'radtan_cam1', 'radtan_rect', 'equi_a', 'equi_rect']:
+        model = 'equidistant' if name.startswith('equi') else 'radtan'
+        out = io.undistort_points(g[name + '_in'], g[name + '_intr'], model, g[name + '_dist'], g[name + '_R'], g[name + '_newK'])
+        ref = g[name + '_out']
+        assert np.max(np.abs(out - ref) / (1.0 + np.abs(ref))) < 1e-12, name
+    assert io.undistort_points([], g['radtan_cam0_intr'], 'radtan', g['radtan_cam0_dist']) == []

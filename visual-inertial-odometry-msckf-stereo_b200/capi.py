@@ -112,6 +112,8 @@ SIGNATURES = {
     'msckf_mark': [_P, _I],
     'msckf_mark_elapsed': [_P, _P],
     'msckf_version': [],
+    'msckf_undistort_points': [_I, _I, _P, _P, _I, _P, _P, _P, _P],
+    'msckf_undistort_stereo': [_I, _I, _P, _P, _P, _I, _P, _P, _I, _P, _P],
     'msckf_host_alloc': [C.c_size_t, _P],
     'msckf_host_free': [_P],
 }

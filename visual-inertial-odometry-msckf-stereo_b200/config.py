@@ -58,6 +58,15 @@ class ConfigEuRoC(object):
             [-0.000343393120525, -0.014090668452714, 0.999900662637729, -0.000853702503357],
             [0, 0, 0, 1.000000000000000]])
         self._vio_T_imu_body__ = np.eye(4)
+        # camera calibration of the EuRoC sensor (config.py:99-121), used by image.undistort_stereo
+        self._vio_cam0_distortion_model__ = 'radtan'
+        self._vio_cam0_distortion_coeffs__ = np.array([-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05])
+        self._vio_cam0_intrinsics__ = np.array([458.654, 457.296, 367.215, 248.375])
+        self._vio_cam0_resolution__ = np.array([752, 480])
+        self._vio_cam1_distortion_model__ = 'radtan'
+        self._vio_cam1_distortion_coeffs__ = np.array([-0.28368365, 0.07451284, -0.00010473, -3.55590700e-05])
+        self._vio_cam1_intrinsics__ = np.array([457.587, 456.134, 379.999, 255.238])
+        self._vio_cam1_resolution__ = np.array([752, 480])
         # literals of the reference, overridable here
         self.row_cap = 1500            # msckf.py:678
         self.chi2_tail = 0.05          # msckf.py:123

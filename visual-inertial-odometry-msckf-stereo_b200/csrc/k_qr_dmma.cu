@@ -40,7 +40,7 @@ size_t qr_dmma_smem_bytes(int cap) {
 
 // Panel factorisation by one warp.  x[t][c] = C(lane + 32 t, j0 + c); reflector jj is applied to the panel columns
 // c > jj only (the other tiles get the blocked update).  Returns V in x, writes R(j0 + jj, j0 + jj ..) and T.
-__device__ __forceinline__ void qd_panel(double* sR, double* sC, double* sTm, int ldr, int j0, int nrefl, int lane) {
+__device__ __forceinline__ void qd_panel(double* sR, double* sC, double* sTm, int ldr, int j0, int nrefl, bool need_T, int lane) {
   double x[4][8];
 #pragma unroll
   for (int t = 0; t < 4; ++t) {
@@ -94,6 +94,7 @@ __device__ __forceinline__ void qd_panel(double* sR, double* sC, double* sTm, in
       // not a reflector column (residual / padding): it carries data of the last panel, which has no trailing tiles
     }
   }
+  if (!need_T) return;       // last panel of the chunk: nothing reads V, T or the chunk again
   // V back to the chunk (only the reflector columns changed meaning; the others hold the updated data)
 #pragma unroll
   for (int t = 0; t < 4; ++t) {
@@ -192,7 +193,7 @@ __global__ void __launch_bounds__(QD_T, 2) k_qr_dmma(Dev d, int cls, int cap) {
       const int pb0 = s_c0 >> 3;                      // columns before the chunk's first non-zero column need no elimination
       for (int pb = pb0; pb < npan; ++pb) {
         const int j0 = 8 * pb;
-        if (warp == 0) qd_panel(sR, sC, sTm, ldr, j0, min(8, na - j0), lane);
+        if (warp == 0) qd_panel(sR, sC, sTm, ldr, j0, min(8, na - j0), pb + 1 < nct, lane);
         __syncthreads();
         // ---- trailing tiles: one 8-column tile per warp
         for (int ct = pb + 1 + warp; ct < nct; ct += nwarp) {

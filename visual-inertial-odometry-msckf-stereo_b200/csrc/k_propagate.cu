@@ -11,48 +11,47 @@ constexpr int PT = 256;   // threads per CTA for the per-filter kernels in this 
 // ------------------------------------------------------------------ RK4 state prediction (thread 0)
 // jit_utils.py:46-128, including the stale-skew quirk: the skew matrix built from the
 // normalised dq(dt) (lines 80-84) is re-used for R(dq(dt/2)) (line 94) and R(q) (line 104).
-__device__ void predict_new_state(double dt, const double* gyro, const double* acc, const double* g,
-                                  double* q, double* v, double* p) {
+// Coefficients of the two quaternion propagators of one gyro sample (jit_utils.py:62-78): dq(dt) = (cA I + sA Omega) q,
+// dq(dt/2) = (cB I + sB Omega) q.  They depend on the sample only, so the samples of a chunk compute them in parallel
+// and the sequential chain below starts from them.
+__device__ __forceinline__ void quat_step_coeffs(double dt, const double* gyro, double* out /*[4]: cA sA cB sB*/) {
   const double gn = norm3(gyro);
+  const double c1 = cos(gn * dt * 0.5), c2 = cos(gn * dt * 0.25);
+  out[0] = c1;
+  out[2] = c2;
+  if (gn > 1e-5) {
+    out[1] = sin(gn * dt * 0.5) / gn;
+    out[3] = sin(gn * dt * 0.25) / gn;
+  } else {                                              // first-order branch: cos(.) (I + Omega dt / 2)
+    out[1] = c1 * (dt * 0.5);
+    out[3] = c2 * (dt * 0.25);
+  }
+}
+__device__ void predict_new_state(double dt, const double* gyro, const double* acc, const double* cf, const double* g,
+                                  double* q, double* v, double* p) {
   const double Om[16] = {0, gyro[2], -gyro[1], gyro[0],
                          -gyro[2], 0, gyro[0], gyro[1],
                          gyro[1], -gyro[0], 0, gyro[2],
                          -gyro[0], -gyro[1], -gyro[2], 0};
   double dq[4], dq2[4];
-  if (gn > 1e-5) {
-    const double c1 = cos(gn * dt * 0.5), s1 = sin(gn * dt * 0.5) / gn;
-    const double c2 = cos(gn * dt * 0.25), s2 = sin(gn * dt * 0.25) / gn;
-    for (int i = 0; i < 4; ++i) {
-      double a = 0, b = 0;
-      for (int j = 0; j < 4; ++j) {
-        const double e = (i == j) ? 1.0 : 0.0;
-        a += (c1 * e + s1 * Om[4 * i + j]) * q[j];
-        b += (c2 * e + s2 * Om[4 * i + j]) * q[j];
-      }
-      dq[i] = a; dq2[i] = b;
-    }
-  } else {
-    const double c1 = cos(gn * dt * 0.5), c2 = cos(gn * dt * 0.25);
-    for (int i = 0; i < 4; ++i) {
-      double a = 0, b = 0;
-      for (int j = 0; j < 4; ++j) {
-        const double e = (i == j) ? 1.0 : 0.0;
-        a += (c1 * (e + Om[4 * i + j] * dt * 0.5)) * q[j];
-        b += (c2 * (e + Om[4 * i + j] * dt * 0.25)) * q[j];
-      }
-      dq[i] = a; dq2[i] = b;
-    }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    double oq = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) oq += Om[4 * i + j] * q[j];
+    dq[i] = cf[0] * q[i] + cf[1] * oq;
+    dq2[i] = cf[2] * q[i] + cf[3] * oq;
   }
-  double n = norm4(dq);
-  for (int i = 0; i < 4; ++i) dq[i] /= n;
+  double n = 1.0 / norm4(dq);
+  for (int i = 0; i < 4; ++i) dq[i] *= n;
   const double stale[3] = {dq[0], dq[1], dq[2]};
   double RdT[9], Rd2T[9], R[9];
   rot_from_parts(dq, dq[3], stale, RdT);            // dR_dt (transposed when applied)
-  n = norm4(dq2);
-  for (int i = 0; i < 4; ++i) dq2[i] /= n;
+  n = 1.0 / norm4(dq2);
+  for (int i = 0; i < 4; ++i) dq2[i] *= n;
   rot_from_parts(dq2, dq2[3], stale, Rd2T);
-  n = norm4(q);
-  const double qn[4] = {q[0] / n, q[1] / n, q[2] / n, q[3] / n};
+  n = 1.0 / norm4(q);
+  const double qn[4] = {q[0] * n, q[1] * n, q[2] * n, q[3] * n};
   rot_from_parts(qn, qn[3], stale, R);
 
   double k1v[3], k2v[3], k4v[3], tmp[3];
@@ -70,8 +69,8 @@ __device__ void predict_new_state(double dt, const double* gyro, const double* a
     k3p[i] = v[i] + k2v[i] * dt / 2;
     k4p[i] = v[i] + k2v[i] * dt;
   }
-  n = norm4(dq);
-  for (int i = 0; i < 4; ++i) q[i] = dq[i] / n;
+  n = 1.0 / norm4(dq);
+  for (int i = 0; i < 4; ++i) q[i] = dq[i] * n;
   for (int i = 0; i < 3; ++i) {
     const double vi = v[i];
     v[i] = vi + (k1v[i] + 2 * k2v[i] + 2 * k2v[i] + k4v[i]) * dt / 6.;
@@ -86,10 +85,10 @@ __device__ void predict_new_state(double dt, const double* gyro, const double* a
 __device__ __forceinline__ bool phi_identity_row(int i) { return !(i < 3 || (i >= 6 && i < 9) || (i >= 12 && i < 15)); }
 __device__ __forceinline__ int phi_row_width(int i) { return i < 3 ? 6 : 15; }
 
-constexpr int PW = 4;                         // warps (= filters) per CTA
-constexpr int PKC = 8;                        // IMU samples per chunk
+constexpr int PW = 4;                         // warps per CTA (one CTA per filter)
+constexpr int PKC = 16;                       // IMU samples per chunk
 constexpr int PHC = 84;                       // doubles of one compact Phi: 8 blocks, dt, sigma_a^2 R^T R
-constexpr int PST = 20;                       // doubles of one staged sample / state: q v p | dt w a
+constexpr int PST = 24;                       // doubles of one staged sample / state: q v p | dt w a | cA sA cB sB
 constexpr int PROP_DOUBLES = 5 * 441 + 252 + PKC * PHC + (PKC + 1) * PST + IMU_STRIDE + 12;
 
 // Compact Phi of one IMU sample (lane-parallel over the samples of a chunk): jit_utils.py:6-43 followed by the
@@ -172,21 +171,22 @@ __device__ void build_phi(const double* x0, const double* x1, const double* qn, 
   for (int e = 0; e < 9; ++e) { out[e] = P00[e]; out[18 + e] = P20[e]; out[45 + e] = P40[e]; }
 }
 
-// One WARP per filter integrates the filter's IMU samples of this frame, PKC samples at a time:
-//   1. lane 0 runs the (sequential) RK4 state chain over the chunk,
-//   2. lane k builds Phi_k of sample k from the states before / after it (samples in parallel),
-//   3. the warp advances the 21x21 IMU block of P sample by sample and accumulates the product of the Phis.
+// One CTA of PW warps per filter integrates the filter's IMU samples of this frame, PKC samples at a time:
+//   1. thread 0 runs the (sequential) RK4 state chain over the chunk,
+//   2. thread k builds Phi_k of sample k from the states before / after it (samples in parallel),
+//   3. the CTA advances the 21x21 IMU block of P sample by sample and accumulates the product of the Phis.
 // The IMU-camera cross covariance only needs that product, applied once at the end (identical algebra:
 // P_IC <- Phi_k ... Phi_1 P_IC; symmetrising it is exact).
-__global__ void __launch_bounds__(PW * 32) k_propagate(Dev d, const int* __restrict__ imu_off, const double* __restrict__ ts,
+__global__ void __launch_bounds__(PW * 32, 4) k_propagate(Dev d, const int* __restrict__ imu_off, const double* __restrict__ ts,
                                                         const double* __restrict__ gyro_m, const double* __restrict__ acc_m) {
   extern __shared__ double psm[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int f = blockIdx.x * PW + warp;
+  constexpr int NT = PW * 32;
+  const int lane = threadIdx.x;            // index inside the filter's CTA
+  const int f = blockIdx.x;
   if (f >= d.F) return;
   const int k0 = imu_off[f], k1 = imu_off[f + 1];
   if (k1 <= k0) return;
-  double* sPhi = psm + (size_t)warp * PROP_DOUBLES;
+  double* sPhi = psm;
   double* sPII = sPhi + 441;
   double* sT = sPII + 441;
   double* sAcc = sT + 441;
@@ -201,13 +201,13 @@ __global__ void __launch_bounds__(PW * 32) k_propagate(Dev d, const int* __restr
   const int ld = d.ld;
   const int n = NI + 6 * d.ncam[f];
 
-  for (int e = lane; e < IMU_STRIDE; e += 32) sx[e] = imu[e];
-  for (int e = lane; e < 441; e += 32) {
+  for (int e = lane; e < IMU_STRIDE; e += NT) sx[e] = imu[e];
+  for (int e = lane; e < 441; e += NT) {
     const int i = e / 21, j = e - 21 * i;
     sPII[e] = P[(size_t)i * ld + j];
     sAcc[e] = (i == j) ? 1.0 : 0.0;
   }
-  __syncwarp();
+  __syncthreads();
 
   for (int c0 = k0; c0 < k1; c0 += PKC) {
     const int kc = min(PKC, k1 - c0);
@@ -215,34 +215,31 @@ __global__ void __launch_bounds__(PW * 32) k_propagate(Dev d, const int* __restr
     if (lane < kc) {
       const int k = c0 + lane;
       double* smp = sSt + lane * PST + 10;
-      smp[0] = ts[k];                       // turned into dt by the chain below
+      smp[0] = ts[k] - (lane == 0 ? sx[MSCKF_IMU_TIME] : ts[k - 1]);      // dt of this sample
       for (int i = 0; i < 3; ++i) {
         smp[1 + i] = gyro_m[3 * k + i] - sx[MSCKF_IMU_BG + i];
         smp[4 + i] = acc_m[3 * k + i] - sx[MSCKF_IMU_BA + i];
       }
+      quat_step_coeffs(smp[0], smp + 1, smp + 7);
     }
     if (lane < 4) sSt[lane] = sx[MSCKF_IMU_Q + lane];
     if (lane < 3) { sSt[4 + lane] = sx[MSCKF_IMU_V + lane]; sSt[7 + lane] = sx[MSCKF_IMU_P + lane]; }
-    __syncwarp();
+    __syncthreads();
     // ---- 1. RK4 chain
     if (lane == 0) {
       double q[4], v[3], p[3];
       for (int i = 0; i < 4; ++i) q[i] = sSt[i];
       for (int i = 0; i < 3; ++i) { v[i] = sSt[4 + i]; p[i] = sSt[7 + i]; }
-      double t_prev = sx[MSCKF_IMU_TIME];
       for (int c = 0; c < kc; ++c) {
-        double* smp = sSt + c * PST + 10;
-        const double t = smp[0], dt = t - t_prev;
-        smp[0] = dt;
-        t_prev = t;
-        predict_new_state(dt, smp + 1, smp + 4, sx + MSCKF_IMU_GRAVITY, q, v, p);
+        const double* smp = sSt + c * PST + 10;
+        predict_new_state(smp[0], smp + 1, smp + 4, smp + 7, sx + MSCKF_IMU_GRAVITY, q, v, p);
         double* nx = sSt + (c + 1) * PST;
         for (int i = 0; i < 4; ++i) nx[i] = q[i];
         for (int i = 0; i < 3; ++i) { nx[4 + i] = v[i]; nx[7 + i] = p[i]; }
       }
-      sx[MSCKF_IMU_TIME] = t_prev;
+      sx[MSCKF_IMU_TIME] = ts[c0 + kc - 1];
     }
-    __syncwarp();
+    __syncthreads();
     // ---- 2. Phi of every sample of the chunk (null state of the first sample = the stored one, then the previous state)
     if (lane < kc) {
       const double* x0 = sSt + lane * PST;
@@ -251,7 +248,7 @@ __global__ void __launch_bounds__(PW * 32) k_propagate(Dev d, const int* __restr
       build_phi(x0, x1, first ? sx + MSCKF_IMU_Q_NULL : x0, first ? sx + MSCKF_IMU_V_NULL : x0 + 4,
                 first ? sx + MSCKF_IMU_P_NULL : x0 + 7, x0 + 10, sx + MSCKF_IMU_GRAVITY, prm.Qc[2], sPc + lane * PHC);
     }
-    __syncwarp();
+    __syncthreads();
     // state after the chunk; null states <- current (msckf.py:366-368)
     {
       const double* xe = sSt + kc * PST;
@@ -266,9 +263,9 @@ __global__ void __launch_bounds__(PW * 32) k_propagate(Dev d, const int* __restr
     for (int c = 0; c < kc; ++c) {
       const double* pc = sPc + c * PHC;
       const double dt = pc[72];
-      for (int e = lane; e < 441; e += 32) sPhi[e] = (e % 22 == 0) ? 1.0 : 0.0;
-      __syncwarp();
-      for (int e = lane; e < 72; e += 32) {
+      for (int e = lane; e < 441; e += NT) sPhi[e] = (e % 22 == 0) ? 1.0 : 0.0;
+      __syncthreads();
+      for (int e = lane; e < 72; e += NT) {
         const int blk = e / 9, r = (e % 9) / 3, cc = e % 3;
         // block -> (row block, column block): 00 01 20 21 23 40 41 43
         const int rb = blk < 2 ? 0 : (blk < 5 ? 6 : 12);
@@ -276,9 +273,9 @@ __global__ void __launch_bounds__(PW * 32) k_propagate(Dev d, const int* __restr
         sPhi[21 * (rb + r) + cb + cc] = pc[e];
       }
       if (lane < 3) sPhi[21 * (12 + lane) + 6 + lane] = 1.0 * dt;
-      __syncwarp();
+      __syncthreads();
       // T = Phi P_II ; U = Phi (G Qc G^T)   (jit_utils.py:132-134)
-      for (int e = lane; e < 441; e += 32) {
+      for (int e = lane; e < 441; e += NT) {
         const int i = e / 21, j = e - 21 * i;
         double s;
         if (phi_identity_row(i)) {
@@ -290,7 +287,7 @@ __global__ void __launch_bounds__(PW * 32) k_propagate(Dev d, const int* __restr
         }
         sT[e] = s;
       }
-      for (int e = lane; e < 252; e += 32) {
+      for (int e = lane; e < 252; e += NT) {
         const int i = e / 12, j = e - 12 * i;
         double u;
         if (j < 3) u = sPhi[21 * i + j] * prm.Qc[0];
@@ -299,11 +296,11 @@ __global__ void __launch_bounds__(PW * 32) k_propagate(Dev d, const int* __restr
         else u = sPhi[21 * i + j] * prm.Qc[3];
         sU[e] = u;
       }
-      __syncwarp();
+      __syncthreads();
       // X = T Phi^T + (U Phi^T) dt ; Phi_acc <- Phi Phi_acc (kept in registers until everyone has read the old one)
-      double newA[14];
+      double newA[(441 + NT - 1) / NT];
       int cnt = 0;
-      for (int e = lane; e < 441; e += 32, ++cnt) {
+      for (int e = lane; e < 441; e += NT, ++cnt) {
         const int i = e / 21, j = e - 21 * i;
         double s;
         if (phi_identity_row(j)) {
@@ -327,25 +324,25 @@ __global__ void __launch_bounds__(PW * 32) k_propagate(Dev d, const int* __restr
         }
         newA[cnt] = acc;
       }
-      __syncwarp();
+      __syncthreads();
       cnt = 0;
-      for (int e = lane; e < 441; e += 32, ++cnt) {
+      for (int e = lane; e < 441; e += NT, ++cnt) {
         const int i = e / 21, j = e - 21 * i;
         sPII[e] = (sX2[e] + sX2[21 * j + i]) / 2.;
         sAcc[e] = newA[cnt];
       }
-      __syncwarp();
+      __syncthreads();
     }
   }
 
   // ---- write back: IMU state, P_II, P_IC = Phi_acc P_IC and its mirror
-  for (int e = lane; e < IMU_STRIDE; e += 32) imu[e] = sx[e];
+  for (int e = lane; e < IMU_STRIDE; e += NT) imu[e] = sx[e];
   if (lane == 0) d.counters[NCNT * f + MSCKF_CNT_IMU_STEPS] += k1 - k0;
-  for (int e = lane; e < 441; e += 32) {
+  for (int e = lane; e < 441; e += NT) {
     const int i = e / 21, j = e - 21 * i;
     P[(size_t)i * ld + j] = sPII[e];
   }
-  for (int j = NI + lane; j < n; j += 32) {
+  for (int j = NI + lane; j < n; j += NT) {
     double col[15];
 #pragma unroll
     for (int i = 0; i < 15; ++i) col[i] = P[(size_t)j * ld + i];      // column j of P_IC read through the (symmetric) row j
@@ -559,12 +556,12 @@ __global__ void __launch_bounds__(PT) k_remove_cams(Dev d) {
 // ------------------------------------------------------------------ launchers
 void launch_propagate(const Dev& d, const int* imu_off, const double* ts, const double* gyro, const double* acc, cudaStream_t st) {
   static bool attr_set = false;
-  const size_t smem = (size_t)PW * PROP_DOUBLES * sizeof(double);
+  const size_t smem = (size_t)PROP_DOUBLES * sizeof(double);
   if (!attr_set) {
     cudaFuncSetAttribute(k_propagate, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     attr_set = true;
   }
-  KLAUNCH(d, KID_PROPAGATE, st, (k_propagate<<<(d.F + PW - 1) / PW, PW * 32, smem, st>>>(d, imu_off, ts, gyro, acc)));
+  KLAUNCH(d, KID_PROPAGATE, st, (k_propagate<<<d.F, PW * 32, smem, st>>>(d, imu_off, ts, gyro, acc)));
 }
 void launch_augment(const Dev& d, const long long* ids, cudaStream_t st) { KLAUNCH(d, KID_AUGMENT, st, (k_augment<<<d.F, PT, 0, st>>>(d, ids))); }
 void launch_finish_frame(const Dev& d, int do_reset_check, cudaStream_t st) {

@@ -89,7 +89,13 @@ constexpr int PW = 4;                         // warps per CTA (one CTA per filt
 constexpr int PKC = 16;                       // IMU samples per chunk
 constexpr int PHC = 84;                       // doubles of one compact Phi: 8 blocks, dt, sigma_a^2 R^T R
 constexpr int PST = 24;                       // doubles of one staged sample / state: q v p | dt w a | cA sA cB sB
-constexpr int PROP_DOUBLES = 5 * 441 + 252 + PKC * PHC + (PKC + 1) * PST + IMU_STRIDE + 12;
+constexpr int PLD = 28;                       // leading dimension of the padded 24 x 24 matrices: 12 (mod 16) doubles, conflict-free DMMA fragments
+constexpr int PMAT = 24 * PLD;
+constexpr int PROP_DOUBLES = 5 * PMAT + PKC * PHC + (PKC + 1) * PST + IMU_STRIDE + 12;
+
+__device__ __forceinline__ void pdmma(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
 
 // Compact Phi of one IMU sample (lane-parallel over the samples of a chunk): jit_utils.py:6-43 followed by the
 // observability-constrained blocks of msckf.py:328-344.  x0 = state before the sample (q v p), x1 = after,
@@ -182,17 +188,17 @@ __global__ void __launch_bounds__(PW * 32, 4) k_propagate(Dev d, const int* __re
   extern __shared__ double psm[];
   constexpr int NT = PW * 32;
   const int lane = threadIdx.x;            // index inside the filter's CTA
+  const int wrp = lane >> 5, g = (lane & 31) >> 2, tg = lane & 3;   // warp, DMMA fragment coordinates
   const int f = blockIdx.x;
   if (f >= d.F) return;
   const int k0 = imu_off[f], k1 = imu_off[f + 1];
   if (k1 <= k0) return;
-  double* sPhi = psm;
-  double* sPII = sPhi + 441;
-  double* sT = sPII + 441;
-  double* sAcc = sT + 441;
-  double* sX2 = sAcc + 441;
-  double* sU = sX2 + 441;                  // [21][12] Phi (G Qc G^T)
-  double* sPc = sU + 252;                  // [PKC][PHC] compact Phis
+  double* sPhi = psm;                      // Phi of the current sample, 24 x 24 zero padded, ld = PLD
+  double* sPII = sPhi + PMAT;              // IMU block of P (+ dt G Qc G^T)
+  double* sT = sPII + PMAT;                // Phi (P_II + dt G Qc G^T)
+  double* sAcc = sT + PMAT;                // product of the Phis of this frame
+  double* sX2 = sAcc + PMAT;               // T Phi^T before symmetrisation
+  double* sPc = sX2 + PMAT;                // [PKC][PHC] compact Phis
   double* sSt = sPc + PKC * PHC;           // [PKC+1][PST]: state after sample c-1 (q v p) | sample c (dt w a)
   double* sx = sSt + (PKC + 1) * PST;
   const Params& prm = *d.prm;
@@ -202,10 +208,10 @@ __global__ void __launch_bounds__(PW * 32, 4) k_propagate(Dev d, const int* __re
   const int n = NI + 6 * d.ncam[f];
 
   for (int e = lane; e < IMU_STRIDE; e += NT) sx[e] = imu[e];
-  for (int e = lane; e < 441; e += NT) {
-    const int i = e / 21, j = e - 21 * i;
-    sPII[e] = P[(size_t)i * ld + j];
-    sAcc[e] = (i == j) ? 1.0 : 0.0;
+  for (int e = lane; e < PMAT; e += NT) {
+    const int i = e / PLD, j = e - PLD * i;
+    sPII[e] = (i < 21 && j < 21) ? P[(size_t)i * ld + j] : 0.0;
+    sAcc[e] = (i == j && i < 21) ? 1.0 : 0.0;
   }
   __syncthreads();
 
@@ -259,77 +265,76 @@ __global__ void __launch_bounds__(PW * 32, 4) k_propagate(Dev d, const int* __re
       }
       if (lane == 0) sx[MSCKF_IMU_NULL_ALIASED] = 1.0;
     }
-    // ---- 3. covariance, sample by sample
+    // ---- 3. covariance, sample by sample, on DMMA tiles (3 x 3 tiles of 8 x 8, K = 24):
+    //   P_II <- sym( Phi (P_II + dt G Qc G^T) Phi^T ),  Phi_acc <- Phi Phi_acc            (jit_utils.py:130-135, msckf.py:346-362)
+    // G Qc G^T = diag(sg I, sbg I, sa R^T R, sba I, 0): R^T R is the identity to rounding, so the noise goes onto the diagonal.
     for (int c = 0; c < kc; ++c) {
       const double* pc = sPc + c * PHC;
       const double dt = pc[72];
-      for (int e = lane; e < 441; e += NT) sPhi[e] = (e % 22 == 0) ? 1.0 : 0.0;
+      for (int e = lane; e < PMAT; e += NT) {
+        const int i = e / PLD, j = e - PLD * i;
+        sPhi[e] = (i == j && i < 21) ? 1.0 : 0.0;
+      }
+      if (lane < 12) sPII[lane * PLD + lane] += dt * prm.Qc[lane / 3];
       __syncthreads();
       for (int e = lane; e < 72; e += NT) {
         const int blk = e / 9, r = (e % 9) / 3, cc = e % 3;
         // block -> (row block, column block): 00 01 20 21 23 40 41 43
         const int rb = blk < 2 ? 0 : (blk < 5 ? 6 : 12);
         const int cb = (blk == 0 || blk == 2 || blk == 5) ? 0 : ((blk == 1 || blk == 3 || blk == 6) ? 3 : 9);
-        sPhi[21 * (rb + r) + cb + cc] = pc[e];
+        sPhi[PLD * (rb + r) + cb + cc] = pc[e];
       }
-      if (lane < 3) sPhi[21 * (12 + lane) + 6 + lane] = 1.0 * dt;
+      if (lane < 3) sPhi[PLD * (12 + lane) + 6 + lane] = 1.0 * dt;
       __syncthreads();
-      // T = Phi P_II ; U = Phi (G Qc G^T)   (jit_utils.py:132-134)
-      for (int e = lane; e < 441; e += NT) {
-        const int i = e / 21, j = e - 21 * i;
-        double s;
-        if (phi_identity_row(i)) {
-          s = sPII[e];
-        } else {
-          s = 0;
-          const int wdt = phi_row_width(i);
-          for (int kk = 0; kk < wdt; ++kk) s += sPhi[21 * i + kk] * sPII[21 * kk + j];
-        }
-        sT[e] = s;
-      }
-      for (int e = lane; e < 252; e += NT) {
-        const int i = e / 12, j = e - 12 * i;
-        double u;
-        if (j < 3) u = sPhi[21 * i + j] * prm.Qc[0];
-        else if (j < 6) u = sPhi[21 * i + j] * prm.Qc[1];
-        else if (j < 9) u = sPhi[21 * i + 6] * pc[73 + j - 6] + sPhi[21 * i + 7] * pc[73 + 3 + j - 6] + sPhi[21 * i + 8] * pc[73 + 6 + j - 6];
-        else u = sPhi[21 * i + j] * prm.Qc[3];
-        sU[e] = u;
-      }
-      __syncthreads();
-      // X = T Phi^T + (U Phi^T) dt ; Phi_acc <- Phi Phi_acc (kept in registers until everyone has read the old one)
-      double newA[(441 + NT - 1) / NT];
-      int cnt = 0;
-      for (int e = lane; e < 441; e += NT, ++cnt) {
-        const int i = e / 21, j = e - 21 * i;
-        double s;
-        if (phi_identity_row(j)) {
-          s = sT[21 * i + j];
-        } else {
-          s = 0;
-          const int wdt = phi_row_width(j);
-          for (int kk = 0; kk < wdt; ++kk) s += sT[21 * i + kk] * sPhi[21 * j + kk];
-        }
-        double qq = 0;
+      // T = Phi M (tiles 0..8) and Phi_acc' = Phi Phi_acc (tiles 9..17, kept in registers until the old one has been read)
+      double na0[3], na1[3];
 #pragma unroll
-        for (int kk = 0; kk < 12; ++kk) qq += sU[12 * i + kk] * sPhi[21 * j + kk];
-        sX2[e] = s + qq * dt;
-        double acc;
-        if (phi_identity_row(i)) {
-          acc = sAcc[e];
-        } else {
-          acc = 0;
-          const int wdt = phi_row_width(i);
-          for (int kk = 0; kk < wdt; ++kk) acc += sPhi[21 * i + kk] * sAcc[21 * kk + j];
+      for (int u = 0; u < 5; ++u) {
+        const int job = wrp + PW * u;
+        if (job < 18) {
+          const int t = job % 9, it = t / 3, jt = t - 3 * it;
+          const double* B = (job < 9) ? sPII : sAcc;
+          double c0v = 0.0, c1v = 0.0;
+#pragma unroll
+          for (int ks = 0; ks < 6; ++ks)
+            pdmma(c0v, c1v, sPhi[(8 * it + g) * PLD + 4 * ks + tg], B[(4 * ks + tg) * PLD + 8 * jt + g]);
+          if (job < 9) {
+            sT[(8 * it + g) * PLD + 8 * jt + 2 * tg] = c0v;
+            sT[(8 * it + g) * PLD + 8 * jt + 2 * tg + 1] = c1v;
+          } else {
+            na0[(u - 2) < 0 ? 0 : (u - 2)] = c0v;
+            na1[(u - 2) < 0 ? 0 : (u - 2)] = c1v;
+          }
         }
-        newA[cnt] = acc;
       }
       __syncthreads();
-      cnt = 0;
-      for (int e = lane; e < 441; e += NT, ++cnt) {
-        const int i = e / 21, j = e - 21 * i;
-        sPII[e] = (sX2[e] + sX2[21 * j + i]) / 2.;
-        sAcc[e] = newA[cnt];
+      // X = T Phi^T ; Phi_acc <- Phi_acc'
+#pragma unroll
+      for (int u = 0; u < 3; ++u) {
+        const int t = wrp + PW * u;
+        if (t < 9) {
+          const int it = t / 3, jt = t - 3 * it;
+          double c0v = 0.0, c1v = 0.0;
+#pragma unroll
+          for (int ks = 0; ks < 6; ++ks)
+            pdmma(c0v, c1v, sT[(8 * it + g) * PLD + 4 * ks + tg], sPhi[(8 * jt + g) * PLD + 4 * ks + tg]);
+          sX2[(8 * it + g) * PLD + 8 * jt + 2 * tg] = c0v;
+          sX2[(8 * it + g) * PLD + 8 * jt + 2 * tg + 1] = c1v;
+        }
+      }
+#pragma unroll
+      for (int u = 2; u < 5; ++u) {
+        const int job = wrp + PW * u;
+        if (job >= 9 && job < 18) {
+          const int t = job - 9, it = t / 3, jt = t - 3 * it;
+          sAcc[(8 * it + g) * PLD + 8 * jt + 2 * tg] = na0[u - 2];
+          sAcc[(8 * it + g) * PLD + 8 * jt + 2 * tg + 1] = na1[u - 2];
+        }
+      }
+      __syncthreads();
+      for (int e = lane; e < PMAT; e += NT) {
+        const int i = e / PLD, j = e - PLD * i;
+        if (i < 24 && j < 24) sPII[e] = (sX2[e] + sX2[j * PLD + i]) / 2.;
       }
       __syncthreads();
     }
@@ -340,22 +345,28 @@ __global__ void __launch_bounds__(PW * 32, 4) k_propagate(Dev d, const int* __re
   if (lane == 0) d.counters[NCNT * f + MSCKF_CNT_IMU_STEPS] += k1 - k0;
   for (int e = lane; e < 441; e += NT) {
     const int i = e / 21, j = e - 21 * i;
-    P[(size_t)i * ld + j] = sPII[e];
+    P[(size_t)i * ld + j] = sPII[i * PLD + j];
   }
-  for (int j = NI + lane; j < n; j += NT) {
-    double col[15];
+  // P_IC <- Phi_acc P_IC and its mirror: a warp owns an 8-column tile (its B fragments are read before anything is written)
+  const int nct = (n - NI + 7) >> 3;
+  for (int jt = wrp; jt < nct; jt += PW) {
+    const int j = NI + 8 * jt + g;
+    double bf[6];
 #pragma unroll
-    for (int i = 0; i < 15; ++i) col[i] = P[(size_t)j * ld + i];      // column j of P_IC read through the (symmetric) row j
+    for (int ks = 0; ks < 6; ++ks) {
+      const int k = 4 * ks + tg;
+      bf[ks] = (k < NI && j < n) ? P[(size_t)k * ld + j] : 0.0;
+    }
 #pragma unroll
-    for (int i = 0; i < 15; ++i) {
-      if (phi_identity_row(i)) continue;
-      double s = 0;
-      const int wdt = phi_row_width(i);
+    for (int it = 0; it < 3; ++it) {
+      double c0v = 0.0, c1v = 0.0;
 #pragma unroll
-      for (int kk = 0; kk < 15; ++kk)
-        if (kk < wdt) s += sAcc[21 * i + kk] * col[kk];
-      P[(size_t)i * ld + j] = s;
-      P[(size_t)j * ld + i] = s;
+      for (int ks = 0; ks < 6; ++ks) pdmma(c0v, c1v, sAcc[(8 * it + g) * PLD + 4 * ks + tg], bf[ks]);
+      const int i = 8 * it + g, jj = NI + 8 * jt + 2 * tg;
+      if (i < NI) {
+        if (jj < n) { P[(size_t)i * ld + jj] = c0v; P[(size_t)jj * ld + i] = c0v; }
+        if (jj + 1 < n) { P[(size_t)i * ld + jj + 1] = c1v; P[(size_t)(jj + 1) * ld + i] = c1v; }
+      }
     }
   }
 }

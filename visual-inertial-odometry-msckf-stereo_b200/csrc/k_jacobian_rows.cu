@@ -74,7 +74,7 @@ __device__ __forceinline__ void jr_row(const double* __restrict__ pre, const dou
 
 
 template <int M, int G>
-__global__ void __launch_bounds__(JR_T) k_jacobian_rows(Dev d, int cls, int write_all) {
+__global__ void __launch_bounds__(JR_T, 6) k_jacobian_rows(Dev d, int cls, int write_all) {
   constexpr int R4 = 4 * M, C6 = 6 * M, R = R4 - 3, LDR = C6 + 1, GPW = 32 / G, GD = jr_group_doubles<M>();
   static_assert(R4 <= G, "one lane per row");
   extern __shared__ __align__(16) double jsm[];

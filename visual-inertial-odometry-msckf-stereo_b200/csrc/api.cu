@@ -14,7 +14,7 @@ using namespace msckf;
 namespace msckf {
 const char* const kKernelNames[KID_COUNT] = {
     "k_propagate", "k_augment", "k_cam_prepare", "k_observe", "k_classify_lost", "k_prune_select", "k_triangulate", "k_plan_items",
-    "k_jacobian_gate", "k_jacobian_rows", "k_jacobian_big", "k_plan_stack", "k_qr", "k_qr_d16", "k_qr_d32", "k_qr_d48", "k_qr_d64", "k_upd_dmma16", "k_upd_dmma64", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
+    "k_jacobian_gate", "k_jacobian_rows", "k_jacobian_big", "k_plan_stack", "k_qr", "k_qr_d16", "k_qr_d32", "k_qr_d48", "k_qr_d64", "k_upd_dmma16", "k_upd_dmma32", "k_upd_dmma48", "k_upd_dmma64", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
     "k_upd_downdate", "k_remove_cams", "k_finish_frame", "k_reset", "misc"};
 
 void KTimer::begin(int id, cudaStream_t st) {
@@ -296,8 +296,11 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
       d.rowmap_cap = (int)(row_cap > 0 ? std::min(all, capped) : all);
     }
     d.jac_rows_ok = getenv("MSCKF_NO_JAC_ROWS") ? 0 : 1;
-    d.upd_dmma_ok[0] = (!getenv("MSCKF_NO_DMMA") && upd_dmma_smem_bytes(d.nmax, 16) <= 220 * 1024) ? 1 : 0;
-    d.upd_dmma_ok[1] = (!getenv("MSCKF_NO_DMMA") && upd_dmma_smem_bytes(d.nmax, 64) <= 220 * 1024) ? 1 : 0;      // debugging knob: route medium updates through the tiled kernels
+    {
+      const int kc[UPD_DMMA_CLASSES] = {16, 32, 48, 64};
+      for (int c = 0; c < UPD_DMMA_CLASSES; ++c)      // MSCKF_NO_DMMA: debugging knob, every update through the tiled kernels
+        d.upd_dmma_ok[c] = (!getenv("MSCKF_NO_DMMA") && upd_dmma_smem_bytes(d.nmax, kc[c]) <= 220 * 1024) ? 1 : 0;
+    }
     const long long na = 6 * M, worst = 640 + na * (na + 1) / 2 + na + 32 * (na + 1) + 64;
     d.qr_scratch_stride = worst > d.qr_smem_doubles ? na * (na + 1) / 2 + na + 256 * (na + 1) : 0;
   }
@@ -341,7 +344,7 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   DA(d.jac_scratch, (size_t)d.jac_big_grid * d.jac_scratch_stride);
   if (d.qr_scratch_stride) DA(d.qr_scratch, F * (size_t)d.qr_scratch_stride);
   DA(d.Adense, (size_t)d.Adense_elems);
-  DA(d.A, F * (size_t)d.A_elems); DA(d.m_rows, F); DA(d.m_pad, F); DA(d.n_act, F); DA(d.k_rows, F); DA(d.colmap, F * (size_t)d.nmax); DA(d.upd_path, F); DA(d.wl_upd_big, F); DA(d.wl_upd_dmma, 2 * F);
+  DA(d.A, F * (size_t)d.A_elems); DA(d.m_rows, F); DA(d.m_pad, F); DA(d.n_act, F); DA(d.k_rows, F); DA(d.colmap, F * (size_t)d.nmax); DA(d.upd_path, F); DA(d.wl_upd_big, F); DA(d.wl_upd_dmma, (size_t)UPD_DMMA_CLASSES * F);
   DA(d.rowmap, F * (size_t)d.rowmap_cap); DA(d.qr_cls, F); DA(d.wl_qr, (size_t)QR_DMMA_CLASSES * F);
   DA(d.T, F * (size_t)d.Tk * Tld(d)); DA(d.S, F * (size_t)d.Tk * d.Tk); DA(d.dx, F * (size_t)d.nmax);
   DA(d.log_id, 2 * F * Fc); DA(d.log_status, 2 * F * Fc); DA(d.log_gamma, 2 * F * Fc); DA(d.log_dof, 2 * F * Fc);
@@ -654,8 +657,7 @@ static void enqueue_lost_stage(msckf_ctx* ctx) {
   launch_plan_items(d, 0, ctx->st);
   launch_jacobian_gate(d, 0xE, 1, 0, ctx->st);            // lost landmarks have at least three observations
   launch_plan_stack(d, 0, ctx->st);
-  launch_qr_all(d, ctx->st);
-  launch_update(d, 0, ctx->st);
+  launch_compress_update(d, ctx->st);
 }
 static void enqueue_prune_stage(msckf_ctx* ctx) {
   const Dev& d = ctx->d;
@@ -666,8 +668,7 @@ static void enqueue_prune_stage(msckf_ctx* ctx) {
   launch_plan_items(d, 1, ctx->st);
   launch_jacobian_gate(d, 0x1, 0, 0, ctx->st);            // the pruning update always involves exactly two camera states
   launch_plan_stack(d, 1, ctx->st);
-  launch_qr_all(d, ctx->st);
-  launch_update(d, 1, ctx->st);
+  launch_compress_update(d, ctx->st);
   launch_remove_cams(d, ctx->st);
 }
 

@@ -250,7 +250,7 @@ __global__ void __launch_bounds__(QD_T, 2) k_qr_dmma(Dev d, int cls, int cap) {
   }
 }
 
-void launch_qr_dmma(const Dev& d, Fork& fk) {
+void launch_qr_dmma_class(const Dev& d, int c, cudaStream_t st) {
   static bool attr_set = false;
   static int sms = 0;
   if (!attr_set) {
@@ -261,13 +261,13 @@ void launch_qr_dmma(const Dev& d, Fork& fk) {
   const int caps[QR_DMMA_CLASSES] = {16, 32, 48, 64};
   const int thr[QR_DMMA_CLASSES] = {64, 128, 128, 256};
   const int kid[QR_DMMA_CLASSES] = {KID_QR_D16, KID_QR_D32, KID_QR_D48, KID_QR_D64};
-  for (int c = 0; c < QR_DMMA_CLASSES; ++c) {
-    const size_t sm = qr_dmma_smem_bytes(caps[c]);
-    int per_sm = (int)std::min<size_t>((224 * 1024) / (sm + 1024), 512 / thr[c]);   // 128 registers per thread
-    per_sm = std::max(1, per_sm);
-    cudaStream_t st = fk.lane(c);
-    KLAUNCH(d, kid[c], st, (k_qr_dmma<<<std::min(d.F, sms * per_sm), thr[c], sm, st>>>(d, c, caps[c])));
-  }
+  const size_t sm = qr_dmma_smem_bytes(caps[c]);
+  int per_sm = (int)std::min<size_t>((224 * 1024) / (sm + 1024), 512 / thr[c]);   // 128 registers per thread
+  per_sm = std::max(1, per_sm);
+  KLAUNCH(d, kid[c], st, (k_qr_dmma<<<std::min(d.F, sms * per_sm), thr[c], sm, st>>>(d, c, caps[c])));
+}
+void launch_qr_dmma(const Dev& d, Fork& fk) {
+  for (int c = 0; c < QR_DMMA_CLASSES; ++c) launch_qr_dmma_class(d, c, fk.lane(c));
 }
 
 }  // namespace msckf

@@ -461,7 +461,9 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
     d.k_rows[f] = kr;
     int path = 0;
     if (kr > 0) {
-      path = (kr <= 16 && na <= 16 && d.upd_dmma_ok[0]) ? 5 : ((kr <= 64 && na <= 64 && d.upd_dmma_ok[1]) ? 6 : 2);   // one-CTA tensor-pipe kernel, else tiled
+      const int wid = max(kr, na) + 1;                  // same thresholds as the compression classes: QR and update of a class share a stream
+      const int uc = wid <= 16 ? 0 : (wid <= 32 ? 1 : (wid <= 48 ? 2 : (wid <= 64 ? 3 : -1)));
+      path = (uc >= 0 && d.upd_dmma_ok[uc]) ? 5 + uc : 2;           // one-CTA tensor-pipe kernel, else tiled
       if (path == 2) d.wl_upd_big[atomicAdd(d.stage_ctr + SC_NUPD_BIG, 1ull)] = f;
       if (path >= 5) d.wl_upd_dmma[(size_t)(path - 5) * d.F + atomicAdd(d.stage_ctr + SC_NUPD_DMMA + (path - 5), 1ull)] = f;
     }

@@ -542,6 +542,23 @@ void launch_qr_all(const Dev& d, cudaStream_t st) {
   launch_qr_dmma(d, fk);
   launch_qr_build(d, fk.lane(4));
 }
+void launch_compress_update(const Dev& d, cudaStream_t st) {
+  launch_qr_build(d, st);                       // wide / uncompressed stacks first: their updates may sit in any class
+  bool all_ok = true;
+  for (int c = 0; c < UPD_DMMA_CLASSES; ++c) all_ok = all_ok && d.upd_dmma_ok[c];
+  {
+    Fork fk(d, st);
+    for (int c = 0; c < QR_DMMA_CLASSES; ++c) {   // class c: compression, then its update, back to back on one stream
+      cudaStream_t s = fk.lane(c);
+      launch_qr_dmma_class(d, c, s);
+      launch_upd_dmma_class(d, c, s);
+    }
+    // the tiled update only takes stacks k_qr_build compressed when every one-CTA class is available ...
+    if (all_ok) launch_update_tiled(d, fk.lane(4));
+  }
+  // ... otherwise it also takes filters of a k_qr_dmma class (window too wide for the class's shared memory): after the join
+  if (!all_ok) launch_update_tiled(d, st);
+}
 void launch_qr_dense(const Dev& d, int filter, int mp_dense, cudaStream_t st) {
   KLAUNCH(d, KID_QR, st, (k_qr_dense<<<1, UT, 0, st>>>(d, filter, mp_dense)));
 }
@@ -550,7 +567,9 @@ void launch_update(const Dev& d, int stage, cudaStream_t st) {
   (void)stage;
   Fork fk(d, st);
   launch_update_dmma(d, fk);
-  st = fk.lane(2);
+  launch_update_tiled(d, fk.lane(4));
+}
+void launch_update_tiled(const Dev& d, cudaStream_t st) {
   // tiled path for the filters k_plan_stack queued in wl_upd_big (none in the common case: the grids exit at once)
   const int tn = (d.nmax + 1 + 31) / 32, tk = (d.Tk + 31) / 32, tp = (d.nmax + 31) / 32;
   const int fz = d.F < 32 ? d.F : 32;

@@ -18,7 +18,6 @@
 
 namespace msckf {
 
-constexpr int DT = 256;            // threads per CTA (8 warps)
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int LDL = 12;            // leading dimension of the inverted diagonal block
 
@@ -87,11 +86,12 @@ __device__ __forceinline__ void tri_decode(int t, int& i, int& j) {
   j = t - i * (i + 1) / 2;
 }
 
-template <int KC>
-__global__ void __launch_bounds__(DT, 2) k_upd_dmma(Dev d, int cls) {
+template <int KC, int DT>
+__global__ void __launch_bounds__(DT, 512 / DT) k_upd_dmma(Dev d, int cls) {
   constexpr int LDX = KC + 4;
   constexpr int NKT = KC / 8;                  // row tiles at capacity
-  constexpr int S_PER_WARP = (NKT * (NKT + 1) / 2 + 7) / 8;
+  constexpr int NW = DT / 32;                  // warps per CTA
+  constexpr int S_PER_WARP = (NKT * (NKT + 1) / 2 + NW - 1) / NW;
   extern __shared__ double us[];
   const int ldT = dmma_ldT(d.nmax);
   double* sX = us;                              // [KC][LDX]
@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(DT, 2) k_upd_dmma(Dev d, int cls) {
 #pragma unroll
     for (int q = 0; q < S_PER_WARP; ++q) {
       sv0[q] = sv1[q] = 0.0;
-      const int t = warp + 8 * q;
+      const int t = warp + NW * q;
       if (t < nst) {
         int it, jt;
         tri_decode(t, it, jt);
@@ -177,7 +177,7 @@ __global__ void __launch_bounds__(DT, 2) k_upd_dmma(Dev d, int cls) {
     __syncthreads();
 #pragma unroll
     for (int q = 0; q < S_PER_WARP; ++q) {
-      const int t = warp + 8 * q;
+      const int t = warp + NW * q;
       if (t < nst) {
         int it, jt;
         tri_decode(t, it, jt);
@@ -315,27 +315,30 @@ __global__ void __launch_bounds__(DT, 2) k_upd_dmma(Dev d, int cls) {
   }
 }
 
-static int g_sm_count_dmma = 0;
-void launch_update_dmma(const Dev& d, Fork& fk) {
+template <int KC, int DT>
+static void launch_upd_class(const Dev& d, int cls, int kid, cudaStream_t st) {
   static bool attr_set = false;
+  static int sms = 0;
   if (!attr_set) {
-    cudaFuncSetAttribute(k_upd_dmma<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-    cudaFuncSetAttribute(k_upd_dmma<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-    g_sm_count_dmma = sm_count();
+    cudaFuncSetAttribute(k_upd_dmma<KC, DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    sms = sm_count();
     attr_set = true;
   }
-  if (d.upd_dmma_ok[0]) {
-    cudaStream_t st = fk.lane(1);
-    const size_t sm = upd_dmma_smem_bytes(d.nmax, 16);
-    const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (224 * 1024) / (sm + 1024)));
-    KLAUNCH(d, KID_UPD_DMMA16, st, (k_upd_dmma<16><<<std::min(d.F, g_sm_count_dmma * per_sm), DT, sm, st>>>(d, 0)));
-  }
-  if (d.upd_dmma_ok[1]) {
-    cudaStream_t st = fk.lane(0);
-    const size_t sm = upd_dmma_smem_bytes(d.nmax, 64);
-    const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(2, (224 * 1024) / (sm + 1024)));
-    KLAUNCH(d, KID_UPD_DMMA64, st, (k_upd_dmma<64><<<std::min(d.F, g_sm_count_dmma * per_sm), DT, sm, st>>>(d, 1)));
-  }
+  const size_t sm = upd_dmma_smem_bytes(d.nmax, KC);
+  const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(512 / DT, (224 * 1024) / (sm + 1024)));    // 128 registers per thread
+  KLAUNCH(d, kid, st, (k_upd_dmma<KC, DT><<<std::min(d.F, sms * per_sm), DT, sm, st>>>(d, cls)));
+}
+
+// update class c = compression class c: k, n_a + 1 <= 16 / 32 / 48 / 64
+void launch_upd_dmma_class(const Dev& d, int cls, cudaStream_t st) {
+  if (!d.upd_dmma_ok[cls]) return;
+  if (cls == 0) launch_upd_class<16, 128>(d, 0, KID_UPD_DMMA16, st);
+  else if (cls == 1) launch_upd_class<32, 128>(d, 1, KID_UPD_DMMA32, st);
+  else if (cls == 2) launch_upd_class<48, 256>(d, 2, KID_UPD_DMMA48, st);
+  else launch_upd_class<64, 256>(d, 3, KID_UPD_DMMA64, st);
+}
+void launch_update_dmma(const Dev& d, Fork& fk) {
+  for (int c = 0; c < UPD_DMMA_CLASSES; ++c) launch_upd_dmma_class(d, c, fk.lane(c == 3 ? 0 : c + 1));
 }
 
 }  // namespace msckf

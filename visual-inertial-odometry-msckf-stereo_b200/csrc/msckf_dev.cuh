@@ -30,9 +30,11 @@ constexpr unsigned ERRBIT_NOT_SPD = 8u;
 constexpr unsigned ERRBIT_CAM_CAP = 16u;
 
 // per-stage device counters (one memset per stage): pool bump pointer and work-list lengths
-constexpr int SC_POOL = 0, SC_NTRI = 1, SC_NJAC_BIG = 2, SC_NUPD_BIG = 3, SC_NJAC_SMALL = 4 /* .. 7: one per size class */, SC_NUPD_DMMA = 10 /* .. 11: tensor-pipe update classes */, SC_NQR = 12 /* .. 15: tensor-pipe QR classes */, SC_COUNT = 16;
+constexpr int SC_POOL = 0, SC_NTRI = 1, SC_NJAC_BIG = 2, SC_NUPD_BIG = 3, SC_NJAC_SMALL = 4 /* .. 7: one per size class */, SC_NQR = 12 /* .. 15: tensor-pipe QR classes */, SC_NUPD_DMMA = 16 /* .. 19: tensor-pipe update classes */, SC_COUNT = 24;
 // stacked-Jacobian compression classes: 0..3 = compressed (m > n_a) with n_a + 1 <= 16 / 32 / 48 / 64 columns (k_qr_dmma), 4 = general CTA kernel
 constexpr int QR_DMMA_CLASSES = 4;
+// one-CTA tensor-pipe update classes, aligned with the compression classes: max(k, n_a) + 1 <= 16 / 32 / 48 / 64
+constexpr int UPD_DMMA_CLASSES = 4;
 // size classes of the group-per-landmark Jacobian kernel (shared memory is sized per class): M <= 2, M = 3, M = 4, M <= 6
 constexpr int JAC_CLASSES = 4;
 __host__ __device__ inline int jac_class(int M) { return M <= 2 ? 0 : (M == 3 ? 1 : (M == 4 ? 2 : 3)); }
@@ -124,10 +126,10 @@ struct Dev {
   int rowmap_cap;
   int* qr_cls;             // [F] compression class of this stage's stacked Jacobian (-1: nothing to do)
   int* wl_qr;              // [QR_DMMA_CLASSES][F] filters of the tensor-pipe QR classes
-  int* upd_path;           // [F] 0 = no update, 2 = tiled kernels (queued in wl_upd_big), 5 / 6 = DMMA kernel (k <= 16 / k <= 64)
+  int* upd_path;           // [F] 0 = no update, 2 = tiled kernels (queued in wl_upd_big), 5 + c = DMMA kernel of class c
   int* wl_upd_big;         // [F]
-  int* wl_upd_dmma;        // [2][F] filters of the tensor-pipe update classes (k <= 16, k <= 64)
-  int upd_dmma_ok[2];      // class fits shared memory for this window size
+  int* wl_upd_dmma;        // [UPD_DMMA_CLASSES][F] filters of the tensor-pipe update classes
+  int upd_dmma_ok[UPD_DMMA_CLASSES];   // class fits shared memory for this window size
   double* T;               // [F][Tk][ld+8]  H_thin P | r  -> W | y
   double* S;               // [F][Tk][Tk]
   double* dx;              // [F][nmax]

@@ -284,3 +284,17 @@ def test_two_frames_in_flight_equal_sequential():
     assert np.array_equal(outs['blocking'][0], outs['pipelined'][0])
     for k in range(F):
         assert np.array_equal(outs['blocking'][1][k], outs['pipelined'][1][k])
+
+
+@pytest.mark.parametrize('knob', ['MSCKF_NO_DMMA', 'MSCKF_NO_LANES', 'MSCKF_NO_JAC_ROWS'])
+def test_alternative_kernel_paths(knob, monkeypatch):
+    """The library's debugging knobs route the same work through its other kernels: the tiled update kernels instead of
+    the one-CTA DMMA update (the path wide windows take), in-order launches instead of concurrent size classes, the
+    group-per-landmark Jacobian kernel instead of the lane-per-row one.  Each must pass the same stepped comparison."""
+    monkeypatch.setenv(knob, '1')
+    n_frames = 40
+    stream = synth.make_stream(n_frames, 120, structure_seed=6, noise_seed=21)
+    worst, counts = run_pair(stream, 10, n_frames, feature_capacity=512)
+    assert counts['gates'] > 300 and counts['prunes'] >= 5 and counts['updates'] > 20, counts
+    assert worst['imu'] < TOL and worst['P'] < TOL and worst['cams'] < TOL and worst['extr'] < TOL, worst
+    assert worst['pos_m'] < 1e-3, worst

@@ -651,8 +651,11 @@ int msckf_set_feature_position(msckf_ctx* ctx, int32_t f, int64_t id, const doub
 static void enqueue_lost_stage(msckf_ctx* ctx) {
   const Dev& d = ctx->d;
   cudaMemsetAsync(d.stage_ctr, 0, SC_COUNT * sizeof(unsigned long long), ctx->st);
-  launch_cam_prepare(d, ctx->st);
-  launch_classify_lost(d, ctx->st);
+  {   // independent bookkeeping of the stage, side by side
+    Fork fk(d, ctx->st);
+    launch_cam_prepare(d, fk.lane(1));
+    launch_classify_lost(d, fk.lane(0));
+  }
   launch_triangulate_store(d, ctx->st);
   launch_plan_items(d, 0, ctx->st);
   launch_jacobian_gate(d, 0xE, 1, 0, ctx->st);            // lost landmarks have at least three observations
@@ -662,8 +665,11 @@ static void enqueue_lost_stage(msckf_ctx* ctx) {
 static void enqueue_prune_stage(msckf_ctx* ctx) {
   const Dev& d = ctx->d;
   cudaMemsetAsync(d.stage_ctr, 0, SC_COUNT * sizeof(unsigned long long), ctx->st);
-  launch_cam_prepare(d, ctx->st);
-  launch_prune_select(d, ctx->st);
+  {
+    Fork fk(d, ctx->st);
+    launch_cam_prepare(d, fk.lane(1));
+    launch_prune_select(d, fk.lane(0));
+  }
   launch_triangulate_store(d, ctx->st);
   launch_plan_items(d, 1, ctx->st);
   launch_jacobian_gate(d, 0x1, 0, 0, ctx->st);            // the pruning update always involves exactly two camera states

@@ -342,15 +342,29 @@ __global__ void __launch_bounds__(ST) k_plan_items(Dev d, int stage) {
       d.item_pass[k] = 0;
       d.item_gamma[k] = 0.0;
       d.item_rowoff[k] = -1;
-      if (M <= JAC_SMALL_M) {
-        const int cls = jac_class(M);
-        d.wl_jac_small[(size_t)cls * d.F * d.Fcap + atomicAdd(d.stage_ctr + SC_NJAC_SMALL + cls, 1ull)] = make_int2(f, ni + r);
-      }
-      else d.wl_jac_big[atomicAdd(d.stage_ctr + SC_NJAC_BIG, 1ull)] = make_int2(f, ni + r);
       const long long Ml = M, R = rows, C6 = 6 * Ml;
       w_obs += Ml;
       w_flops += 300 * Ml + 12 * (4 * Ml) * (C6 + 1) + 2 * R * C6 * C6 + 2 * R * R * C6 + (R * R * R) / 3 + 2 * R * R;
       w_bytes += 36 * Ml + 8 * R * (C6 + 1);
+    }
+    // queue the item for its Jacobian kernel class: one atomic per warp and class instead of one per item
+    {
+      const int cls = !isitem ? -1 : (M <= JAC_SMALL_M ? jac_class(M) : JAC_CLASSES);
+      const unsigned lane = tid & 31;
+#pragma unroll
+      for (int c = 0; c <= JAC_CLASSES; ++c) {
+        const unsigned bal = __ballot_sync(0xffffffffu, cls == c);
+        if (bal == 0) continue;
+        unsigned long long base = 0;
+        if (lane == (unsigned)(__ffs(bal) - 1))
+          base = atomicAdd(d.stage_ctr + (c < JAC_CLASSES ? SC_NJAC_SMALL + c : SC_NJAC_BIG), (unsigned long long)__popc(bal));
+        base = __shfl_sync(0xffffffffu, base, __ffs(bal) - 1);
+        if (cls == c) {
+          const unsigned long long pos = base + __popc(bal & ((1u << lane) - 1u));
+          if (c < JAC_CLASSES) d.wl_jac_small[(size_t)c * d.F * d.Fcap + pos] = make_int2(f, ni + r);
+          else d.wl_jac_big[pos] = make_int2(f, ni + r);
+        }
+      }
     }
     ni += tot;
     elems_total += tot_e;

@@ -514,7 +514,7 @@ __global__ void __launch_bounds__(PT) k_reset(Dev d, int only_filter, int reset_
 // ------------------------------------------------------------------ camera-state removal (msckf.py:803-818)
 // In-place compaction of P, the camera table and the physical-slot mask.  Rows are moved in
 // increasing order in batches staged through shared memory (destination row <= source row).
-constexpr int RB = 8;   // rows per batch
+constexpr int RB = 24;  // rows per batch
 __global__ void __launch_bounds__(PT) k_remove_cams(Dev d) {
   const int f = blockIdx.x, tid = threadIdx.x;
   const int r0 = d.rm_idx[2 * f], r1 = d.rm_idx[2 * f + 1];
@@ -528,16 +528,19 @@ __global__ void __launch_bounds__(PT) k_remove_cams(Dev d) {
     if (i < NI + 6 * (r1 - 1)) return i + 6;
     return i + 12;
   };
+  // rows above the first removed camera state keep their place: only their columns right of it move (in-row shift)
+  const int first = NI + 6 * r0;
   for (int base = 0; base < n2; base += RB) {
     const int nb = min(RB, n2 - base);
-    for (int e = tid; e < nb * n2; e += PT) {
-      const int i = e / n2, j = e - i * n2;
-      srow[i * ld + j] = P[(size_t)src_of(base + i) * ld + src_of(j)];
+    const int j0 = (base + nb <= first) ? first : 0;
+    for (int i = tid >> 5; i < nb; i += PT / 32) {                         // a warp owns a row, lanes run along it
+      const double* src = P + (size_t)src_of(base + i) * ld;
+      for (int j = j0 + (tid & 31); j < n2; j += 32) srow[i * ld + j] = src[src_of(j)];
     }
     __syncthreads();
-    for (int e = tid; e < nb * n2; e += PT) {
-      const int i = e / n2, j = e - i * n2;
-      P[(size_t)(base + i) * ld + j] = srow[i * ld + j];
+    for (int i = tid >> 5; i < nb; i += PT / 32) {
+      double* dst = P + (size_t)(base + i) * ld;
+      for (int j = j0 + (tid & 31); j < n2; j += 32) dst[j] = srow[i * ld + j];
     }
     __syncthreads();
   }
@@ -582,6 +585,11 @@ void launch_reset(const Dev& d, int only_filter, int reset_imu, cudaStream_t st)
   KLAUNCH(d, KID_RESET, st, (k_reset<<<only_filter >= 0 ? 1 : d.F, PT, 0, st>>>(d, only_filter, reset_imu)));
 }
 void launch_remove_cams(const Dev& d, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(k_remove_cams, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    attr_set = true;
+  }
   KLAUNCH(d, KID_REMOVE_CAMS, st, (k_remove_cams<<<d.F, PT, (size_t)RB * d.ld * sizeof(double), st>>>(d)));
 }
 

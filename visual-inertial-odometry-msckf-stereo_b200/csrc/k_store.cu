@@ -147,6 +147,18 @@ __global__ void __launch_bounds__(ST) k_observe(Dev d, const int* __restrict__ f
   }
 }
 
+// Appends (filter, candidate) to the triangulation work list: one atomic per warp, not per landmark.
+__device__ __forceinline__ void wl_push_tri(const Dev& d, bool want, int f, int idx) {
+  const unsigned bal = __ballot_sync(0xffffffffu, want);
+  if (!bal) return;
+  const unsigned lane = threadIdx.x & 31;
+  const int leader = __ffs(bal) - 1;
+  unsigned long long base = 0;
+  if ((int)lane == leader) base = atomicAdd(d.stage_ctr + SC_NTRI, (unsigned long long)__popc(bal));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  if (want) d.wl_tri[base + __popc(bal & ((1u << lane) - 1u))] = make_int2(f, idx);
+}
+
 // ------------------------------------------------------------------ remove_lost_features, pass 1 (msckf.py:623-650)
 // Splits the map into tracked (kept) and lost landmarks, both in map order.  Lost landmarks go to
 // the candidate list with status FEW_OBS / CS_NEED_TRI / CS_READY; their slots are released
@@ -178,6 +190,8 @@ __global__ void __launch_bounds__(ST) k_classify_lost(Dev d) {
     const int rl = block_rank(lost, s_warp, tl);
     const int rk = block_rank(keep, s_warp, tk);
     if (keep) tmp[nkeep + rk] = slot;
+    bool want_tri = false;
+    int tri_idx = 0;
     if (lost) {
       const int ci = nlost + rl;
       cand[ci] = slot;
@@ -185,9 +199,11 @@ __global__ void __launch_bounds__(ST) k_classify_lost(Dev d) {
       if (__popcll(mask) < 3) st = MSCKF_FEAT_FEW_OBS;
       else st = (d.f_flags[(size_t)f * d.Fcap + slot] & FF_INIT) ? CS_READY : CS_NEED_TRI;
       cst[ci] = st;
-      if (st == CS_NEED_TRI) d.wl_tri[atomicAdd(d.stage_ctr + SC_NTRI, 1ull)] = make_int2(f, ci);
+      want_tri = st == CS_NEED_TRI;
+      tri_idx = ci;
       d.free_stack[(size_t)f * d.Fcap + nfree0 + ci] = slot;
     }
+    wl_push_tri(d, want_tri, f, tri_idx);
     nkeep += tk;
     nlost += tl;
   }
@@ -285,12 +301,14 @@ __global__ void __launch_bounds__(ST) k_prune_select(Dev d) {
     }
     int tot;
     const int r = block_rank(c >= 2, s_warp, tot);
+    bool want_tri = false;
     if (c >= 2) {
       cand[nc + r] = slot;
       const int st = (d.f_flags[(size_t)f * d.Fcap + slot] & FF_INIT) ? CS_READY : CS_NEED_TRI;
       cst[nc + r] = st;
-      if (st == CS_NEED_TRI) d.wl_tri[atomicAdd(d.stage_ctr + SC_NTRI, 1ull)] = make_int2(f, nc + r);
+      want_tri = st == CS_NEED_TRI;
     }
+    wl_push_tri(d, want_tri, f, nc + r);
     nc += tot;
   }
   if (tid == 0) d.ncand[f] = nc;

@@ -86,6 +86,11 @@ struct msckf_ctx {
   struct FrameSlot { double* pub = nullptr; unsigned char* reset = nullptr; unsigned* err = nullptr; cudaEvent_t done = nullptr; } slot[2];
   int n_pending = 0, head = 0;
   cudaStream_t copy_st = nullptr;    // H2D of the next frame's inputs overlaps the kernels of the current one
+  // the kernel sequence of a whole frame, captured once (forks onto the auxiliary streams included) and replayed
+  cudaGraphExec_t frame_graph = nullptr;
+  bool graph_enabled = true;
+  int eager_frames = 0;              // frames run launch by launch before the capture (function attributes get set there)
+  long long graph_launches[KID_COUNT] = {};
   cudaEvent_t h2d_done = nullptr;
   KTimer kt;                        // launch counts / optional per-kernel event timing
   Lanes lanes;                      // auxiliary streams for the independent launches of one step
@@ -254,6 +259,7 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   for (auto& evn : ctx->lanes.join) CKC(cudaEventCreateWithFlags(&evn, cudaEventDisableTiming));
   CKC(cudaEventCreateWithFlags(&ctx->lanes.fork, cudaEventDisableTiming));
   ctx->lanes.enabled = getenv("MSCKF_NO_LANES") == nullptr;
+  ctx->graph_enabled = getenv("MSCKF_NO_GRAPH") == nullptr;
 
   Dev& d = ctx->d;
   memset(&d, 0, sizeof d);
@@ -349,7 +355,7 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   DA(d.T, F * (size_t)d.Tk * Tld(d)); DA(d.S, F * (size_t)d.Tk * d.Tk); DA(d.dx, F * (size_t)d.nmax);
   DA(d.log_id, 2 * F * Fc); DA(d.log_status, 2 * F * Fc); DA(d.log_gamma, 2 * F * Fc); DA(d.log_dof, 2 * F * Fc);
   DA(d.log_n, 2 * F); DA(d.log_upd, 2 * F * 2); DA(d.log_rm, F * 2);
-  DA(d.counters, F * NCNT); DA(d.err, 8); DA(d.did_reset, F); DA(d.imu_pub, F * IMU_STRIDE);
+  DA(d.frame_in, 1); DA(d.counters, F * NCNT); DA(d.err, 8); DA(d.did_reset, F); DA(d.imu_pub, F * IMU_STRIDE);
 #undef DA
   CKC(cudaMallocHost((void**)&ctx->h_pub, F * IMU_STRIDE * sizeof(double)));
   CKC(cudaMallocHost((void**)&ctx->h_reset, F));
@@ -397,6 +403,7 @@ void msckf_destroy(msckf_ctx* ctx) {
   for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
   ctx->kt.release();
   for (auto& e : ctx->mark) if (e) cudaEventDestroy(e);
+  if (ctx->frame_graph) cudaGraphExecDestroy(ctx->frame_graph);
   for (auto& s : ctx->lanes.aux) if (s) { cudaStreamSynchronize(s); cudaStreamDestroy(s); }
   for (auto& e : ctx->lanes.join) if (e) cudaEventDestroy(e);
   if (ctx->lanes.fork) cudaEventDestroy(ctx->lanes.fork);
@@ -766,6 +773,63 @@ int msckf_reset(msckf_ctx* ctx, int32_t f) {
   return MSCKF_OK;
 }
 
+__global__ void k_set_frame_in(FrameIn* dst, FrameIn v) { *dst = v; }
+
+static void enqueue_frame_eager(msckf_ctx* ctx, const FrameIn& in, const FrameIn* fin) {
+  const Dev& d = ctx->d;
+  const bool tm = ctx->timing && !fin;
+  if (tm) cudaEventRecord(ctx->ev[0], ctx->st);
+  launch_propagate(d, in.imu_off, in.ts, in.gyro, in.acc, ctx->st, fin);
+  launch_augment(d, in.cam_ids, ctx->st, fin);
+  if (tm) cudaEventRecord(ctx->ev[1], ctx->st);
+  launch_observe(d, in.feat_off, in.ids, in.uv, ctx->st, fin);
+  if (tm) cudaEventRecord(ctx->ev[2], ctx->st);
+  enqueue_lost_stage(ctx);
+  if (tm) cudaEventRecord(ctx->ev[3], ctx->st);
+  enqueue_prune_stage(ctx);
+  if (tm) cudaEventRecord(ctx->ev[4], ctx->st);
+  launch_finish_frame(d, 1, ctx->st);
+  if (tm) cudaEventRecord(ctx->ev[5], ctx->st);
+}
+
+// One frame's kernels on the context stream.  After two eager frames the sequence is captured into a CUDA graph whose
+// message-consuming kernels read their pointers from d.frame_in; from then on a frame is one tiny kernel that stores
+// the pointers plus one graph launch.  Stage timing / per-kernel timing run eagerly.
+static int enqueue_frame(msckf_ctx* ctx, const FrameIn& in) {
+  const Dev& d = ctx->d;
+  const bool use_graph = ctx->graph_enabled && !ctx->timing && !ctx->kt.timing;
+  if (!use_graph || ctx->eager_frames < 2) {
+    ctx->eager_frames += 1;
+    enqueue_frame_eager(ctx, in, nullptr);
+    return MSCKF_OK;
+  }
+  k_set_frame_in<<<1, 1, 0, ctx->st>>>(d.frame_in, in);
+  if (!ctx->frame_graph) {
+    long long before[KID_COUNT];
+    memcpy(before, ctx->kt.launches, sizeof before);
+    cudaGraph_t g = nullptr;
+    CK(cudaStreamBeginCapture(ctx->st, cudaStreamCaptureModeRelaxed));
+    enqueue_frame_eager(ctx, in, d.frame_in);
+    cudaError_t e = cudaStreamEndCapture(ctx->st, &g);
+    for (int i = 0; i < KID_COUNT; ++i) {
+      ctx->graph_launches[i] = ctx->kt.launches[i] - before[i];
+      ctx->kt.launches[i] = before[i];
+    }
+    if (e != cudaSuccess || !g || cudaGraphInstantiate(&ctx->frame_graph, g, 0) != cudaSuccess) {
+      cudaGetLastError();
+      if (g) cudaGraphDestroy(g);
+      ctx->frame_graph = nullptr;
+      ctx->graph_enabled = false;                   // capture not possible here: stay with plain launches
+      enqueue_frame_eager(ctx, in, nullptr);
+      return MSCKF_OK;
+    }
+    cudaGraphDestroy(g);
+  }
+  CK(cudaGraphLaunch(ctx->frame_graph, ctx->st));
+  for (int i = 0; i < KID_COUNT; ++i) ctx->kt.launches[i] += ctx->graph_launches[i];
+  return MSCKF_OK;
+}
+
 int msckf_feature_callback_async(msckf_ctx* ctx, const int32_t* imu_off, const double* ts, const double* gyro, const double* acc,
                                  const int64_t* cam_ids, const int32_t* feat_off, const int64_t* ids, const double* uv) {
   if (!ctx) return MSCKF_ERR_ARG;
@@ -784,19 +848,11 @@ int msckf_feature_callback_async(msckf_ctx* ctx, const int32_t* imu_off, const d
   int rc = stage_commit(ctx, p, true);
   if (rc) return rc;
   char* b = p.s->d;
-  const bool tm = ctx->timing;
-  if (tm) cudaEventRecord(ctx->ev[0], ctx->st);
-  launch_propagate(d, (const int*)(b + o0), (const double*)(b + o1), (const double*)(b + o2), (const double*)(b + o3), ctx->st);
-  launch_augment(d, (const long long*)(b + o4), ctx->st);
-  if (tm) cudaEventRecord(ctx->ev[1], ctx->st);
-  launch_observe(d, (const int*)(b + o5), (const long long*)(b + o6), (const double*)(b + o7), ctx->st);
-  if (tm) cudaEventRecord(ctx->ev[2], ctx->st);
-  enqueue_lost_stage(ctx);
-  if (tm) cudaEventRecord(ctx->ev[3], ctx->st);
-  enqueue_prune_stage(ctx);
-  if (tm) cudaEventRecord(ctx->ev[4], ctx->st);
-  launch_finish_frame(d, 1, ctx->st);
-  if (tm) cudaEventRecord(ctx->ev[5], ctx->st);
+  FrameIn in;
+  in.imu_off = (const int*)(b + o0); in.ts = (const double*)(b + o1); in.gyro = (const double*)(b + o2); in.acc = (const double*)(b + o3);
+  in.cam_ids = (const long long*)(b + o4); in.feat_off = (const int*)(b + o5); in.ids = (const long long*)(b + o6); in.uv = (const double*)(b + o7);
+  rc = enqueue_frame(ctx, in);
+  if (rc) return rc;
   stage_end(ctx, p);
   msckf_ctx::FrameSlot& fs = ctx->slot[(ctx->head + ctx->n_pending) & 1];
   CK(cudaMemcpyAsync(fs.pub, d.imu_pub, (size_t)F * IMU_STRIDE * sizeof(double), cudaMemcpyDeviceToHost, ctx->st));
@@ -816,12 +872,11 @@ int msckf_feature_callback_dev(msckf_ctx* ctx, const int32_t* imu_off, const dou
   ARG(ctx->n_pending == 0, "previous frame not collected");
   CK(cudaSetDevice(ctx->device));
   const Dev& d = ctx->d;
-  launch_propagate(d, imu_off, ts, gyro, acc, ctx->st);
-  launch_augment(d, (const long long*)cam_ids, ctx->st);
-  launch_observe(d, feat_off, (const long long*)ids, uv, ctx->st);
-  enqueue_lost_stage(ctx);
-  enqueue_prune_stage(ctx);
-  launch_finish_frame(d, 1, ctx->st);
+  FrameIn in;
+  in.imu_off = imu_off; in.ts = ts; in.gyro = gyro; in.acc = acc;
+  in.cam_ids = (const long long*)cam_ids; in.feat_off = feat_off; in.ids = (const long long*)ids; in.uv = uv;
+  int rc = enqueue_frame(ctx, in);
+  if (rc) return rc;
   if (imu_out_dev)
     CK(cudaMemcpyAsync(imu_out_dev, d.imu_pub, (size_t)d.F * IMU_STRIDE * sizeof(double), cudaMemcpyDeviceToDevice, ctx->st));
   CK(cudaGetLastError());

@@ -184,8 +184,9 @@ __device__ void build_phi(const double* x0, const double* x1, const double* qn, 
 // The IMU-camera cross covariance only needs that product, applied once at the end (identical algebra:
 // P_IC <- Phi_k ... Phi_1 P_IC; symmetrising it is exact).
 __global__ void __launch_bounds__(PW * 32, 4) k_propagate(Dev d, const int* __restrict__ imu_off, const double* __restrict__ ts,
-                                                        const double* __restrict__ gyro_m, const double* __restrict__ acc_m) {
+                                                        const double* __restrict__ gyro_m, const double* __restrict__ acc_m, const FrameIn* fin) {
   extern __shared__ double psm[];
+  if (fin) { imu_off = fin->imu_off; ts = fin->ts; gyro_m = fin->gyro; acc_m = fin->acc; }
   constexpr int NT = PW * 32;
   const int lane = threadIdx.x;            // index inside the filter's CTA
   const int wrp = lane >> 5, g = (lane & 31) >> 2, tg = lane & 3;   // warp, DMMA fragment coordinates
@@ -373,7 +374,8 @@ __global__ void __launch_bounds__(PW * 32, 4) k_propagate(Dev d, const int* __re
 
 // ------------------------------------------------------------------ state augmentation
 // msckf.py:385-407 + jit_utils.py:137-167.  One CTA per filter.
-__global__ void __launch_bounds__(PT) k_augment(Dev d, const long long* __restrict__ new_ids) {
+__global__ void __launch_bounds__(PT) k_augment(Dev d, const long long* __restrict__ new_ids, const FrameIn* fin) {
+  if (fin) new_ids = fin->cam_ids;
   const int f = blockIdx.x, tid = threadIdx.x;
   const int N = d.ncam[f];
   if (N >= d.Nmax) {
@@ -568,16 +570,18 @@ __global__ void __launch_bounds__(PT) k_remove_cams(Dev d) {
 }
 
 // ------------------------------------------------------------------ launchers
-void launch_propagate(const Dev& d, const int* imu_off, const double* ts, const double* gyro, const double* acc, cudaStream_t st) {
+void launch_propagate(const Dev& d, const int* imu_off, const double* ts, const double* gyro, const double* acc, cudaStream_t st, const FrameIn* fin) {
   static bool attr_set = false;
   const size_t smem = (size_t)PROP_DOUBLES * sizeof(double);
   if (!attr_set) {
     cudaFuncSetAttribute(k_propagate, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     attr_set = true;
   }
-  KLAUNCH(d, KID_PROPAGATE, st, (k_propagate<<<d.F, PW * 32, smem, st>>>(d, imu_off, ts, gyro, acc)));
+  KLAUNCH(d, KID_PROPAGATE, st, (k_propagate<<<d.F, PW * 32, smem, st>>>(d, imu_off, ts, gyro, acc, fin)));
 }
-void launch_augment(const Dev& d, const long long* ids, cudaStream_t st) { KLAUNCH(d, KID_AUGMENT, st, (k_augment<<<d.F, PT, 0, st>>>(d, ids))); }
+void launch_augment(const Dev& d, const long long* ids, cudaStream_t st, const FrameIn* fin) {
+  KLAUNCH(d, KID_AUGMENT, st, (k_augment<<<d.F, PT, 0, st>>>(d, ids, fin)));
+}
 void launch_finish_frame(const Dev& d, int do_reset_check, cudaStream_t st) {
   KLAUNCH(d, KID_FINISH_FRAME, st, (k_finish_frame<<<d.F, PT, 0, st>>>(d, do_reset_check)));
 }

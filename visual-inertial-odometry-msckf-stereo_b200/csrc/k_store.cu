@@ -65,7 +65,8 @@ __device__ __forceinline__ unsigned hash64(long long k) {
 
 // ------------------------------------------------------------------ add_feature_observations (msckf.py:409-427)
 __global__ void __launch_bounds__(ST) k_observe(Dev d, const int* __restrict__ feat_off, const long long* __restrict__ ids,
-                                                 const double* __restrict__ uv) {
+                                                 const double* __restrict__ uv, const FrameIn* fin) {
+  if (fin) { feat_off = fin->feat_off; ids = fin->ids; uv = fin->uv; }
   const int f = blockIdx.x, tid = threadIdx.x;
   __shared__ int s_warp[ST / 32];
   __shared__ int s_tracked;
@@ -518,8 +519,8 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
   }
 }
 
-void launch_observe(const Dev& d, const int* feat_off, const long long* ids, const double* uv, cudaStream_t st) {
-  KLAUNCH(d, KID_OBSERVE, st, (k_observe<<<d.F, ST, 0, st>>>(d, feat_off, ids, uv)));
+void launch_observe(const Dev& d, const int* feat_off, const long long* ids, const double* uv, cudaStream_t st, const FrameIn* fin) {
+  KLAUNCH(d, KID_OBSERVE, st, (k_observe<<<d.F, ST, 0, st>>>(d, feat_off, ids, uv, fin)));
 }
 void launch_classify_lost(const Dev& d, cudaStream_t st) {
   KLAUNCH(d, KID_CLASSIFY_LOST, st, (k_classify_lost<<<d.F, ST, 0, st>>>(d)));

@@ -56,6 +56,13 @@ struct Params {
   int row_cap;             // msckf.py:678
 };
 
+// Message pointers of the frame being processed (device addresses).  The kernels that consume the message read them
+// from here when the frame runs as a replayed CUDA graph: the graph is static, only this block changes per frame.
+struct FrameIn {
+  const int* imu_off; const double* ts; const double* gyro; const double* acc;
+  const long long* cam_ids; const int* feat_off; const long long* ids; const double* uv;
+};
+
 // Everything a kernel needs, passed by value.
 struct Dev {
   int F, Nmax, nmax, ld, Fcap, Hs;
@@ -145,6 +152,7 @@ struct Dev {
   unsigned* err;           // [1] error bits, followed by [7] ints of detail about the first numeric failure
   unsigned char* did_reset;        // [F]
   double* imu_pub;         // [F][IMU_STRIDE] snapshot for publish()
+  FrameIn* frame_in;       // [1] device copy of the current frame's message pointers (graph replay)
   void* host_timer;        // KTimer* of the owning context (host only; never dereferenced on the device)
   void* host_lanes;        // Lanes* of the owning context (host only): auxiliary streams for independent launches of one step
 };

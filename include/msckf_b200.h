@@ -206,6 +206,10 @@ int msckf_get_stage_log(msckf_ctx* ctx, int32_t filter, int32_t stage, int32_t* 
                         int32_t* update_rows, int32_t* update_cols, int64_t* removed_cam_ids);
 /* Counters since creation, per filter: counters[F][MSCKF_N_COUNTERS] (MSCKF_CNT_* above). */
 int msckf_get_counters(msckf_ctx* ctx, int64_t* counters);
+/* Shapes of the most recent measurement update of every filter (the last stage that ran): shapes[F][4] =
+ * stacked rows m, active columns n_a, rows after compression k = min(m, n_a) (msckf.py:549-556), and the kernel
+ * path taken (0 none, 2 tiled kernels, 5 + c one-CTA tensor-pipe class c).  Diagnostic: tests and profiling. */
+int msckf_get_update_shapes(msckf_ctx* ctx, int32_t* shapes);
 
 /* ---- directly callable pieces of the reference API ---------------------------------------- */
 

@@ -286,11 +286,12 @@ def test_two_frames_in_flight_equal_sequential():
         assert np.array_equal(outs['blocking'][1][k], outs['pipelined'][1][k])
 
 
-@pytest.mark.parametrize('knob', ['MSCKF_NO_DMMA', 'MSCKF_NO_LANES', 'MSCKF_NO_JAC_ROWS'])
+@pytest.mark.parametrize('knob', ['MSCKF_NO_DMMA', 'MSCKF_NO_LANES', 'MSCKF_NO_JAC_ROWS', 'MSCKF_NO_QR_TALL', 'MSCKF_NO_GRAPH'])
 def test_alternative_kernel_paths(knob, monkeypatch):
     """The library's debugging knobs route the same work through its other kernels: the tiled update kernels instead of
     the one-CTA DMMA update (the path wide windows take), in-order launches instead of concurrent size classes, the
-    group-per-landmark Jacobian kernel instead of the lane-per-row one.  Each must pass the same stepped comparison."""
+    group-per-landmark Jacobian kernel instead of the lane-per-row one, the blocked tensor-pipe QR instead of the
+    tall-skinny TSQR for the pruning stacks, eager launches instead of the captured frame graph.  Each must pass the same stepped comparison."""
     monkeypatch.setenv(knob, '1')
     n_frames = 40
     stream = synth.make_stream(n_frames, 120, structure_seed=6, noise_seed=21)

@@ -92,6 +92,7 @@ SIGNATURES = {
     'msckf_feature_callback_dev': [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     'msckf_get_stage_log': [_P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P],
     'msckf_get_counters': [_P, _P],
+    'msckf_get_update_shapes': [_P, _P],
     'msckf_triangulate': [_P, _I, _P, _P, _P, _P, _P, _P, _P],
     'msckf_initialize_position': [_P, _I, _P, _P, _P, _P, _P, _P, _P],
     'msckf_check_motion': [_P, _I, _P, _P, _P, _P, _P],
@@ -408,6 +409,11 @@ class Context(object):
     def counters(self):
         out = np.zeros((self.F, N_COUNTERS), dtype=np.int64)
         self._ck(self.lib.msckf_get_counters(self.h, _ptr(out)))
+        return out
+
+    def update_shapes(self):
+        out = np.zeros((self.F, 4), dtype=np.int32)
+        self._ck(self.lib.msckf_get_update_shapes(self.h, _ptr(out)))
         return out
 
     def feature_callback_dev(self, imu_off, ts, gyro, acc, cam_ids, feat_off, ids, uv, imu_out=0):

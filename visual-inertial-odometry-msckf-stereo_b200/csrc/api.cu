@@ -14,7 +14,7 @@ using namespace msckf;
 namespace msckf {
 const char* const kKernelNames[KID_COUNT] = {
     "k_propagate", "k_augment", "k_cam_prepare", "k_observe", "k_classify_lost", "k_prune_select", "k_triangulate", "k_plan_items",
-    "k_jacobian_gate", "k_jacobian_rows", "k_jacobian_big", "k_plan_stack", "k_qr", "k_qr_d16", "k_qr_d32", "k_qr_d48", "k_qr_d64", "k_upd_dmma16", "k_upd_dmma32", "k_upd_dmma48", "k_upd_dmma64", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
+    "k_jacobian_gate", "k_jacobian_rows", "k_jacobian_big", "k_plan_stack", "k_qr", "k_qr_tall", "k_qr_d16", "k_qr_d32", "k_qr_d48", "k_qr_d64", "k_upd_dmma16", "k_upd_dmma32", "k_upd_dmma48", "k_upd_dmma64", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
     "k_upd_downdate", "k_remove_cams", "k_finish_frame", "k_reset", "misc"};
 
 void KTimer::begin(int id, cudaStream_t st) {
@@ -258,6 +258,7 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   for (auto& s : ctx->lanes.aux) CKC(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
   for (auto& evn : ctx->lanes.join) CKC(cudaEventCreateWithFlags(&evn, cudaEventDisableTiming));
   CKC(cudaEventCreateWithFlags(&ctx->lanes.fork, cudaEventDisableTiming));
+  CKC(cudaEventCreateWithFlags(&ctx->lanes.built, cudaEventDisableTiming));
   ctx->lanes.enabled = getenv("MSCKF_NO_LANES") == nullptr;
   ctx->graph_enabled = getenv("MSCKF_NO_GRAPH") == nullptr;
 
@@ -302,6 +303,7 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
       d.rowmap_cap = (int)(row_cap > 0 ? std::min(all, capped) : all);
     }
     d.jac_rows_ok = getenv("MSCKF_NO_JAC_ROWS") ? 0 : 1;
+    d.qr_tall_ok = getenv("MSCKF_NO_QR_TALL") ? 0 : 1;
     {
       const int kc[UPD_DMMA_CLASSES] = {16, 32, 48, 64};
       for (int c = 0; c < UPD_DMMA_CLASSES; ++c)      // MSCKF_NO_DMMA: debugging knob, every update through the tiled kernels
@@ -351,7 +353,7 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   if (d.qr_scratch_stride) DA(d.qr_scratch, F * (size_t)d.qr_scratch_stride);
   DA(d.Adense, (size_t)d.Adense_elems);
   DA(d.A, F * (size_t)d.A_elems); DA(d.m_rows, F); DA(d.m_pad, F); DA(d.n_act, F); DA(d.k_rows, F); DA(d.colmap, F * (size_t)d.nmax); DA(d.upd_path, F); DA(d.wl_upd_big, F); DA(d.wl_upd_dmma, (size_t)UPD_DMMA_CLASSES * F);
-  DA(d.rowmap, F * (size_t)d.rowmap_cap); DA(d.qr_cls, F); DA(d.wl_qr, (size_t)QR_DMMA_CLASSES * F);
+  DA(d.rowmap, F * (size_t)d.rowmap_cap); DA(d.qr_cls, F); DA(d.wl_qr, (size_t)QR_DMMA_CLASSES * F); DA(d.wl_qrb, F); DA(d.wl_qrt, F);
   DA(d.T, F * (size_t)d.Tk * Tld(d)); DA(d.S, F * (size_t)d.Tk * d.Tk); DA(d.dx, F * (size_t)d.nmax);
   DA(d.log_id, 2 * F * Fc); DA(d.log_status, 2 * F * Fc); DA(d.log_gamma, 2 * F * Fc); DA(d.log_dof, 2 * F * Fc);
   DA(d.log_n, 2 * F); DA(d.log_upd, 2 * F * 2); DA(d.log_rm, F * 2);
@@ -407,6 +409,7 @@ void msckf_destroy(msckf_ctx* ctx) {
   for (auto& s : ctx->lanes.aux) if (s) { cudaStreamSynchronize(s); cudaStreamDestroy(s); }
   for (auto& e : ctx->lanes.join) if (e) cudaEventDestroy(e);
   if (ctx->lanes.fork) cudaEventDestroy(ctx->lanes.fork);
+  if (ctx->lanes.built) cudaEventDestroy(ctx->lanes.built);
   if (ctx->h_pub) cudaFreeHost(ctx->h_pub);
   if (ctx->h_reset) cudaFreeHost(ctx->h_reset);
   if (ctx->h_err) cudaFreeHost(ctx->h_err);
@@ -667,7 +670,7 @@ static void enqueue_lost_stage(msckf_ctx* ctx) {
   launch_plan_items(d, 0, ctx->st);
   launch_jacobian_gate(d, 0xE, 1, 0, ctx->st);            // lost landmarks have at least three observations
   launch_plan_stack(d, 0, ctx->st);
-  launch_compress_update(d, ctx->st);
+  launch_compress_update(d, 0, ctx->st);
 }
 static void enqueue_prune_stage(msckf_ctx* ctx) {
   const Dev& d = ctx->d;
@@ -681,7 +684,7 @@ static void enqueue_prune_stage(msckf_ctx* ctx) {
   launch_plan_items(d, 1, ctx->st);
   launch_jacobian_gate(d, 0x1, 0, 0, ctx->st);            // the pruning update always involves exactly two camera states
   launch_plan_stack(d, 1, ctx->st);
-  launch_compress_update(d, ctx->st);
+  launch_compress_update(d, 1, ctx->st);
   launch_remove_cams(d, ctx->st);
 }
 
@@ -957,6 +960,21 @@ int msckf_get_counters(msckf_ctx* ctx, int64_t* counters) {
   int rc = sync_and_check(ctx);
   if (rc) return rc;
   CK(cudaMemcpy(counters, ctx->d.counters, (size_t)ctx->d.F * NCNT * sizeof(int64_t), cudaMemcpyDeviceToHost));
+  return MSCKF_OK;
+}
+
+int msckf_get_update_shapes(msckf_ctx* ctx, int32_t* shapes) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  ARG(shapes, "pointer");
+  CK(cudaSetDevice(ctx->device));
+  int rc = sync_and_check(ctx);
+  if (rc) return rc;
+  const size_t F = (size_t)ctx->d.F;
+  std::vector<int32_t> tmp(4 * F);
+  const int* src[4] = {ctx->d.m_rows, ctx->d.n_act, ctx->d.k_rows, ctx->d.upd_path};
+  for (int a = 0; a < 4; ++a) CK(cudaMemcpy(tmp.data() + a * F, src[a], F * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  for (size_t f = 0; f < F; ++f)
+    for (int a = 0; a < 4; ++a) shapes[4 * f + a] = tmp[a * F + f];
   return MSCKF_OK;
 }
 

@@ -485,7 +485,12 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
     int qcls = -1;
     if (m > 0) {
       qcls = (m <= na || na + 1 > 64) ? QR_DMMA_CLASSES : (na + 1 <= 16 ? 0 : (na + 1 <= 32 ? 1 : (na + 1 <= 48 ? 2 : 3)));
-      if (qcls < QR_DMMA_CLASSES) d.wl_qr[(size_t)qcls * d.F + atomicAdd(d.stage_ctr + SC_NQR + qcls, 1ull)] = f;
+      // pruning stage: every landmark sits on the two cameras being removed (5 rows x 12 columns each): tall-skinny TSQR
+      if (stage == 1 && qcls == 0 && na == 12 && d.qr_tall_ok) {
+        qcls = QR_DMMA_CLASSES + 1;
+        d.wl_qrt[atomicAdd(d.stage_ctr + SC_NQR_TALL, 1ull)] = f;
+      } else if (qcls < QR_DMMA_CLASSES) d.wl_qr[(size_t)qcls * d.F + atomicAdd(d.stage_ctr + SC_NQR + qcls, 1ull)] = f;
+      else d.wl_qrb[atomicAdd(d.stage_ctr + SC_NQR_BUILD, 1ull)] = f;
     }
     d.qr_cls[f] = qcls;
     d.m_rows[f] = m;

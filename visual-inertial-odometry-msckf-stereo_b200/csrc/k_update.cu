@@ -42,9 +42,8 @@ __device__ __forceinline__ double record_elem(const double* rec, int M, unsigned
   return rec[li * ldr + 6 * a + e6];
 }
 
-__global__ void __launch_bounds__(QT) k_qr_build(Dev d, int smem_doubles) {
-  extern __shared__ double sm[];
-  const int f = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+__device__ void qr_build_body(const Dev& d, int f, int smem_doubles, double* sm) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int m = d.m_rows[f];
   if (m == 0 || d.qr_cls[f] != QR_DMMA_CLASSES) return;   // compressed updates of up to 64 columns go through k_qr_dmma
   const int na = d.n_act[f], nc = na + 1, k = d.k_rows[f], mp = d.m_pad[f], ni = d.nitem[f];
@@ -187,6 +186,15 @@ __global__ void __launch_bounds__(QT) k_qr_build(Dev d, int smem_doubles) {
   for (int e = tid; e < na * nc; e += QT) {
     const int i = e % na, c = e / na;
     A[(size_t)c * mp + i] = (c >= i) ? Rp[qr_row_off(i, na) + c - i] : 0.0;
+  }
+}
+// Persistent grid over the filters k_plan_stack queued in wl_qrb (a few per cent of the updates at the headline workload).
+__global__ void __launch_bounds__(QT) k_qr_build(Dev d, int smem_doubles) {
+  extern __shared__ double sm[];
+  const int nlist = (int)d.stage_ctr[SC_NQR_BUILD];
+  for (int w = blockIdx.x; w < nlist; w += gridDim.x) {
+    qr_build_body(d, d.wl_qrb[w], smem_doubles, sm);
+    __syncthreads();
   }
 }
 
@@ -531,30 +539,40 @@ __global__ void k_zero_krows_except(Dev d, int keep) {
 
 void launch_qr_build(const Dev& d, cudaStream_t st) {
   static bool attr_set = false;
+  static int sms = 0;
   if (!attr_set) {
     cudaFuncSetAttribute(k_qr_build, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+    sms = sm_count();
     attr_set = true;
   }
-  KLAUNCH(d, KID_QR, st, (k_qr_build<<<d.F, QT, (size_t)d.qr_smem_doubles * sizeof(double), st>>>(d, d.qr_smem_doubles)));
+  KLAUNCH(d, KID_QR, st, (k_qr_build<<<std::min(d.F, 2 * sms), QT, (size_t)d.qr_smem_doubles * sizeof(double), st>>>(d, d.qr_smem_doubles)));
 }
 void launch_qr_all(const Dev& d, cudaStream_t st) {
   Fork fk(d, st);
   launch_qr_dmma(d, fk);
   launch_qr_build(d, fk.lane(4));
 }
-void launch_compress_update(const Dev& d, cudaStream_t st) {
-  launch_qr_build(d, st);                       // wide / uncompressed stacks first: their updates may sit in any class
+void launch_compress_update(const Dev& d, int stage, cudaStream_t st) {
   bool all_ok = true;
   for (int c = 0; c < UPD_DMMA_CLASSES; ++c) all_ok = all_ok && d.upd_dmma_ok[c];
+  // the pruning stage only ever stacks landmarks on the two cameras being removed: n_a = 12, class 0 (or uncompressed)
+  const int ncls = (stage == 1) ? 1 : QR_DMMA_CLASSES;
   {
     Fork fk(d, st);
-    for (int c = 0; c < QR_DMMA_CLASSES; ++c) {   // class c: compression, then its update, back to back on one stream
+    // wide / uncompressed stacks on their own lane, next to the tensor-pipe compression classes; their updates may sit in
+    // any class, so every class's update waits for this lane (event `built`)
+    cudaStream_t sb = fk.lane(4);
+    launch_qr_build(d, sb);
+    if (fk.on) cudaEventRecord(fk.L->built, sb);
+    for (int c = 0; c < ncls; ++c) {              // class c: compression, then its update, back to back on one stream
       cudaStream_t s = fk.lane(c);
+      if (c == 0 && stage == 1 && d.qr_tall_ok) launch_qr_tall(d, s);
       launch_qr_dmma_class(d, c, s);
+      if (fk.on && s != sb) cudaStreamWaitEvent(s, fk.L->built, 0);
       launch_upd_dmma_class(d, c, s);
     }
     // the tiled update only takes stacks k_qr_build compressed when every one-CTA class is available ...
-    if (all_ok) launch_update_tiled(d, fk.lane(4));
+    if (all_ok && stage != 1) launch_update_tiled(d, sb);
   }
   // ... otherwise it also takes filters of a k_qr_dmma class (window too wide for the class's shared memory): after the join
   if (!all_ok) launch_update_tiled(d, st);

@@ -30,7 +30,7 @@ constexpr unsigned ERRBIT_NOT_SPD = 8u;
 constexpr unsigned ERRBIT_CAM_CAP = 16u;
 
 // per-stage device counters (one memset per stage): pool bump pointer and work-list lengths
-constexpr int SC_POOL = 0, SC_NTRI = 1, SC_NJAC_BIG = 2, SC_NUPD_BIG = 3, SC_NJAC_SMALL = 4 /* .. 7: one per size class */, SC_NQR = 12 /* .. 15: tensor-pipe QR classes */, SC_NUPD_DMMA = 16 /* .. 19: tensor-pipe update classes */, SC_COUNT = 24;
+constexpr int SC_POOL = 0, SC_NTRI = 1, SC_NJAC_BIG = 2, SC_NUPD_BIG = 3, SC_NJAC_SMALL = 4 /* .. 7: one per size class */, SC_NQR = 12 /* .. 15: tensor-pipe QR classes */, SC_NUPD_DMMA = 16 /* .. 19: tensor-pipe update classes */, SC_NQR_BUILD = 20 /* wide / uncompressed stacks (k_qr_build) */, SC_NQR_TALL = 21 /* pruning stacks (k_qr_tall) */, SC_COUNT = 24;
 // stacked-Jacobian compression classes: 0..3 = compressed (m > n_a) with n_a + 1 <= 16 / 32 / 48 / 64 columns (k_qr_dmma), 4 = general CTA kernel
 constexpr int QR_DMMA_CLASSES = 4;
 // one-CTA tensor-pipe update classes, aligned with the compression classes: max(k, n_a) + 1 <= 16 / 32 / 48 / 64
@@ -133,6 +133,9 @@ struct Dev {
   int rowmap_cap;
   int* qr_cls;             // [F] compression class of this stage's stacked Jacobian (-1: nothing to do)
   int* wl_qr;              // [QR_DMMA_CLASSES][F] filters of the tensor-pipe QR classes
+  int* wl_qrt;             // [F] filters whose pruning stack (n_a = 12, every landmark on the same two cameras) goes through k_qr_tall
+  int qr_tall_ok;          // 0: debugging knob MSCKF_NO_QR_TALL, those stacks take k_qr_dmma class 0
+  int* wl_qrb;             // [F] filters whose stack goes through k_qr_build (wider than 64 columns, or not compressed)
   int* upd_path;           // [F] 0 = no update, 2 = tiled kernels (queued in wl_upd_big), 5 + c = DMMA kernel of class c
   int* wl_upd_big;         // [F]
   int* wl_upd_dmma;        // [UPD_DMMA_CLASSES][F] filters of the tensor-pipe update classes

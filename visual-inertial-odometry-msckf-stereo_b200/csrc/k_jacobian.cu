@@ -583,8 +583,14 @@ void launch_jacobian_gate(const Dev& d, int class_mask, int with_big, int write_
     if (d.jac_rows_ok) launch_jacobian_rows(d, 0, write_all, fk.lane(0));
     else launch_small<8>(d, 0, write_all, fk.lane(0));
   }
-  if (class_mask & 2) launch_small<16>(d, 1, write_all, fk.lane(1));
-  if (class_mask & 4) launch_small<32>(d, 2, write_all, fk.lane(2));
+  if (class_mask & 2) {
+    if (d.jac_rows_ok) launch_jacobian_rows(d, 1, write_all, fk.lane(1));
+    else launch_small<16>(d, 1, write_all, fk.lane(1));
+  }
+  if (class_mask & 4) {
+    if (d.jac_rows_ok) launch_jacobian_rows(d, 2, write_all, fk.lane(2));
+    else launch_small<32>(d, 2, write_all, fk.lane(2));
+  }
   if (class_mask & 8) launch_small<32>(d, 3, write_all, fk.lane(3));
   if (with_big) {
     st = fk.lane(4);

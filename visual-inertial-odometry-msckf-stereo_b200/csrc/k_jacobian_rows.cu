@@ -73,8 +73,12 @@ __device__ __forceinline__ void jr_row(const double* __restrict__ pre, const dou
 }
 
 
+// registers: the projected row (6M), its product with Pcc (6M) and the row of S (4M-3) live in registers per lane
+template <int M>
+constexpr int jr_ctas_per_sm() { return M == 2 ? 6 : (M == 3 ? 4 : 3); }
+
 template <int M, int G>
-__global__ void __launch_bounds__(JR_T, 6) k_jacobian_rows(Dev d, int cls, int write_all) {
+__global__ void __launch_bounds__(JR_T, jr_ctas_per_sm<M>()) k_jacobian_rows(Dev d, int cls, int write_all) {
   constexpr int R4 = 4 * M, C6 = 6 * M, R = R4 - 3, LDR = C6 + 1, GPW = 32 / G, GD = jr_group_doubles<M>();
   static_assert(R4 <= G, "one lane per row");
   extern __shared__ __align__(16) double jsm[];
@@ -91,10 +95,17 @@ __global__ void __launch_bounds__(JR_T, 6) k_jacobian_rows(Dev d, int cls, int w
   const bool rowv = r < R4;                                // lanes beyond the 4M rows are padding
   const int a = rowv ? (r >> 2) : 0, q = r & 3;
   const int ii = r - 3;                                    // index of the projected row (rows 0..2 are eliminated)
-  const int stride = gridDim.x * (JR_T / 32) * GPW;
-  for (int w0 = (blockIdx.x * (JR_T / 32) + warp) * GPW; w0 < n; w0 += stride) {
-    const bool active = w0 + grp < n;
-    const int2 it = wl[active ? w0 + grp : n - 1];
+  // Every group takes a contiguous piece of the work list: k_plan_items queues the landmarks of a filter next to each
+  // other, and in the pruning stage they all sit on the same two cameras, so the gathered Pcc block is reused from one
+  // landmark to the next (P does not change while this kernel runs).
+  const int ngroups = gridDim.x * (JR_T / 32) * GPW;
+  const int per = (n + ngroups - 1) / ngroups;
+  const int wbeg = ((blockIdx.x * (JR_T / 32) + warp) * GPW + grp) * per;
+  int have_f = -1;
+  unsigned long long have_lmask = 0;
+  for (int wi = 0; wi < per; ++wi) {
+    const bool active = wbeg + wi < n;
+    const int2 it = wl[active ? wbeg + wi : n - 1];
     const int f = it.x, k = it.y;
     const size_t ik = (size_t)f * d.Fcap + k;
     const int N = d.ncam[f], ld = d.ld;
@@ -134,7 +145,9 @@ __global__ void __launch_bounds__(JR_T, 6) k_jacobian_rows(Dev d, int cls, int w
       v[0] = -Hx[3]; v[1] = -Hx[4]; v[2] = -Hx[5];
     }
     // ---- Pcc into shared memory (group-cooperative gather; P is exactly symmetric)
-    {
+    if (f != have_f || lmask != have_lmask) {               // group-uniform
+      have_f = f;
+      have_lmask = lmask;
       const double* P = d.P + (size_t)f * ld * ld;
       for (int e = r; e < C6 * C6; e += G) {
         const int i = e / C6, c = e - i * C6;
@@ -270,13 +283,15 @@ static void launch_rows(const Dev& d, int cls, int write_all, cudaStream_t st) {
     sms = sm_count();
     attr_set = true;
   }
-  int per_sm = (int)std::min<size_t>(12, (220 * 1024) / (smem + 1024));
+  int per_sm = (int)std::min<size_t>(2 * jr_ctas_per_sm<M>(), (220 * 1024) / (smem + 1024));
   per_sm = std::max(per_sm, 1);
   KLAUNCH(d, KID_JACOBIAN_ROWS, st, (k_jacobian_rows<M, G><<<sms * per_sm, JR_T, smem, st>>>(d, cls, write_all)));
 }
 
 void launch_jacobian_rows(const Dev& d, int cls, int write_all, cudaStream_t st) {
   if (cls == 0) launch_rows<2, 8>(d, cls, write_all, st);
+  else if (cls == 1) launch_rows<3, 16>(d, cls, write_all, st);
+  else launch_rows<4, 16>(d, cls, write_all, st);
 }
 
 }  // namespace msckf

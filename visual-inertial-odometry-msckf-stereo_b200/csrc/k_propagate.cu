@@ -85,13 +85,14 @@ __device__ void predict_new_state(double dt, const double* gyro, const double* a
 __device__ __forceinline__ bool phi_identity_row(int i) { return !(i < 3 || (i >= 6 && i < 9) || (i >= 12 && i < 15)); }
 __device__ __forceinline__ int phi_row_width(int i) { return i < 3 ? 6 : 15; }
 
-constexpr int PW = 4;                         // warps per CTA (one CTA per filter)
-constexpr int PKC = 16;                       // IMU samples per chunk
+constexpr int PW = 2;                         // warps per CTA (one CTA per filter): small CTAs so that 7 fit on an SM and 1024 filters are
+                                              // all resident at once - the kernel is as long as one filter's serial RK4 chain, not two waves of it
+constexpr int PKC = 10;                       // IMU samples per chunk
 constexpr int PHC = 84;                       // doubles of one compact Phi: 8 blocks, dt, sigma_a^2 R^T R
 constexpr int PST = 24;                       // doubles of one staged sample / state: q v p | dt w a | cA sA cB sB
 constexpr int PLD = 28;                       // leading dimension of the padded 24 x 24 matrices: 12 (mod 16) doubles, conflict-free DMMA fragments
 constexpr int PMAT = 24 * PLD;
-constexpr int PROP_DOUBLES = 5 * PMAT + PKC * PHC + (PKC + 1) * PST + IMU_STRIDE + 12;
+constexpr int PROP_DOUBLES = 4 * PMAT + PKC * PHC + (PKC + 1) * PST + IMU_STRIDE + 12;
 
 __device__ __forceinline__ void pdmma(double& c0, double& c1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
@@ -183,7 +184,7 @@ __device__ void build_phi(const double* x0, const double* x1, const double* qn, 
 //   3. the CTA advances the 21x21 IMU block of P sample by sample and accumulates the product of the Phis.
 // The IMU-camera cross covariance only needs that product, applied once at the end (identical algebra:
 // P_IC <- Phi_k ... Phi_1 P_IC; symmetrising it is exact).
-__global__ void __launch_bounds__(PW * 32, 4) k_propagate(Dev d, const int* __restrict__ imu_off, const double* __restrict__ ts,
+__global__ void __launch_bounds__(PW * 32, 7) k_propagate(Dev d, const int* __restrict__ imu_off, const double* __restrict__ ts,
                                                         const double* __restrict__ gyro_m, const double* __restrict__ acc_m, const FrameIn* fin) {
   extern __shared__ double psm[];
   if (fin) { imu_off = fin->imu_off; ts = fin->ts; gyro_m = fin->gyro; acc_m = fin->acc; }
@@ -198,8 +199,7 @@ __global__ void __launch_bounds__(PW * 32, 4) k_propagate(Dev d, const int* __re
   double* sPII = sPhi + PMAT;              // IMU block of P (+ dt G Qc G^T)
   double* sT = sPII + PMAT;                // Phi (P_II + dt G Qc G^T)
   double* sAcc = sT + PMAT;                // product of the Phis of this frame
-  double* sX2 = sAcc + PMAT;               // T Phi^T before symmetrisation
-  double* sPc = sX2 + PMAT;                // [PKC][PHC] compact Phis
+  double* sPc = sAcc + PMAT;               // [PKC][PHC] compact Phis
   double* sSt = sPc + PKC * PHC;           // [PKC+1][PST]: state after sample c-1 (q v p) | sample c (dt w a)
   double* sx = sSt + (PKC + 1) * PST;
   const Params& prm = *d.prm;
@@ -213,6 +213,7 @@ __global__ void __launch_bounds__(PW * 32, 4) k_propagate(Dev d, const int* __re
     const int i = e / PLD, j = e - PLD * i;
     sPII[e] = (i < 21 && j < 21) ? P[(size_t)i * ld + j] : 0.0;
     sAcc[e] = (i == j && i < 21) ? 1.0 : 0.0;
+    sPhi[e] = (i == j && i < 21) ? 1.0 : 0.0;           // every sample rewrites the same 8 blocks + the dt diagonal; the rest stays I
   }
   __syncthreads();
 
@@ -272,12 +273,7 @@ __global__ void __launch_bounds__(PW * 32, 4) k_propagate(Dev d, const int* __re
     for (int c = 0; c < kc; ++c) {
       const double* pc = sPc + c * PHC;
       const double dt = pc[72];
-      for (int e = lane; e < PMAT; e += NT) {
-        const int i = e / PLD, j = e - PLD * i;
-        sPhi[e] = (i == j && i < 21) ? 1.0 : 0.0;
-      }
       if (lane < 12) sPII[lane * PLD + lane] += dt * prm.Qc[lane / 3];
-      __syncthreads();
       for (int e = lane; e < 72; e += NT) {
         const int blk = e / 9, r = (e % 9) / 3, cc = e % 3;
         // block -> (row block, column block): 00 01 20 21 23 40 41 43
@@ -288,54 +284,66 @@ __global__ void __launch_bounds__(PW * 32, 4) k_propagate(Dev d, const int* __re
       if (lane < 3) sPhi[PLD * (12 + lane) + 6 + lane] = 1.0 * dt;
       __syncthreads();
       // T = Phi M (tiles 0..8) and Phi_acc' = Phi Phi_acc (tiles 9..17, kept in registers until the old one has been read)
-      double na0[3], na1[3];
+      constexpr int UT = (18 + PW - 1) / PW, U0 = (10 - PW + PW - 1) / PW, UX = (9 + PW - 1) / PW;   // job rounds; first round with a Phi_acc tile
+      // all accumulators first, stores afterwards: the rounds are independent DMMA chains the scheduler can interleave
+      double ac0[UT], ac1[UT];
 #pragma unroll
-      for (int u = 0; u < 5; ++u) {
+      for (int u = 0; u < UT; ++u) {
         const int job = wrp + PW * u;
+        ac0[u] = 0.0;
+        ac1[u] = 0.0;
         if (job < 18) {
           const int t = job % 9, it = t / 3, jt = t - 3 * it;
           const double* B = (job < 9) ? sPII : sAcc;
-          double c0v = 0.0, c1v = 0.0;
 #pragma unroll
           for (int ks = 0; ks < 6; ++ks)
-            pdmma(c0v, c1v, sPhi[(8 * it + g) * PLD + 4 * ks + tg], B[(4 * ks + tg) * PLD + 8 * jt + g]);
-          if (job < 9) {
-            sT[(8 * it + g) * PLD + 8 * jt + 2 * tg] = c0v;
-            sT[(8 * it + g) * PLD + 8 * jt + 2 * tg + 1] = c1v;
-          } else {
-            na0[(u - 2) < 0 ? 0 : (u - 2)] = c0v;
-            na1[(u - 2) < 0 ? 0 : (u - 2)] = c1v;
+            pdmma(ac0[u], ac1[u], sPhi[(8 * it + g) * PLD + 4 * ks + tg], B[(4 * ks + tg) * PLD + 8 * jt + g]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UT; ++u) {
+        const int job = wrp + PW * u;
+        if (job < 9) {
+          const int it = job / 3, jt = job - 3 * it;
+          sT[(8 * it + g) * PLD + 8 * jt + 2 * tg] = ac0[u];
+          sT[(8 * it + g) * PLD + 8 * jt + 2 * tg + 1] = ac1[u];
+        }
+      }
+      __syncthreads();
+      // P_II <- (X + X^T) / 2 with X = T Phi^T: a tile of X^T = Phi T^T is the same products in the same order as the mirrored
+      // tile of X, so both halves of the sum come out of this warp's own DMMAs and P_II stays exactly symmetric.
+      // Phi_acc <- Phi_acc'
+      double xc0[UX], xc1[UX], xe0[UX], xe1[UX];
+#pragma unroll
+      for (int u = 0; u < UX; ++u) {
+        const int t = wrp + PW * u;
+        xc0[u] = xc1[u] = xe0[u] = xe1[u] = 0.0;
+        if (t < 9) {
+          const int it = t / 3, jt = t - 3 * it;
+#pragma unroll
+          for (int ks = 0; ks < 6; ++ks) {
+            pdmma(xc0[u], xc1[u], sT[(8 * it + g) * PLD + 4 * ks + tg], sPhi[(8 * jt + g) * PLD + 4 * ks + tg]);
+            pdmma(xe0[u], xe1[u], sPhi[(8 * it + g) * PLD + 4 * ks + tg], sT[(8 * jt + g) * PLD + 4 * ks + tg]);
           }
         }
       }
-      __syncthreads();
-      // X = T Phi^T ; Phi_acc <- Phi_acc'
 #pragma unroll
-      for (int u = 0; u < 3; ++u) {
+      for (int u = 0; u < UX; ++u) {
         const int t = wrp + PW * u;
         if (t < 9) {
           const int it = t / 3, jt = t - 3 * it;
-          double c0v = 0.0, c1v = 0.0;
-#pragma unroll
-          for (int ks = 0; ks < 6; ++ks)
-            pdmma(c0v, c1v, sT[(8 * it + g) * PLD + 4 * ks + tg], sPhi[(8 * jt + g) * PLD + 4 * ks + tg]);
-          sX2[(8 * it + g) * PLD + 8 * jt + 2 * tg] = c0v;
-          sX2[(8 * it + g) * PLD + 8 * jt + 2 * tg + 1] = c1v;
+          sPII[(8 * it + g) * PLD + 8 * jt + 2 * tg] = (xc0[u] + xe0[u]) / 2.;
+          sPII[(8 * it + g) * PLD + 8 * jt + 2 * tg + 1] = (xc1[u] + xe1[u]) / 2.;
         }
       }
 #pragma unroll
-      for (int u = 2; u < 5; ++u) {
+      for (int u = U0; u < UT; ++u) {
         const int job = wrp + PW * u;
         if (job >= 9 && job < 18) {
           const int t = job - 9, it = t / 3, jt = t - 3 * it;
-          sAcc[(8 * it + g) * PLD + 8 * jt + 2 * tg] = na0[u - 2];
-          sAcc[(8 * it + g) * PLD + 8 * jt + 2 * tg + 1] = na1[u - 2];
+          sAcc[(8 * it + g) * PLD + 8 * jt + 2 * tg] = ac0[u];
+          sAcc[(8 * it + g) * PLD + 8 * jt + 2 * tg + 1] = ac1[u];
         }
-      }
-      __syncthreads();
-      for (int e = lane; e < PMAT; e += NT) {
-        const int i = e / PLD, j = e - PLD * i;
-        if (i < 24 && j < 24) sPII[e] = (sX2[e] + sX2[j * PLD + i]) / 2.;
       }
       __syncthreads();
     }
@@ -350,14 +358,18 @@ __global__ void __launch_bounds__(PW * 32, 4) k_propagate(Dev d, const int* __re
   }
   // P_IC <- Phi_acc P_IC and its mirror: a warp owns an 8-column tile (its B fragments are read before anything is written)
   const int nct = (n - NI + 7) >> 3;
-  for (int jt = wrp; jt < nct; jt += PW) {
+  double bf[6], bn[6];
+  auto load_b = [&](int jt, double* o) {
     const int j = NI + 8 * jt + g;
-    double bf[6];
 #pragma unroll
     for (int ks = 0; ks < 6; ++ks) {
       const int k = 4 * ks + tg;
-      bf[ks] = (k < NI && j < n) ? P[(size_t)k * ld + j] : 0.0;
+      o[ks] = (jt < nct && k < NI && j < n) ? P[(size_t)k * ld + j] : 0.0;
     }
+  };
+  load_b(wrp, bf);
+  for (int jt = wrp; jt < nct; jt += PW) {
+    load_b(jt + PW, bn);                                   // next tile's fragments are in flight while this one is multiplied
 #pragma unroll
     for (int it = 0; it < 3; ++it) {
       double c0v = 0.0, c1v = 0.0;
@@ -369,6 +381,8 @@ __global__ void __launch_bounds__(PW * 32, 4) k_propagate(Dev d, const int* __re
         if (jj + 1 < n) { P[(size_t)i * ld + jj + 1] = c1v; P[(size_t)(jj + 1) * ld + i] = c1v; }
       }
     }
+#pragma unroll
+    for (int ks = 0; ks < 6; ++ks) bf[ks] = bn[ks];
   }
 }
 

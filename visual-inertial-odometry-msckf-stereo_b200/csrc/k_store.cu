@@ -65,7 +65,7 @@ __device__ __forceinline__ unsigned hash64(long long k) {
 
 // ------------------------------------------------------------------ add_feature_observations (msckf.py:409-427)
 __global__ void __launch_bounds__(ST) k_observe(Dev d, const int* __restrict__ feat_off, const long long* __restrict__ ids,
-                                                 const double* __restrict__ uv, const FrameIn* fin) {
+                                                 const double* __restrict__ uv, const FrameIn* fin, int use_smem) {
   if (fin) { feat_off = fin->feat_off; ids = fin->ids; uv = fin->uv; }
   const int f = blockIdx.x, tid = threadIdx.x;
   __shared__ int s_warp[ST / 32];
@@ -73,8 +73,10 @@ __global__ void __launch_bounds__(ST) k_observe(Dev d, const int* __restrict__ f
   const int n0 = d.nlive[f];
   const int off = feat_off[f], cnt = feat_off[f + 1] - off;
   const int N = d.ncam[f];
-  long long* hk = d.h_key + (size_t)f * d.Hs;
-  int* hv = d.h_val + (size_t)f * d.Hs;
+  // the per-frame id -> slot table lives in shared memory when it fits (launch_observe), else in its global scratch
+  extern __shared__ __align__(16) unsigned char obs_sm[];
+  long long* hk = use_smem ? (long long*)obs_sm : d.h_key + (size_t)f * d.Hs;
+  int* hv = use_smem ? (int*)(obs_sm + (size_t)d.Hs * sizeof(long long)) : d.h_val + (size_t)f * d.Hs;
   const unsigned hmask = (unsigned)d.Hs - 1u;
   if (tid == 0) s_tracked = 0;
   for (int e = tid; e < d.Hs; e += ST) hk[e] = EMPTY_KEY;
@@ -525,7 +527,14 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
 }
 
 void launch_observe(const Dev& d, const int* feat_off, const long long* ids, const double* uv, cudaStream_t st, const FrameIn* fin) {
-  KLAUNCH(d, KID_OBSERVE, st, (k_observe<<<d.F, ST, 0, st>>>(d, feat_off, ids, uv, fin)));
+  const size_t table = (size_t)d.Hs * (sizeof(long long) + sizeof(int));
+  const int use_smem = table <= 96 * 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(k_observe, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+    attr_set = true;
+  }
+  KLAUNCH(d, KID_OBSERVE, st, (k_observe<<<d.F, ST, use_smem ? table : 0, st>>>(d, feat_off, ids, uv, fin, use_smem)));
 }
 void launch_classify_lost(const Dev& d, cudaStream_t st) {
   KLAUNCH(d, KID_CLASSIFY_LOST, st, (k_classify_lost<<<d.F, ST, 0, st>>>(d)));

@@ -377,7 +377,7 @@ void launch_triangulate_store(const Dev& d, cudaStream_t st) {
     cudaFuncSetAttribute(k_triangulate_raw, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     attr_set = true;
   }
-  const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(12, (200 * 1024) / (smem + 1024)));
+  const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(12, (224 * 1024) / (smem + 1024)));     // 3 CTAs / SM at a 20-camera window
   KLAUNCH(d, KID_TRIANGULATE, st, (k_triangulate_store<<<sm_count() * per_sm, wpb * 32, smem, st>>>(d)));
 }
 

@@ -270,20 +270,32 @@ __global__ void __launch_bounds__(DT, 512 / DT) k_upd_dmma(Dev d, int cls) {
 
     // ---- P <- P - W^T W : 16x16 warp tiles over the upper triangle, mirrored store
     const int nb = (n + 15) >> 4, nblk = nb * (nb + 1) / 2;
-    for (int item = warp; item < nblk; item += DT / 32) {
+    // the P values of the warp's next tile are requested before this tile's DMMAs and stores (tiles are disjoint, and the
+    // mirrored stores only touch the strict lower triangle, which nobody reads)
+    double pv[2][2][2], pn[2][2][2];
+    auto load_tile = [&](int item, double (&o)[2][2][2]) {
       int bj, bi;
-      tri_decode(item, bj, bi);                  // bi <= bj
-      const int a0 = 16 * bi, b0 = 16 * bj;
-      double pv[2][2][2], acc[2][2][2];
+      tri_decode(item, bj, bi);
 #pragma unroll
       for (int x = 0; x < 2; ++x)
 #pragma unroll
         for (int y = 0; y < 2; ++y) {
-          const int a = a0 + 8 * x + g, b = b0 + 8 * y + 2 * tg;
-          acc[x][y][0] = acc[x][y][1] = 0.0;
-          pv[x][y][0] = (a < n && b < n) ? P[(size_t)a * ld + b] : 0.0;
-          pv[x][y][1] = (a < n && b + 1 < n) ? P[(size_t)a * ld + b + 1] : 0.0;
+          const int a = 16 * bi + 8 * x + g, b = 16 * bj + 8 * y + 2 * tg;
+          o[x][y][0] = (a < n && b < n) ? P[(size_t)a * ld + b] : 0.0;
+          o[x][y][1] = (a < n && b + 1 < n) ? P[(size_t)a * ld + b + 1] : 0.0;
         }
+    };
+    if (warp < nblk) load_tile(warp, pv);
+    for (int item = warp; item < nblk; item += DT / 32) {
+      int bj, bi;
+      tri_decode(item, bj, bi);                  // bi <= bj
+      const int a0 = 16 * bi, b0 = 16 * bj;
+      if (item + DT / 32 < nblk) load_tile(item + DT / 32, pn);
+      double acc[2][2][2];
+#pragma unroll
+      for (int x = 0; x < 2; ++x)
+#pragma unroll
+        for (int y = 0; y < 2; ++y) acc[x][y][0] = acc[x][y][1] = 0.0;
       const double* wa = sT + tg * ldT + a0 + g;
       const double* wb = sT + tg * ldT + b0 + g;
       for (int ks = 0; ks < nkk; ++ks) {
@@ -310,6 +322,10 @@ __global__ void __launch_bounds__(DT, 512 / DT) k_upd_dmma(Dev d, int cls) {
             }
           }
         }
+#pragma unroll
+      for (int x = 0; x < 2; ++x)
+#pragma unroll
+        for (int y = 0; y < 2; ++y) { pv[x][y][0] = pn[x][y][0]; pv[x][y][1] = pn[x][y][1]; }
     }
     __syncthreads();
   }

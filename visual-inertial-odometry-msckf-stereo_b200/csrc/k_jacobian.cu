@@ -222,9 +222,11 @@ __device__ void jac_core(const Dev& d, int f, int k, int M, unsigned long long l
       if (xn2 == 0.0) {
         tau[kk] = 0.0;
       } else {
-        const double nrm = sqrt(alpha * alpha + xn2);
+        const double n2 = alpha * alpha + xn2;
+        const double rn = rsqrt(n2);                 // 1 / |beta|
+        const double nrm = n2 * rn;
         const double beta = (alpha >= 0) ? -nrm : nrm;
-        tau[kk] = (beta - alpha) / beta;
+        tau[kk] = (beta - alpha) * ((alpha >= 0) ? -rn : rn);
         const double sc = 1.0 / (alpha - beta);
         for (int i = kk + 1 + lane; i < R4; i += LW) V[3 * i + kk] *= sc;
       }
@@ -352,10 +354,10 @@ __device__ void jac_core(const Dev& d, int f, int k, int M, unsigned long long l
   for (int j = 0; j < R; ++j) {
     const double dj = B.S[j * R + j];
     if (!(dj > 0.0)) { spd = false; break; }
-    const double l = sqrt(dj);
-    const double yj = B.y[j] / l;
+    const double il = rsqrt(dj);                    // only 1 / L(j,j) is needed: one reciprocal square root, no divides
+    const double yj = B.y[j] * il;
     gsync<NT>(gmask);
-    for (int i = j + 1 + tid; i < R; i += NT) B.S[i * R + j] /= l;
+    for (int i = j + 1 + tid; i < R; i += NT) B.S[i * R + j] *= il;
     if (tid == 0) B.y[j] = yj;
     gsync<NT>(gmask);
     for (int i = j + 1 + tid; i < R; i += NT) {

@@ -45,7 +45,7 @@ __device__ __forceinline__ void jr_row(const double* __restrict__ pre, const dou
   }
   const double iz = 1.0 / p[2];
   const double pn = (i ? p[1] : p[0]);
-  const double b2 = -pn / (p[2] * p[2]);
+  const double b2 = -(pn * iz) * iz;                                // one reciprocal of the depth serves the row and the residual
   const double b[3] = {i ? 0.0 : iz, i ? iz : 0.0, b2};            // row of dz/dp
   double c[3];
   if (h) {
@@ -69,7 +69,7 @@ __device__ __forceinline__ void jr_row(const double* __restrict__ pre, const dou
   const double sc = au / uu;
 #pragma unroll
   for (int e = 0; e < 6; ++e) Hx[e] = A[e] - sc * u[e];
-  res = z[q] - pn / p[2];
+  res = z[q] - pn * iz;
 }
 
 
@@ -160,10 +160,13 @@ __global__ void __launch_bounds__(JR_T, jr_ctas_per_sm<M>()) k_jacobian_rows(Dev
     for (int kk = 0; kk < 3; ++kk) {
       const double xn2 = jr_gsum<G>(r > kk ? v[kk] * v[kk] : 0.0);
       const double alpha = __shfl_sync(JFULL, v[kk], kk, G);
-      const double nrm = sqrt(alpha * alpha + xn2);
-      const double beta = (alpha >= 0) ? -nrm : nrm;
+      // 1 / |beta| from one reciprocal square root (the FP64 sqrt and divide sequences are most of this kernel's instructions)
+      const double n2 = alpha * alpha + xn2;
       const bool nz = xn2 != 0.0;
-      tau[kk] = nz ? (beta - alpha) / beta : 0.0;
+      const double rn = nz ? rsqrt(n2) : 0.0;
+      const double nrm = n2 * rn;
+      const double beta = (alpha >= 0) ? -nrm : nrm;
+      tau[kk] = nz ? (beta - alpha) * ((alpha >= 0) ? -rn : rn) : 0.0;
       const double sc = nz ? 1.0 / (alpha - beta) : 1.0;
       v[kk] = (r > kk) ? v[kk] * sc : (r == kk ? 1.0 : 0.0);
 #pragma unroll
@@ -244,7 +247,7 @@ __global__ void __launch_bounds__(JR_T, jr_ctas_per_sm<M>()) k_jacobian_rows(Dev
     for (int j = 0; j < R; ++j) {
       const double djj = __shfl_sync(JFULL, srow[j], j + 3, G);
       if (!(djj > 0.0)) spd = false;                       // group-uniform
-      const double l = sqrt(djj), il = 1.0 / l;
+      const double il = rsqrt(djj);                        // only 1 / L(j,j) is needed
       const double lij = srow[j] * il;                     // meaningful on rows ii > j
       const double yj = __shfl_sync(JFULL, res * il, j + 3, G);
       gamma += yj * yj;

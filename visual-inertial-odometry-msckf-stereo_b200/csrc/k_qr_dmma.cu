@@ -75,9 +75,11 @@ __device__ __forceinline__ void qd_panel(double* sR, double* sC, double* sTm, in
       }
       if (s[jj] != 0.0) {
         const double alpha = rrow[jj];
-        const double nrm = sqrt(alpha * alpha + s[jj]);
+        const double n2 = alpha * alpha + s[jj];
+        const double rn = rsqrt(n2);                       // 1 / |beta|: one reciprocal square root instead of a square root and a divide
+        const double nrm = n2 * rn;
         const double beta = (alpha >= 0) ? -nrm : nrm;
-        const double tj = (beta - alpha) / beta, sc = 1.0 / (alpha - beta);
+        const double tj = (beta - alpha) * ((alpha >= 0) ? -rn : rn), sc = 1.0 / (alpha - beta);
         tau[jj] = tj;
 #pragma unroll
         for (int t = 0; t < 4; ++t) x[t][jj] *= sc;

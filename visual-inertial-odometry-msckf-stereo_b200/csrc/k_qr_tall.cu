@@ -39,9 +39,11 @@ __device__ __forceinline__ void tq_fold(double (&x)[4][TQ_NC], double* R, int la
     }
     if (s[jj] != 0.0) {                                    // warp-uniform (the butterfly leaves identical sums in every lane)
       const double alpha = R[jj * TQ_LDR + jj];
-      const double nrm = sqrt(alpha * alpha + s[jj]);
+      const double n2 = alpha * alpha + s[jj];
+      const double rn = rsqrt(n2);                         // 1 / |beta|: one reciprocal square root instead of a square root and a divide
+      const double nrm = n2 * rn;
       const double beta = (alpha >= 0) ? -nrm : nrm;
-      const double tj = (beta - alpha) / beta, sc = 1.0 / (alpha - beta);
+      const double tj = (beta - alpha) * ((alpha >= 0) ? -rn : rn), sc = 1.0 / (alpha - beta);
 #pragma unroll
       for (int t = 0; t < 4; ++t) x[t][jj] *= sc;
 #pragma unroll

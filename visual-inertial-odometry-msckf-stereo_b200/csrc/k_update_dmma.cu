@@ -48,9 +48,8 @@ __device__ __forceinline__ bool chol8_inverse(const double* sX, int LDX, int p0,
   for (int j = 0; j < 8; ++j) {
     const double djj = __shfl_sync(FULL, a[j], j);
     if (!(djj > 0.0)) bad = true;                      // warp-uniform
-    const double l = sqrt(djj);
-    il[j] = 1.0 / l;
-    const double lrj = (r == j) ? l : a[j] * il[j];
+    il[j] = rsqrt(djj);                                // one reciprocal square root instead of a square root and a divide
+    const double lrj = (r == j) ? djj * il[j] : a[j] * il[j];
     a[j] = lrj;
 #pragma unroll
     for (int c = j + 1; c < 8; ++c) {

@@ -24,7 +24,8 @@ __device__ __forceinline__ double jr_gsum(double v) {
 template <int M>
 __host__ __device__ constexpr int jr_group_doubles() {
   // Pcc [6M][6M] | Z [3][6M] | H' rows + residual [4M-3][6M+1] (padded to even) | cl [M] ints
-  return 36 * M * M + 18 * M + (((4 * M - 3) * (6 * M + 1) + 1) & ~1) + ((M + 1) / 2) + 2;
+  // even, so that every group's Pcc block is 16-byte aligned and its rows are read with 128-bit loads
+  return (36 * M * M + 18 * M + (((4 * M - 3) * (6 * M + 1) + 1) & ~1) + ((M + 1) / 2) + 2 + 1) & ~1;
 }
 
 // One row of msckf.py:429-498: q = 0,1 -> cam0 u,v ; q = 2,3 -> cam1 u,v.

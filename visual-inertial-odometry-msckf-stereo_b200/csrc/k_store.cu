@@ -472,16 +472,30 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
     lga[d.item_cand[ik]] = d.item_gamma[ik];
     ldf[d.item_cand[ik]] = d.item_dof[ik];
   }
+  // active columns in logical order: warp 0, one camera per lane (a serial walk is a chain of dependent global loads)
+  __shared__ int s_na;
+  if (tid < 32) {
+    const int N = d.ncam[f];
+    const unsigned long long act = s_act;
+    int* cm = d.colmap + (size_t)f * d.nmax;
+    int nblk = 0;
+    for (int c0 = 0; c0 < N; c0 += 32) {
+      const int c = c0 + tid;
+      const int bit = (c < N) ? (int)((act >> d.cam_phys[(size_t)f * d.Nmax + c]) & 1ull) : 0;
+      const unsigned b = __ballot_sync(0xffffffffu, bit);
+      if (bit) {
+        const int o = 6 * (nblk + __popc(b & ((1u << tid) - 1u)));
+        for (int e = 0; e < 6; ++e) cm[o + e] = NI + 6 * c + e;
+      }
+      nblk += __popc(b);
+    }
+    if (tid == 0) s_na = 6 * nblk;
+    __syncwarp();
+  }
   if (tid == 0) {
     int m = (int)used_rows;
     const int N = d.ncam[f];
-    // active columns in logical order
-    const unsigned long long act = s_act;
-    int na = 0;
-    int* cm = d.colmap + (size_t)f * d.nmax;
-    for (int c = 0; c < N; ++c)
-      if ((act >> d.cam_phys[(size_t)f * d.Nmax + c]) & 1ull)
-        for (int e = 0; e < 6; ++e) cm[na++] = NI + 6 * c + e;
+    const int na = s_na;
     if (m > d.rowmap_cap) { atomicOr(d.err, ERRBIT_ROWS); m = 0; }
     const int kr = (m > na) ? na : m;
     int qcls = -1;

@@ -299,3 +299,36 @@ def test_alternative_kernel_paths(knob, monkeypatch):
     assert counts['gates'] > 300 and counts['prunes'] >= 5 and counts['updates'] > 20, counts
     assert worst['imu'] < TOL and worst['P'] < TOL and worst['cams'] < TOL and worst['extr'] < TOL, worst
     assert worst['pos_m'] < 1e-3, worst
+
+
+def test_update_shapes_of_the_pruning_stage():
+    """msckf_get_update_shapes after feature_callback describes the pruning update (the last stage of a frame): every
+    landmark sits on the two camera states being removed, so n_a = 12, k = min(m, 12), the one-CTA class-0 update runs,
+    and m is the row count of the decision log.  These are the stacks k_qr_tall compresses."""
+    n_frames, max_cam = 26, 6
+    stream = synth.make_stream(n_frames, 100, structure_seed=5, noise_seed=3)
+    dcfg = ConfigEuRoC()
+    dcfg._vio_max_cam_state_size__ = max_cam
+    df = MSCKF(dcfg, feature_capacity=512)
+    msgs = stream.imu_msgs()
+    k = 0
+    pruned = tall = 0
+    try:
+        for f in range(n_frames):
+            while k < len(msgs) and msgs[k].vio_timestamp__ <= stream.frame_ts[f]:
+                df.imu_callback(msgs[k])
+                k += 1
+            df.feature_callback(stream.feature_msg(f))
+            m, na, kr, path = df.ctx.update_shapes()[0]
+            log = df.ctx.stage_log(0, 1)
+            assert m == log['update_rows']
+            if m == 0:
+                assert path == 0 and kr == 0
+                continue
+            pruned += 1
+            assert na == 12 and kr == min(m, 12) and path == 5, (m, na, kr, path)
+            assert m % 5 == 0                       # 4 M - 3 rows per landmark with M = 2
+            tall += int(m > 12)
+    finally:
+        df.close()
+    assert pruned >= 5 and tall >= 5, (pruned, tall)

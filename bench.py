@@ -420,8 +420,8 @@ def run_b200(args):
             'triangulate': (['k_triangulate'], 632.0 * dc[capi.CNT_TRI_OBS] + 150.0 * dc[capi.CNT_TRIANGULATIONS]
                             + (dc[capi.CNT_TRI_SOLVES] - dc[capi.CNT_TRIANGULATIONS]) * 40.0, 36.0 * dc[capi.CNT_TRI_OBS] + 25.0 * dc[capi.CNT_TRIANGULATIONS]),
             'jacobian_nullspace_gate': (['k_jacobian_gate', 'k_jacobian_rows', 'k_jacobian_big'], dc[capi.CNT_K2_FLOPS], dc[capi.CNT_K2_BYTES]),
-            'stacked_qr': (['k_qr', 'k_qr_tall', 'k_qr_d16', 'k_qr_d32', 'k_qr_d48', 'k_qr_d64'], dc[capi.CNT_QR_FLOPS], dc[capi.CNT_QR_BYTES]),
-            'gain_update': (['k_upd_dmma16', 'k_upd_dmma32', 'k_upd_dmma48', 'k_upd_dmma64', 'k_upd_T', 'k_upd_S', 'k_upd_chol', 'k_upd_trsm', 'k_upd_inject', 'k_upd_downdate'], dc[capi.CNT_K4_FLOPS],
+            'stacked_qr': (['k_qr', 'k_qr_tall', 'k_qr_d16', 'k_qr_d32', 'k_qr_d48', 'k_qr_d64', 'k_qr_d80'], dc[capi.CNT_QR_FLOPS], dc[capi.CNT_QR_BYTES]),
+            'gain_update': (['k_upd_dmma16', 'k_upd_dmma32', 'k_upd_dmma48', 'k_upd_dmma64', 'k_upd_dmma80', 'k_upd_T', 'k_upd_S', 'k_upd_chol', 'k_upd_trsm', 'k_upd_inject', 'k_upd_downdate'], dc[capi.CNT_K4_FLOPS],
                             dc[capi.CNT_K4_BYTES]),
         }
         total_ms = sum(v[2] for v in kt.values())

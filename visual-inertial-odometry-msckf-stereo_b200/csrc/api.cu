@@ -14,7 +14,7 @@ using namespace msckf;
 namespace msckf {
 const char* const kKernelNames[KID_COUNT] = {
     "k_propagate", "k_augment", "k_cam_prepare", "k_observe", "k_classify_lost", "k_prune_select", "k_triangulate", "k_plan_items",
-    "k_jacobian_gate", "k_jacobian_rows", "k_jacobian_big", "k_plan_stack", "k_qr", "k_qr_tall", "k_qr_d16", "k_qr_d32", "k_qr_d48", "k_qr_d64", "k_upd_dmma16", "k_upd_dmma32", "k_upd_dmma48", "k_upd_dmma64", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
+    "k_jacobian_gate", "k_jacobian_rows", "k_jacobian_big", "k_plan_stack", "k_qr", "k_qr_tall", "k_qr_d16", "k_qr_d32", "k_qr_d48", "k_qr_d64", "k_qr_d80", "k_upd_dmma16", "k_upd_dmma32", "k_upd_dmma48", "k_upd_dmma64", "k_upd_dmma80", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
     "k_upd_downdate", "k_remove_cams", "k_finish_frame", "k_reset", "misc"};
 
 void KTimer::begin(int id, cudaStream_t st) {
@@ -305,7 +305,7 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
     d.jac_rows_ok = getenv("MSCKF_NO_JAC_ROWS") ? 0 : 1;
     d.qr_tall_ok = getenv("MSCKF_NO_QR_TALL") ? 0 : 1;
     {
-      const int kc[UPD_DMMA_CLASSES] = {16, 32, 48, 64};
+      const int kc[UPD_DMMA_CLASSES] = {16, 32, 48, 64, 80};
       for (int c = 0; c < UPD_DMMA_CLASSES; ++c)      // MSCKF_NO_DMMA: debugging knob, every update through the tiled kernels
         d.upd_dmma_ok[c] = (!getenv("MSCKF_NO_DMMA") && upd_dmma_smem_bytes(d.nmax, kc[c]) <= 220 * 1024) ? 1 : 0;
     }

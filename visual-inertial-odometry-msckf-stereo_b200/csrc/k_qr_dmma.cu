@@ -260,9 +260,9 @@ void launch_qr_dmma_class(const Dev& d, int c, cudaStream_t st) {
     sms = sm_count();
     attr_set = true;
   }
-  const int caps[QR_DMMA_CLASSES] = {16, 32, 48, 64};
-  const int thr[QR_DMMA_CLASSES] = {64, 128, 128, 256};
-  const int kid[QR_DMMA_CLASSES] = {KID_QR_D16, KID_QR_D32, KID_QR_D48, KID_QR_D64};
+  const int caps[QR_DMMA_CLASSES] = {16, 32, 48, 64, 80};
+  const int thr[QR_DMMA_CLASSES] = {64, 128, 128, 256, 256};
+  const int kid[QR_DMMA_CLASSES] = {KID_QR_D16, KID_QR_D32, KID_QR_D48, KID_QR_D64, KID_QR_D80};
   const size_t sm = qr_dmma_smem_bytes(caps[c]);
   int per_sm = (int)std::min<size_t>((224 * 1024) / (sm + 1024), 512 / thr[c]);   // 128 registers per thread
   per_sm = std::max(1, per_sm);

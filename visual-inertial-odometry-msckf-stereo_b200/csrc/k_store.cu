@@ -500,7 +500,7 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
     const int kr = (m > na) ? na : m;
     int qcls = -1;
     if (m > 0) {
-      qcls = (m <= na || na + 1 > 64) ? QR_DMMA_CLASSES : (na + 1 <= 16 ? 0 : (na + 1 <= 32 ? 1 : (na + 1 <= 48 ? 2 : 3)));
+      qcls = (m <= na || na + 1 > 80) ? QR_DMMA_CLASSES : (na + 1 <= 16 ? 0 : (na + 1 <= 32 ? 1 : (na + 1 <= 48 ? 2 : (na + 1 <= 64 ? 3 : 4))));
       // pruning stage: every landmark sits on the two cameras being removed (5 rows x 12 columns each): tall-skinny TSQR
       if (stage == 1 && qcls == 0 && na == 12 && d.qr_tall_ok) {
         qcls = QR_DMMA_CLASSES + 1;
@@ -516,7 +516,7 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
     int path = 0;
     if (kr > 0) {
       const int wid = max(kr, na) + 1;                  // same thresholds as the compression classes: QR and update of a class share a stream
-      const int uc = wid <= 16 ? 0 : (wid <= 32 ? 1 : (wid <= 48 ? 2 : (wid <= 64 ? 3 : -1)));
+      const int uc = wid <= 16 ? 0 : (wid <= 32 ? 1 : (wid <= 48 ? 2 : (wid <= 64 ? 3 : (wid <= 80 ? 4 : -1))));
       path = (uc >= 0 && d.upd_dmma_ok[uc]) ? 5 + uc : 2;           // one-CTA tensor-pipe kernel, else tiled
       if (path == 2) d.wl_upd_big[atomicAdd(d.stage_ctr + SC_NUPD_BIG, 1ull)] = f;
       if (path >= 5) d.wl_upd_dmma[(size_t)(path - 5) * d.F + atomicAdd(d.stage_ctr + SC_NUPD_DMMA + (path - 5), 1ull)] = f;

@@ -86,7 +86,7 @@ __device__ __forceinline__ void tri_decode(int t, int& i, int& j) {
 }
 
 template <int KC, int DT>
-__global__ void __launch_bounds__(DT, 512 / DT) k_upd_dmma(Dev d, int cls) {
+__global__ void __launch_bounds__(DT, KC > 64 ? 1 : 512 / DT) k_upd_dmma(Dev d, int cls) {
   constexpr int LDX = KC + 4;
   constexpr int NKT = KC / 8;                  // row tiles at capacity
   constexpr int NW = DT / 32;                  // warps per CTA
@@ -344,13 +344,14 @@ static void launch_upd_class(const Dev& d, int cls, int kid, cudaStream_t st) {
   KLAUNCH(d, kid, st, (k_upd_dmma<KC, DT><<<std::min(d.F, sms * per_sm), DT, sm, st>>>(d, cls)));
 }
 
-// update class c = compression class c: k, n_a + 1 <= 16 / 32 / 48 / 64
+// update class c = compression class c: k, n_a + 1 <= 16 / 32 / 48 / 64 / 80
 void launch_upd_dmma_class(const Dev& d, int cls, cudaStream_t st) {
   if (!d.upd_dmma_ok[cls]) return;
   if (cls == 0) launch_upd_class<16, 128>(d, 0, KID_UPD_DMMA16, st);
   else if (cls == 1) launch_upd_class<32, 128>(d, 1, KID_UPD_DMMA32, st);
   else if (cls == 2) launch_upd_class<48, 256>(d, 2, KID_UPD_DMMA48, st);
-  else launch_upd_class<64, 256>(d, 3, KID_UPD_DMMA64, st);
+  else if (cls == 3) launch_upd_class<64, 256>(d, 3, KID_UPD_DMMA64, st);
+  else launch_upd_class<80, 256>(d, 4, KID_UPD_DMMA80, st);       // n_a = 66 .. 78: one filter in a few thousand updates, but the tiled path costs it 0.3 ms
 }
 void launch_update_dmma(const Dev& d, Fork& fk) {
   for (int c = 0; c < UPD_DMMA_CLASSES; ++c) launch_upd_dmma_class(d, c, fk.lane(c == 3 ? 0 : c + 1));

@@ -9,7 +9,7 @@ namespace msckf {
 // Kernel ids for launch counting and optional per-kernel event timing (msckf_kernel_times).
 enum KernelId {
   KID_PROPAGATE = 0, KID_AUGMENT, KID_CAM_PREPARE, KID_OBSERVE, KID_CLASSIFY_LOST, KID_PRUNE_SELECT, KID_TRIANGULATE, KID_PLAN_ITEMS,
-  KID_JACOBIAN_GATE, KID_JACOBIAN_ROWS, KID_JACOBIAN_BIG, KID_PLAN_STACK, KID_QR, KID_QR_TALL, KID_QR_D16, KID_QR_D32, KID_QR_D48, KID_QR_D64, KID_UPD_DMMA16, KID_UPD_DMMA32, KID_UPD_DMMA48, KID_UPD_DMMA64, KID_UPD_T, KID_UPD_S, KID_UPD_CHOL, KID_UPD_TRSM, KID_UPD_INJECT,
+  KID_JACOBIAN_GATE, KID_JACOBIAN_ROWS, KID_JACOBIAN_BIG, KID_PLAN_STACK, KID_QR, KID_QR_TALL, KID_QR_D16, KID_QR_D32, KID_QR_D48, KID_QR_D64, KID_QR_D80, KID_UPD_DMMA16, KID_UPD_DMMA32, KID_UPD_DMMA48, KID_UPD_DMMA64, KID_UPD_DMMA80, KID_UPD_T, KID_UPD_S, KID_UPD_CHOL, KID_UPD_TRSM, KID_UPD_INJECT,
   KID_UPD_DOWNDATE, KID_REMOVE_CAMS, KID_FINISH_FRAME, KID_RESET, KID_MISC, KID_COUNT
 };
 extern const char* const kKernelNames[KID_COUNT];

@@ -30,11 +30,11 @@ constexpr unsigned ERRBIT_NOT_SPD = 8u;
 constexpr unsigned ERRBIT_CAM_CAP = 16u;
 
 // per-stage device counters (one memset per stage): pool bump pointer and work-list lengths
-constexpr int SC_POOL = 0, SC_NTRI = 1, SC_NJAC_BIG = 2, SC_NUPD_BIG = 3, SC_NJAC_SMALL = 4 /* .. 7: one per size class */, SC_NQR = 12 /* .. 15: tensor-pipe QR classes */, SC_NUPD_DMMA = 16 /* .. 19: tensor-pipe update classes */, SC_NQR_BUILD = 20 /* wide / uncompressed stacks (k_qr_build) */, SC_NQR_TALL = 21 /* pruning stacks (k_qr_tall) */, SC_COUNT = 24;
+constexpr int SC_POOL = 0, SC_NTRI = 1, SC_NJAC_BIG = 2, SC_NUPD_BIG = 3, SC_NJAC_SMALL = 4 /* .. 7: one per size class */, SC_NQR = 12 /* .. 16: tensor-pipe QR classes */, SC_NUPD_DMMA = 17 /* .. 21: tensor-pipe update classes */, SC_NQR_BUILD = 22 /* wide / uncompressed stacks (k_qr_build) */, SC_NQR_TALL = 23 /* pruning stacks (k_qr_tall) */, SC_COUNT = 24;
 // stacked-Jacobian compression classes: 0..3 = compressed (m > n_a) with n_a + 1 <= 16 / 32 / 48 / 64 columns (k_qr_dmma), 4 = general CTA kernel
-constexpr int QR_DMMA_CLASSES = 4;
+constexpr int QR_DMMA_CLASSES = 5;
 // one-CTA tensor-pipe update classes, aligned with the compression classes: max(k, n_a) + 1 <= 16 / 32 / 48 / 64
-constexpr int UPD_DMMA_CLASSES = 4;
+constexpr int UPD_DMMA_CLASSES = 5;
 // size classes of the group-per-landmark Jacobian kernel (shared memory is sized per class): M <= 2, M = 3, M = 4, M <= 6
 constexpr int JAC_CLASSES = 4;
 __host__ __device__ inline int jac_class(int M) { return M <= 2 ? 0 : (M == 3 ? 1 : (M == 4 ? 2 : 3)); }

@@ -65,12 +65,13 @@ __device__ __forceinline__ void measurement_jacobian_half(const double* pre, con
   double S0[9];
   skew3(pc0, S0);
   double A[12];
-  double pcx, pcy, pcz;
+  double pcx, pcy, pcz, iz;
   if (h == 0) {
     pcx = pc0[0]; pcy = pc0[1]; pcz = pc0[2];
     // dz/dp rows (only the non-zero 2x3 halves)
-    const double a0[3] = {1 / pcz, 0.0, -pcx / (pcz * pcz)};
-    const double a1[3] = {0.0, 1 / pcz, -pcy / (pcz * pcz)};
+    iz = 1 / pcz;                                               // one reciprocal of the depth for the row pair and the residual
+    const double a0[3] = {iz, 0.0, -(pcx * iz) * iz};
+    const double a1[3] = {0.0, iz, -(pcy * iz) * iz};
 #pragma unroll
     for (int j = 0; j < 3; ++j) {
       A[j] = a0[0] * S0[j] + a0[1] * S0[3 + j] + a0[2] * S0[6 + j];
@@ -86,8 +87,9 @@ __device__ __forceinline__ void measurement_jacobian_half(const double* pre, con
     mat3_vec(R1, d1, pc1);
     mat3_mul(R01, S0, D1);
     pcx = pc1[0]; pcy = pc1[1]; pcz = pc1[2];
-    const double b0[3] = {1 / pcz, 0.0, -pcx / (pcz * pcz)};
-    const double b1[3] = {0.0, 1 / pcz, -pcy / (pcz * pcz)};
+    iz = 1 / pcz;
+    const double b0[3] = {iz, 0.0, -(pcx * iz) * iz};
+    const double b1[3] = {0.0, iz, -(pcy * iz) * iz};
 #pragma unroll
     for (int j = 0; j < 3; ++j) {
       A[j] = b0[0] * D1[j] + b0[1] * D1[3 + j] + b0[2] * D1[6 + j];
@@ -104,19 +106,20 @@ __device__ __forceinline__ void measurement_jacobian_half(const double* pre, con
   double uu = 0;
 #pragma unroll
   for (int i = 0; i < 6; ++i) uu += u[i] * u[i];
+  const double iuu = 1.0 / uu;
 #pragma unroll
   for (int i = 0; i < 2; ++i) {
     double au = 0;
 #pragma unroll
     for (int j = 0; j < 6; ++j) au += A[6 * i + j] * u[j];
-    const double sc = au / uu;           // (reference: A - (A u) u^T / (u^T u); one division per row instead of six)
+    const double sc = au * iuu;          // (reference: A - (A u) u^T / (u^T u); one reciprocal for both rows)
 #pragma unroll
     for (int j = 0; j < 6; ++j) Hx[6 * i + j] = A[6 * i + j] - sc * u[j];
 #pragma unroll
     for (int j = 0; j < 3; ++j) Hf[3 * i + j] = -Hx[6 * i + 3 + j];
   }
-  r[0] = z[2 * h] - pcx / pcz;
-  r[1] = z[2 * h + 1] - pcy / pcz;
+  r[0] = z[2 * h] - pcx * iz;
+  r[1] = z[2 * h + 1] - pcy * iz;
 }
 
 // Work buffers of one landmark (shared memory, or global scratch for T1 / S of very long tracks).

@@ -548,24 +548,25 @@ __global__ void __launch_bounds__(256) k_gate_dense(Dev d, int f, const double* 
   }
 }
 
-static int g_sm_count = 0;
-int sm_count() {
-  if (!g_sm_count) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
-    if (g_sm_count <= 0) g_sm_count = 148;
+int sm_count() {                        // of the current device (contexts of one process may sit on different GPUs)
+  static std::atomic<int> cache[64];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  int n = cache[dev & 63].load(std::memory_order_relaxed);
+  if (!n) {
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+    cache[dev & 63].store(n, std::memory_order_relaxed);
   }
-  return g_sm_count;
+  return n;
 }
 
 template <int G>
 static void launch_small(const Dev& d, int cls, int write_all, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DevOnce once;     // function attributes are per device
+  once.run([&] {
     cudaFuncSetAttribute(k_jacobian_gate_small<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    attr_set = true;
-  }
+  });
   int per_group = (jac_small_doubles(jac_class_maxM(cls)) + 15) & ~15;
   if (G < 32) per_group += 8;      // neighbouring groups of a warp land on different halves of the banks
   const size_t smem = (size_t)JAC_WARPS * (32 / G) * per_group * sizeof(double);
@@ -578,11 +579,10 @@ static void launch_small(const Dev& d, int cls, int write_all, cudaStream_t st) 
 // pruning stage only has M = 2).  Lanes per landmark grow with the class so that the shared-memory-limited number of
 // landmarks in flight still fills the SM with warps.
 void launch_jacobian_gate(const Dev& d, int class_mask, int with_big, int write_all, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DevOnce once;     // function attributes are per device
+  once.run([&] {
     cudaFuncSetAttribute(k_jacobian_gate_big, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    attr_set = true;
-  }
+  });
   Fork fk(d, st);
   if (class_mask & 1) {
     if (d.jac_rows_ok) launch_jacobian_rows(d, 0, write_all, fk.lane(0));

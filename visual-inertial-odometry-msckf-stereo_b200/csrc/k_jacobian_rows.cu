@@ -279,14 +279,12 @@ __global__ void __launch_bounds__(JR_T, jr_ctas_per_sm<M>()) k_jacobian_rows(Dev
 
 template <int M, int G>
 static void launch_rows(const Dev& d, int cls, int write_all, cudaStream_t st) {
-  static bool attr_set = false;
-  static int sms = 0;
+  static DevOnce once;     // function attributes are per device
   const size_t smem = (size_t)(JR_T / G) * jr_group_doubles<M>() * sizeof(double);
-  if (!attr_set) {
+  once.run([&] {
     cudaFuncSetAttribute(k_jacobian_rows<M, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    sms = sm_count();
-    attr_set = true;
-  }
+  });
+  const int sms = sm_count();
   int per_sm = (int)std::min<size_t>(2 * jr_ctas_per_sm<M>(), (220 * 1024) / (smem + 1024));
   per_sm = std::max(per_sm, 1);
   KLAUNCH(d, KID_JACOBIAN_ROWS, st, (k_jacobian_rows<M, G><<<sms * per_sm, JR_T, smem, st>>>(d, cls, write_all)));

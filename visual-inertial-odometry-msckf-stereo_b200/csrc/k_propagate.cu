@@ -585,12 +585,11 @@ __global__ void __launch_bounds__(PT) k_remove_cams(Dev d) {
 
 // ------------------------------------------------------------------ launchers
 void launch_propagate(const Dev& d, const int* imu_off, const double* ts, const double* gyro, const double* acc, cudaStream_t st, const FrameIn* fin) {
-  static bool attr_set = false;
+  static DevOnce once;     // function attributes are per device
   const size_t smem = (size_t)PROP_DOUBLES * sizeof(double);
-  if (!attr_set) {
+  once.run([&] {
     cudaFuncSetAttribute(k_propagate, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    attr_set = true;
-  }
+  });
   KLAUNCH(d, KID_PROPAGATE, st, (k_propagate<<<d.F, PW * 32, smem, st>>>(d, imu_off, ts, gyro, acc, fin)));
 }
 void launch_augment(const Dev& d, const long long* ids, cudaStream_t st, const FrameIn* fin) {
@@ -603,11 +602,10 @@ void launch_reset(const Dev& d, int only_filter, int reset_imu, cudaStream_t st)
   KLAUNCH(d, KID_RESET, st, (k_reset<<<only_filter >= 0 ? 1 : d.F, PT, 0, st>>>(d, only_filter, reset_imu)));
 }
 void launch_remove_cams(const Dev& d, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DevOnce once;     // function attributes are per device
+  once.run([&] {
     cudaFuncSetAttribute(k_remove_cams, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    attr_set = true;
-  }
+  });
   KLAUNCH(d, KID_REMOVE_CAMS, st, (k_remove_cams<<<d.F, PT, (size_t)RB * d.ld * sizeof(double), st>>>(d)));
 }
 

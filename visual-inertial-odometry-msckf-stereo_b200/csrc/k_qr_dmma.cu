@@ -253,13 +253,11 @@ __global__ void __launch_bounds__(QD_T, 2) k_qr_dmma(Dev d, int cls, int cap) {
 }
 
 void launch_qr_dmma_class(const Dev& d, int c, cudaStream_t st) {
-  static bool attr_set = false;
-  static int sms = 0;
-  if (!attr_set) {
+  static DevOnce once;     // function attributes are per device
+  once.run([&] {
     cudaFuncSetAttribute(k_qr_dmma, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-    sms = sm_count();
-    attr_set = true;
-  }
+  });
+  const int sms = sm_count();
   const int caps[QR_DMMA_CLASSES] = {16, 32, 48, 64, 80};
   const int thr[QR_DMMA_CLASSES] = {64, 128, 128, 256, 256};
   const int kid[QR_DMMA_CLASSES] = {KID_QR_D16, KID_QR_D32, KID_QR_D48, KID_QR_D64, KID_QR_D80};

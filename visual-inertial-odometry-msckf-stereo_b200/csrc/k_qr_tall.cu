@@ -117,8 +117,7 @@ __global__ void __launch_bounds__(32 * TQ_WARPS, 3) k_qr_tall(Dev d) {
 }
 
 void launch_qr_tall(const Dev& d, cudaStream_t st) {
-  static int sms = 0;
-  if (!sms) sms = sm_count();
+  const int sms = sm_count();
   KLAUNCH(d, KID_QR_TALL, st, (k_qr_tall<<<std::min(d.F, sms * 3), 32 * TQ_WARPS, 0, st>>>(d)));
 }
 

@@ -543,11 +543,10 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
 void launch_observe(const Dev& d, const int* feat_off, const long long* ids, const double* uv, cudaStream_t st, const FrameIn* fin) {
   const size_t table = (size_t)d.Hs * (sizeof(long long) + sizeof(int));
   const int use_smem = table <= 96 * 1024;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DevOnce once;     // function attributes are per device
+  once.run([&] {
     cudaFuncSetAttribute(k_observe, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-    attr_set = true;
-  }
+  });
   KLAUNCH(d, KID_OBSERVE, st, (k_observe<<<d.F, ST, use_smem ? table : 0, st>>>(d, feat_off, ids, uv, fin, use_smem)));
 }
 void launch_classify_lost(const Dev& d, cudaStream_t st) {

@@ -374,12 +374,11 @@ void launch_triangulate_store(const Dev& d, cudaStream_t st) {
   int wpb = TRI_WPB;                     // fewer warps per CTA for wide windows so that the views fit shared memory
   while (wpb > 1 && (size_t)wpb * (32 / TRI_G) * (VIEW_DOUBLES * 2 * d.Nmax + 8) * sizeof(double) > 96 * 1024) wpb >>= 1;
   const size_t smem = (size_t)wpb * (32 / TRI_G) * (VIEW_DOUBLES * 2 * d.Nmax + 8) * sizeof(double);
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DevOnce once;     // function attributes are per device
+  once.run([&] {
     cudaFuncSetAttribute(k_triangulate_store, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     cudaFuncSetAttribute(k_triangulate_raw, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    attr_set = true;
-  }
+  });
   const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(12, (224 * 1024) / (smem + 1024)));     // 3 CTAs / SM at a 20-camera window
   KLAUNCH(d, KID_TRIANGULATE, st, (k_triangulate_store<<<sm_count() * per_sm, wpb * 32, smem, st>>>(d)));
 }
@@ -387,11 +386,10 @@ void launch_triangulate_store(const Dev& d, cudaStream_t st) {
 void launch_triangulate_raw(const Dev& d, int n, const int* obs_off, const double* uv, const double* cam_q, const double* cam_p,
                             double* pos, unsigned char* valid, int* solves, int max_obs, int mode, cudaStream_t st) {
   const size_t smem = (size_t)TRI_WPB * VIEW_DOUBLES * 2 * max_obs * sizeof(double);
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DevOnce once;     // function attributes are per device
+  once.run([&] {
     cudaFuncSetAttribute(k_triangulate_raw, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    attr_set = true;
-  }
+  });
   KLAUNCH(d, KID_TRIANGULATE, st,
           (k_triangulate_raw<<<(n + TRI_WPB - 1) / TRI_WPB, TRI_WPB * 32, smem, st>>>(d, n, obs_off, uv, cam_q, cam_p, pos, valid, solves,
                                                                                    max_obs, mode)));

@@ -538,13 +538,11 @@ __global__ void k_zero_krows_except(Dev d, int keep) {
 }
 
 void launch_qr_build(const Dev& d, cudaStream_t st) {
-  static bool attr_set = false;
-  static int sms = 0;
-  if (!attr_set) {
+  static DevOnce once;     // function attributes are per device
+  once.run([&] {
     cudaFuncSetAttribute(k_qr_build, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
-    sms = sm_count();
-    attr_set = true;
-  }
+  });
+  const int sms = sm_count();
   KLAUNCH(d, KID_QR, st, (k_qr_build<<<std::min(d.F, 2 * sms), QT, (size_t)d.qr_smem_doubles * sizeof(double), st>>>(d, d.qr_smem_doubles)));
 }
 void launch_qr_all(const Dev& d, cudaStream_t st) {

@@ -332,13 +332,11 @@ __global__ void __launch_bounds__(DT, KC > 64 ? 1 : 512 / DT) k_upd_dmma(Dev d, 
 
 template <int KC, int DT>
 static void launch_upd_class(const Dev& d, int cls, int kid, cudaStream_t st) {
-  static bool attr_set = false;
-  static int sms = 0;
-  if (!attr_set) {
+  static DevOnce once;     // function attributes are per device
+  once.run([&] {
     cudaFuncSetAttribute(k_upd_dmma<KC, DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-    sms = sm_count();
-    attr_set = true;
-  }
+  });
+  const int sms = sm_count();
   const size_t sm = upd_dmma_smem_bytes(d.nmax, KC);
   const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(512 / DT, (224 * 1024) / (sm + 1024)));    // 128 registers per thread
   KLAUNCH(d, kid, st, (k_upd_dmma<KC, DT><<<std::min(d.F, sms * per_sm), DT, sm, st>>>(d, cls)));

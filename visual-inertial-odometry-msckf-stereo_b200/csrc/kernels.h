@@ -1,10 +1,30 @@
 // Host-side launchers of the CUDA kernels (one translation unit per kernel family).
 #pragma once
 #include <cuda_runtime.h>
+#include <atomic>
+#include <mutex>
 #include <vector>
 #include "msckf_dev.cuh"
 
 namespace msckf {
+
+// One-time work per device (cudaFuncSetAttribute is per device; a process may hold contexts on several GPUs and
+// drive them from several host threads).
+struct DevOnce {
+  std::atomic<unsigned long long> done{0};
+  std::mutex mu;
+  template <class Fn>
+  void run(Fn&& fn) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const unsigned long long bit = 1ull << (dev & 63);
+    if (done.load(std::memory_order_acquire) & bit) return;
+    std::lock_guard<std::mutex> g(mu);
+    if (done.load(std::memory_order_relaxed) & bit) return;
+    fn();
+    done.fetch_or(bit, std::memory_order_release);
+  }
+};
 
 // Kernel ids for launch counting and optional per-kernel event timing (msckf_kernel_times).
 enum KernelId {

@@ -14,7 +14,7 @@ using namespace msckf;
 namespace msckf {
 const char* const kKernelNames[KID_COUNT] = {
     "k_propagate", "k_augment", "k_cam_prepare", "k_observe", "k_classify_lost", "k_prune_select", "k_triangulate", "k_plan_items",
-    "k_jacobian_gate", "k_jacobian_rows", "k_jacobian_big", "k_plan_stack", "k_qr", "k_qr_tall", "k_qr_d16", "k_qr_d32", "k_qr_d48", "k_qr_d64", "k_qr_d80", "k_upd_dmma16", "k_upd_dmma32", "k_upd_dmma48", "k_upd_dmma64", "k_upd_dmma80", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
+    "k_jacobian_gate", "k_jacobian_rows", "k_jacobian_big", "k_plan_stack", "k_qr", "k_qr_wide", "k_qr_tall", "k_qr_d16", "k_qr_d32", "k_qr_d48", "k_qr_d64", "k_qr_d80", "k_upd_dmma16", "k_upd_dmma32", "k_upd_dmma48", "k_upd_dmma64", "k_upd_dmma80", "k_upd_T", "k_upd_S", "k_upd_chol", "k_upd_trsm", "k_upd_inject",
     "k_upd_downdate", "k_remove_cams", "k_finish_frame", "k_reset", "misc"};
 
 void KTimer::begin(int id, cudaStream_t st) {
@@ -277,6 +277,8 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   const int row_cap = cfg->row_cap;
   d.max_rows = cfg->max_rows > 0 ? cfg->max_rows : ((row_cap > 0 ? row_cap : 1500) + 4 * d.Nmax + 8);
   d.Tk = d.nmax;
+  d.Sld = (d.Tk + 7) & ~7;
+  d.Uinv_stride = (long long)((d.Sld + 31) / 32) * 32 * 32;
   d.A_elems = (long long)((d.Tk + 3) / 4 * 4) * (d.nmax + 1);
   d.Adense_elems = (((long long)d.max_rows + 3) / 4 * 4) * (d.nmax + 1);
   // Jacobian records: (4M-3) x (6M+1) doubles per landmark that reaches the gate in one stage
@@ -296,7 +298,6 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
     const int per_sm = (int)std::max<long long>(1, std::min<long long>(8, (200 * 1024) / ((long long)d.jac_big_smem_doubles * 8 + 1024)));
     d.jac_big_grid = prop.multiProcessorCount * per_sm;
     d.jac_scratch_stride = 4 * M * (6 * M + 1) + (4 * M - 3) * (4 * M - 3);
-    d.qr_smem_doubles = qr_smem_doubles_for(d.Nmax);
     {   // stacked rows: the capped lost-landmark update, or the pruning update (5 rows per live landmark); everything when the cap is lifted
       const long long all = (long long)d.Fcap * (4 * M - 3);
       const long long capped = std::max<long long>(d.max_rows, 5LL * d.Fcap + 8);
@@ -309,8 +310,17 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
       for (int c = 0; c < UPD_DMMA_CLASSES; ++c)      // MSCKF_NO_DMMA: debugging knob, every update through the tiled kernels
         d.upd_dmma_ok[c] = (!getenv("MSCKF_NO_DMMA") && upd_dmma_smem_bytes(d.nmax, kc[c]) <= 220 * 1024) ? 1 : 0;
     }
-    const long long na = 6 * M, worst = 640 + na * (na + 1) / 2 + na + 32 * (na + 1) + 64;
-    d.qr_scratch_stride = worst > d.qr_smem_doubles ? na * (na + 1) / 2 + na + 256 * (na + 1) : 0;
+    {   // TSQR of wide / tall stacks (k_qr_wide): up to leaf_cap leaves per filter so that a single filter's stack
+        // spreads over the GPU, none when the batch already fills it; a tree of ceil(log2(leaf_cap)) levels
+      d.qr_capcols = (int)((6 * M + 1 + 7) & ~7LL);
+      long long lc = std::max<long long>(1, (2LL * prop.multiProcessorCount) / d.F);
+      lc = std::min<long long>(lc, prop.multiProcessorCount);
+      lc = std::min<long long>(lc, std::max<long long>(1, ((long long)d.rowmap_cap + 511) / 512));
+      d.qr_leaf_cap = (int)lc;
+      d.qr_levels = 0;
+      while ((1 << d.qr_levels) < d.qr_leaf_cap) d.qr_levels += 1;
+      d.Rnode_stride = (long long)d.qr_capcols * d.qr_capcols;
+    }
   }
 
   Params& hp = ctx->hp;
@@ -350,11 +360,11 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   DA(d.pool, (size_t)d.pool_cap); DA(d.stage_ctr, SC_COUNT); DA(d.item_lmask, F * Fc);
   DA(d.wl_tri, F * Fc); DA(d.wl_jac_small, JAC_CLASSES * F * Fc); DA(d.wl_jac_big, F * Fc);
   DA(d.jac_scratch, (size_t)d.jac_big_grid * d.jac_scratch_stride);
-  if (d.qr_scratch_stride) DA(d.qr_scratch, F * (size_t)d.qr_scratch_stride);
+  DA(d.Rnode, F * (size_t)d.qr_leaf_cap * (size_t)d.Rnode_stride);
   DA(d.Adense, (size_t)d.Adense_elems);
   DA(d.A, F * (size_t)d.A_elems); DA(d.m_rows, F); DA(d.m_pad, F); DA(d.n_act, F); DA(d.k_rows, F); DA(d.colmap, F * (size_t)d.nmax); DA(d.upd_path, F); DA(d.wl_upd_big, F); DA(d.wl_upd_dmma, (size_t)UPD_DMMA_CLASSES * F);
   DA(d.rowmap, F * (size_t)d.rowmap_cap); DA(d.qr_cls, F); DA(d.wl_qr, (size_t)QR_DMMA_CLASSES * F); DA(d.wl_qrb, F); DA(d.wl_qrt, F);
-  DA(d.T, F * (size_t)d.Tk * Tld(d)); DA(d.S, F * (size_t)d.Tk * d.Tk); DA(d.dx, F * (size_t)d.nmax);
+  DA(d.T, F * (size_t)d.Tk * Tld(d)); DA(d.S, F * (size_t)d.Tk * d.Sld); DA(d.TactT, F * (size_t)d.Tk * d.Sld); DA(d.Uinv, F * (size_t)d.Uinv_stride); DA(d.dx, F * (size_t)d.nmax);
   DA(d.log_id, 2 * F * Fc); DA(d.log_status, 2 * F * Fc); DA(d.log_gamma, 2 * F * Fc); DA(d.log_dof, 2 * F * Fc);
   DA(d.log_n, 2 * F); DA(d.log_upd, 2 * F * 2); DA(d.log_rm, F * 2);
   DA(d.frame_in, 1); DA(d.counters, F * NCNT); DA(d.err, 8); DA(d.did_reset, F); DA(d.imu_pub, F * IMU_STRIDE);

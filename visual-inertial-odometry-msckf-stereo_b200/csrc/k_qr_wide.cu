@@ -1,0 +1,362 @@
+// Stacked-Jacobian compression of measurement_update (msckf.py:549-553, numba _fastQR jit_utils.py:173-175) for stacks
+// that are too wide for the one-CTA classes of k_qr_dmma (more than 79 active columns: windows of 14 .. 64 camera states)
+// or too tall for one CTA to be reasonable (the 1e5-row stress frame): a tall-skinny QR (TSQR) over the whole grid.
+//
+//   leaves   k_qr_wide<RPL>(level = -1): the rows of a filter's stack are cut into nleaf contiguous pieces; one CTA per
+//            piece expands its rows chunk by chunk from the per-landmark records into shared memory and folds them into
+//            the piece's own triangular factor (the tpqrt scheme of k_qr_dmma.cu: panel of 8 reflectors by one warp,
+//            compact-WY trailing update W = R + V^T C, Y = T^T W, R -= Y, C -= V Y on DMMA tiles);
+//   tree     k_qr_wide<RPL>(level = 0, 1, ...): node a folds the factor of node a + 2^level into its own (the partner's
+//            rows arrive as chunks by bulk copy), log2(nleaf) launches;
+//   finish   k_qr_wide_finish: H_thin = R of node 0, r_thin = its last column, into the filter's compressed slot.
+//
+// The running factor R does not fit shared memory next to a chunk (185 x 185 doubles at a 30-state window, 393 x 393 at
+// 64), so it lives in L2 / HBM and only the 8-row slab a panel step touches is resident: slab p+1 is fetched by the TMA
+// engine (cp.async.bulk + mbarrier, two buffers) while panel p is applied, updated R tiles go straight back to global.
+// Look-ahead: the warp that factors panels first applies panel p to the columns of panel p+1 and factors it while the
+// other warps finish the trailing tiles of panel p -- one CTA barrier per panel and no warp waits for the factorisation.
+// Row signs of R differ from a sequential Householder QR; the update is invariant to them (as in k_qr_tall.cu).
+#include <algorithm>
+#include "msckf_dev.cuh"
+#include "kernels.h"
+#include "tma.cuh"
+
+namespace msckf {
+
+constexpr int QW_T = 256;
+constexpr int QW_LDL = 12;         // leading dimension of T and of the per-warp W / Y staging tiles
+constexpr unsigned QWFULL = 0xffffffffu;
+
+__host__ __device__ inline int qw_cap(int na) { return (na + 1 + 7) & ~7; }          // columns of [H | r], padded to 8
+// leaves of a stack of m rows: pieces of at least 512 rows, at most leaf_cap of them
+__host__ __device__ inline int qw_rows_per_leaf(int m, int leaf_cap, int CR) {
+  int nl = (m + 511) / 512;
+  nl = nl < 1 ? 1 : (nl > leaf_cap ? leaf_cap : nl);
+  const int per = (m + nl - 1) / nl;
+  return (per + CR - 1) / CR * CR;
+}
+
+static size_t qw_smem_bytes(int capmax, int CR) {
+  const size_t LP = capmax + 4;
+  return ((size_t)CR * LP + 2 * 8 * LP + 2 * 8 * QW_LDL + 8 * 8 * QW_LDL) * sizeof(double) + 64 * sizeof(int) + 64;
+}
+
+// Panel factorisation by one warp.  x[t][c] = C(lane + 32 t, j0 + c).  The 8 x 8 diagonal block of R comes from the
+// shared-memory slab (row jj of the slab = row j0 + jj of R), its new values go to global memory.  V replaces the
+// panel columns of the chunk, T goes to sTm.
+template <int RPL>
+__device__ __forceinline__ void qw_panel(const double* slab, double* Rg, int ldg, double* sC, double* sTm, int LP, int j0, int nrefl,
+                                         bool need_T, int lane) {
+  double x[RPL][8];
+#pragma unroll
+  for (int t = 0; t < RPL; ++t) {
+    const double* row = sC + (size_t)(lane + 32 * t) * LP + j0;
+#pragma unroll
+    for (int c = 0; c < 8; c += 2) {
+      const double2 v = *(const double2*)(row + c);
+      x[t][c] = v.x;
+      x[t][c + 1] = v.y;
+    }
+  }
+  double tau[8];
+#pragma unroll
+  for (int jj = 0; jj < 8; ++jj) {
+    tau[jj] = 0.0;
+    if (jj < nrefl) {                                     // warp-uniform
+      double s[8];
+#pragma unroll
+      for (int c = jj; c < 8; ++c) {
+        double a = 0.0;
+#pragma unroll
+        for (int t = 0; t < RPL; ++t) a += x[t][jj] * x[t][c];
+        s[c] = a;
+      }
+      double rrow[8];
+#pragma unroll
+      for (int c = jj; c < 8; ++c) rrow[c] = slab[jj * LP + j0 + c];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int c = jj; c < 8; ++c) s[c] += __shfl_xor_sync(QWFULL, s[c], o);
+      }
+      if (s[jj] != 0.0) {
+        const double alpha = rrow[jj];
+        const double n2 = alpha * alpha + s[jj];
+        const double rn = rsqrt(n2);                       // 1 / |beta|
+        const double nrm = n2 * rn;
+        const double beta = (alpha >= 0) ? -nrm : nrm;
+        const double tj = (beta - alpha) * ((alpha >= 0) ? -rn : rn), sc = 1.0 / (alpha - beta);
+        tau[jj] = tj;
+#pragma unroll
+        for (int t = 0; t < RPL; ++t) x[t][jj] *= sc;
+#pragma unroll
+        for (int c = jj + 1; c < 8; ++c) {
+          const double w = tj * (rrow[c] + s[c] * sc);
+          if (lane == 0) Rg[(size_t)(j0 + jj) * ldg + j0 + c] = rrow[c] - w;
+#pragma unroll
+          for (int t = 0; t < RPL; ++t) x[t][c] -= w * x[t][jj];
+        }
+        if (lane == 0) Rg[(size_t)(j0 + jj) * ldg + j0 + jj] = beta;
+      }
+    }
+  }
+  if (!need_T) return;
+#pragma unroll
+  for (int t = 0; t < RPL; ++t) {
+    double* row = sC + (size_t)(lane + 32 * t) * LP + j0;
+#pragma unroll
+    for (int c = 0; c < 8; c += 2) *(double2*)(row + c) = make_double2(x[t][c], x[t][c + 1]);
+  }
+  // T (8 x 8 upper): T(i,i) = tau_i, T(i,j) = -tau_j sum_{l=i}^{j-1} T(i,l) (v_l . v_j); lane i < 8 owns row i
+  double gm[8][8];
+#pragma unroll
+  for (int j = 1; j < 8; ++j)
+#pragma unroll
+    for (int l = 0; l < j; ++l) {
+      double a = 0.0;
+#pragma unroll
+      for (int t = 0; t < RPL; ++t) a += x[t][l] * x[t][j];
+      gm[l][j] = a;
+    }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+    for (int j = 1; j < 8; ++j)
+#pragma unroll
+      for (int l = 0; l < j; ++l) gm[l][j] += __shfl_xor_sync(QWFULL, gm[l][j], o);
+  }
+  double trow[8];
+  const int ri = lane & 7;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    double acc = 0.0;
+#pragma unroll
+    for (int l = 0; l < j; ++l) acc += trow[l] * gm[l][j];
+    trow[j] = (ri == j) ? tau[j] : ((ri < j) ? -tau[j] * acc : 0.0);
+  }
+  if (lane < 8) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sTm[ri * QW_LDL + j] = trow[j];
+  }
+}
+
+// Applies the block reflector of panel j0 (V in the chunk, T in sTm) to the 8-column tile at c0: R rows from the slab,
+// new R rows to global memory, chunk columns updated in place.
+__device__ __forceinline__ void qw_apply(const double* slab, double* Rg, int ldg, double* sC, const double* sTm, double* sYw, int LP, int j0,
+                                         int c0, int crk, int crt, int g, int tg) {
+  const double r_old0 = slab[g * LP + c0 + 2 * tg], r_old1 = slab[g * LP + c0 + 2 * tg + 1];
+  double w0[4] = {r_old0, 0.0, 0.0, 0.0}, w1[4] = {r_old1, 0.0, 0.0, 0.0};
+  const double* va = sC + (size_t)tg * LP + j0 + g;
+  const double* cb = sC + (size_t)tg * LP + c0 + g;
+  int ks = 0;
+  for (; ks + 4 <= crk; ks += 4) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) dmma(w0[u], w1[u], va[(size_t)(4 * (ks + u)) * LP], cb[(size_t)(4 * (ks + u)) * LP]);
+  }
+  for (; ks < crk; ++ks) dmma(w0[0], w1[0], va[(size_t)4 * ks * LP], cb[(size_t)4 * ks * LP]);
+  const double ww0 = (w0[0] + w0[1]) + (w0[2] + w0[3]), ww1 = (w1[0] + w1[1]) + (w1[2] + w1[3]);
+  // Y = T^T W
+  sYw[g * QW_LDL + 2 * tg] = ww0;
+  sYw[g * QW_LDL + 2 * tg + 1] = ww1;
+  __syncwarp();
+  const double wb0 = sYw[tg * QW_LDL + g], wb1 = sYw[(4 + tg) * QW_LDL + g];
+  const double ta0 = sTm[tg * QW_LDL + g], ta1 = sTm[(4 + tg) * QW_LDL + g];
+  double y0 = 0.0, y1 = 0.0;
+  dmma(y0, y1, ta0, wb0);
+  dmma(y0, y1, ta1, wb1);
+  *(double2*)(Rg + (size_t)(j0 + g) * ldg + c0 + 2 * tg) = make_double2(r_old0 - y0, r_old1 - y1);
+  __syncwarp();
+  sYw[g * QW_LDL + 2 * tg] = y0;
+  sYw[g * QW_LDL + 2 * tg + 1] = y1;
+  __syncwarp();
+  const double yb0 = sYw[tg * QW_LDL + g], yb1 = sYw[(4 + tg) * QW_LDL + g];
+  // C(:, tile) -= V Y
+  for (int rt = 0; rt < crt; ++rt) {
+    const double* vr = sC + (size_t)(8 * rt + g) * LP + j0 + tg;
+    double2* cp = (double2*)(sC + (size_t)(8 * rt + g) * LP + c0 + 2 * tg);
+    double2 cv = *cp;
+    dmma(cv.x, cv.y, -vr[0], yb0);
+    dmma(cv.x, cv.y, -vr[4], yb1);
+    *cp = cv;
+  }
+  __syncwarp();
+}
+
+template <int RPL>
+__global__ void __launch_bounds__(QW_T, 1) k_qr_wide(Dev d, int level) {
+  constexpr int CR = 32 * RPL;
+  extern __shared__ __align__(128) double qs[];
+  __shared__ uint64_t s_slab[2], s_rows;
+  __shared__ int s_c0;
+  const int capmax = d.qr_capcols, LP = capmax + 4, ldg = capmax;
+  double* sC = qs;                                    // [CR][LP]   chunk of stacked rows
+  double* sSlab = sC + (size_t)CR * LP;               // [2][8][LP] the 8 rows of R a panel step reads
+  double* sTm = sSlab + 2 * 8 * LP;                   // [2][8][QW_LDL]
+  double* sY = sTm + 2 * 8 * QW_LDL;                  // [8 warps][8][QW_LDL]
+  int* camcol = (int*)(sY + 8 * 8 * QW_LDL);          // [64] logical camera -> active column block
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, tg = lane & 3;
+  double* sYw = sY + warp * 8 * QW_LDL;
+  if (tid == 0) {
+    mbar_init(&s_slab[0], 1);
+    mbar_init(&s_slab[1], 1);
+    mbar_init(&s_rows, 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  unsigned su[2] = {0u, 0u}, srows = 0u;              // completed uses of each barrier (phase parity)
+  const int nlist = (int)d.stage_ctr[SC_NQR_BUILD];
+  const int leaf_cap = d.qr_leaf_cap;
+
+  for (int item = blockIdx.x; item < nlist * leaf_cap; item += gridDim.x) {
+    const int f = d.wl_qrb[item / leaf_cap], node = item % leaf_cap;
+    const int m = d.m_rows[f], na = d.n_act[f];
+    if (m <= na) continue;                            // not compressed (msckf.py:549): k_qr_build copies the rows out
+    const int cap = qw_cap(na), nct = cap >> 3, npan = (na + 7) >> 3;
+    const int rpl = qw_rows_per_leaf(m, leaf_cap, CR), nleaf = (m + rpl - 1) / rpl;
+    int rb = 0, re = 0;
+    const double* Rb = nullptr;
+    if (level < 0) {
+      if (node >= nleaf) continue;
+      rb = node * rpl;
+      re = min(m, rb + rpl);
+    } else {
+      if ((node & ((2 << level) - 1)) != 0 || node + (1 << level) >= nleaf) continue;
+      Rb = d.Rnode + ((size_t)f * leaf_cap + node + (1 << level)) * d.Rnode_stride;
+      re = na;                                        // the partner's factor has n_a rows
+    }
+    double* Rg = d.Rnode + ((size_t)f * leaf_cap + node) * d.Rnode_stride;
+    const size_t fb = (size_t)f * d.Fcap;
+    const int* cm = d.colmap + (size_t)f * d.nmax;
+    const int* rmap = d.rowmap + (size_t)f * d.rowmap_cap;
+    __syncthreads();
+    if (level < 0) {
+      for (int e = tid; e < cap * (ldg / 2); e += QW_T) ((double2*)Rg)[e] = make_double2(0.0, 0.0);
+      for (int c = tid; c < 64; c += QW_T) camcol[c] = -1;
+      fence_proxy_async();
+      __syncthreads();
+      for (int b = tid; b < na / 6; b += QW_T) camcol[(cm[6 * b] - NI) / 6] = b;
+    }
+
+    for (int r0 = rb; r0 < re; r0 += CR) {
+      const int cr = min(CR, re - r0);
+      const int crk = (cr + 3) >> 2, crt = (cr + 7) >> 3;
+      int pb0;
+      __syncthreads();                                // the previous chunk is folded (and its R stores fenced)
+      if (level < 0) {
+        // ---- expand the rows of this chunk from the landmark records (zero fill, then 6-column blocks and the residual)
+        for (int e = tid; e < CR * LP / 2; e += QW_T) ((double2*)sC)[e] = make_double2(0.0, 0.0);
+        if (tid == 0) s_c0 = na;
+        __syncthreads();
+        for (int i = tid; i < cr; i += QW_T) {
+          const int rm = rmap[r0 + i];
+          const int kk = rm >> 8, li = rm & 255;
+          const int rows = d.item_rows[fb + kk], M = (rows + 3) / 4;
+          unsigned long long lmask = d.item_lmask[fb + kk];
+          const double* rec = d.pool + d.item_off[fb + kk] + (size_t)li * (6 * M + 1);
+          double* row = sC + (size_t)i * LP;
+          const int first = camcol[__ffsll((long long)lmask) - 1];
+          for (int a = 0; a < M; ++a) {
+            const int cam = __ffsll((long long)lmask) - 1;
+            lmask &= lmask - 1;
+            double* dst = row + 6 * camcol[cam];
+#pragma unroll
+            for (int e = 0; e < 6; ++e) dst[e] = rec[6 * a + e];
+          }
+          row[na] = rec[6 * M];
+          atomicMin(&s_c0, 6 * first);
+        }
+        __syncthreads();
+        pb0 = s_c0 >> 3;                              // columns before the chunk's first non-zero column need no elimination
+      } else {
+        // ---- rows r0 .. r0 + cr of the partner's factor, columns r0 .. cap (zero before the diagonal), by bulk copy
+        pb0 = r0 >> 3;
+        for (int e = tid; e < (CR - cr) * LP; e += QW_T) sC[(size_t)cr * LP + e] = 0.0;
+        if (tid == 0) mbar_arrive_expect_tx(&s_rows, (unsigned)((size_t)cr * (cap - r0) * sizeof(double)));
+        __syncthreads();
+        for (int i = tid; i < cr; i += QW_T) bulk_g2s(sC + (size_t)i * LP + r0, Rb + (size_t)(r0 + i) * ldg + r0, (cap - r0) * sizeof(double), &s_rows);
+        mbar_wait(&s_rows, srows & 1u);
+        srows += 1;
+      }
+      auto issue_slab = [&](int pb) {                 // warp 1, lanes 0..7: row i of slab pb, columns 8 pb .. cap
+        const int b = pb & 1;
+        if (lane == 0) mbar_arrive_expect_tx(&s_slab[b], (unsigned)(8 * (cap - 8 * pb) * sizeof(double)));
+        __syncwarp();
+        if (lane < 8) bulk_g2s(sSlab + (size_t)(b * 8 + lane) * LP + 8 * pb, Rg + (size_t)(8 * pb + lane) * ldg + 8 * pb, (cap - 8 * pb) * sizeof(double), &s_slab[b]);
+      };
+      if (warp == 1) issue_slab(pb0);
+      if (warp == 0) {
+        mbar_wait(&s_slab[pb0 & 1], su[pb0 & 1] & 1u);
+        qw_panel<RPL>(sSlab + (size_t)(pb0 & 1) * 8 * LP, Rg, ldg, sC, sTm + (pb0 & 1) * 8 * QW_LDL, LP, 8 * pb0, min(8, na - 8 * pb0), pb0 + 1 < nct, lane);
+      }
+      __syncthreads();
+      for (int pb = pb0; pb < npan; ++pb) {
+        const int cur = pb & 1, j0 = 8 * pb;
+        const double* slab = sSlab + (size_t)cur * 8 * LP;
+        const double* Tm = sTm + cur * 8 * QW_LDL;
+        const bool ahead = pb + 1 < npan;             // another panel follows: warp 0 looks ahead
+        if (ahead && warp == 1) issue_slab(pb + 1);
+        mbar_wait(&s_slab[cur], su[cur] & 1u);        // (already complete for warp 0)
+        if (ahead) {
+          if (warp == 0) {
+            qw_apply(slab, Rg, ldg, sC, Tm, sYw, LP, j0, j0 + 8, crk, crt, g, tg);
+            mbar_wait(&s_slab[cur ^ 1], su[cur ^ 1] & 1u);
+            qw_panel<RPL>(sSlab + (size_t)(cur ^ 1) * 8 * LP, Rg, ldg, sC, sTm + (cur ^ 1) * 8 * QW_LDL, LP, j0 + 8, min(8, na - j0 - 8), pb + 2 < nct, lane);
+          } else {
+            for (int ct = pb + 2 + (warp - 1); ct < nct; ct += QW_T / 32 - 1) qw_apply(slab, Rg, ldg, sC, Tm, sYw, LP, j0, 8 * ct, crk, crt, g, tg);
+          }
+        } else {
+          for (int ct = pb + 1 + warp; ct < nct; ct += QW_T / 32) qw_apply(slab, Rg, ldg, sC, Tm, sYw, LP, j0, 8 * ct, crk, crt, g, tg);
+        }
+        su[cur] += 1;
+        if (pb + 1 == npan) fence_proxy_async();      // R rows written with ordinary stores are read back by the TMA engine
+        __syncthreads();
+      }
+    }
+  }
+}
+
+// H_thin = R (k = n_a rows), r_thin = first n_a entries of Q^T r, from the root of the filter's tree
+__global__ void __launch_bounds__(QW_T) k_qr_wide_finish(Dev d) {
+  const int nlist = (int)d.stage_ctr[SC_NQR_BUILD];
+  for (int w = blockIdx.x; w < nlist; w += gridDim.x) {
+    const int f = d.wl_qrb[w];
+    const int m = d.m_rows[f], na = d.n_act[f], nc = na + 1, mp = d.m_pad[f];
+    if (m <= na) continue;
+    const double* Rg = d.Rnode + (size_t)f * d.qr_leaf_cap * d.Rnode_stride;
+    const int ldg = d.qr_capcols;
+    double* A = d.A + (size_t)f * d.A_elems;
+    for (int e = threadIdx.x; e < na * nc; e += QW_T) {
+      const int i = e % na, c = e / na;
+      A[(size_t)c * mp + i] = (c >= i) ? Rg[(size_t)i * ldg + c] : 0.0;
+    }
+  }
+}
+
+template <int RPL>
+static void launch_qw(const Dev& d, cudaStream_t st) {
+  static DevOnce once;     // function attributes are per device
+  once.run([&] { cudaFuncSetAttribute(k_qr_wide<RPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); });
+  const int sms = sm_count();
+  const size_t sm = qw_smem_bytes(d.qr_capcols, 32 * RPL);
+  const int grid = (int)std::min<long long>((long long)d.F * d.qr_leaf_cap, 2LL * sms);
+  for (int level = -1; level < d.qr_levels; ++level)
+    KLAUNCH(d, KID_QR_WIDE, st, (k_qr_wide<RPL><<<grid, QW_T, sm, st>>>(d, level)));
+  KLAUNCH(d, KID_QR_WIDE, st, (k_qr_wide_finish<<<std::min(d.F, 2 * sms), QW_T, 0, st>>>(d)));
+}
+
+int qr_wide_rows_per_chunk(int Nmax) {
+  const int capmax = qw_cap(6 * Nmax);
+  for (int rpl = 4; rpl >= 1; rpl >>= 1)
+    if (qw_smem_bytes(capmax, 32 * rpl) <= 226 * 1024) return 32 * rpl;
+  return 0;
+}
+int qr_wide_leaf_rows(int m, int leaf_cap, int CR) { return qw_rows_per_leaf(m, leaf_cap, CR); }
+
+void launch_qr_wide(const Dev& d, cudaStream_t st) {
+  const int cr = qr_wide_rows_per_chunk(d.Nmax);
+  if (cr == 128) launch_qw<4>(d, st);
+  else if (cr == 64) launch_qw<2>(d, st);
+  else launch_qw<1>(d, st);
+}
+
+}  // namespace msckf

@@ -500,7 +500,8 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
     const int kr = (m > na) ? na : m;
     int qcls = -1;
     if (m > 0) {
-      qcls = (m <= na || na + 1 > 80) ? QR_DMMA_CLASSES : (na + 1 <= 16 ? 0 : (na + 1 <= 32 ? 1 : (na + 1 <= 48 ? 2 : (na + 1 <= 64 ? 3 : 4))));
+      // not compressed, wider than the one-CTA classes, or (when the batch leaves SMs idle) tall enough to be worth a tree: k_qr_build / k_qr_wide
+      qcls = (m <= na || na + 1 > 80 || (d.qr_leaf_cap > 1 && m >= 2048)) ? QR_DMMA_CLASSES : (na + 1 <= 16 ? 0 : (na + 1 <= 32 ? 1 : (na + 1 <= 48 ? 2 : (na + 1 <= 64 ? 3 : 4))));
       // pruning stage: every landmark sits on the two cameras being removed (5 rows x 12 columns each): tall-skinny TSQR
       if (stage == 1 && qcls == 0 && na == 12 && d.qr_tall_ok) {
         qcls = QR_DMMA_CLASSES + 1;

@@ -29,7 +29,7 @@ struct DevOnce {
 // Kernel ids for launch counting and optional per-kernel event timing (msckf_kernel_times).
 enum KernelId {
   KID_PROPAGATE = 0, KID_AUGMENT, KID_CAM_PREPARE, KID_OBSERVE, KID_CLASSIFY_LOST, KID_PRUNE_SELECT, KID_TRIANGULATE, KID_PLAN_ITEMS,
-  KID_JACOBIAN_GATE, KID_JACOBIAN_ROWS, KID_JACOBIAN_BIG, KID_PLAN_STACK, KID_QR, KID_QR_TALL, KID_QR_D16, KID_QR_D32, KID_QR_D48, KID_QR_D64, KID_QR_D80, KID_UPD_DMMA16, KID_UPD_DMMA32, KID_UPD_DMMA48, KID_UPD_DMMA64, KID_UPD_DMMA80, KID_UPD_T, KID_UPD_S, KID_UPD_CHOL, KID_UPD_TRSM, KID_UPD_INJECT,
+  KID_JACOBIAN_GATE, KID_JACOBIAN_ROWS, KID_JACOBIAN_BIG, KID_PLAN_STACK, KID_QR, KID_QR_WIDE, KID_QR_TALL, KID_QR_D16, KID_QR_D32, KID_QR_D48, KID_QR_D64, KID_QR_D80, KID_UPD_DMMA16, KID_UPD_DMMA32, KID_UPD_DMMA48, KID_UPD_DMMA64, KID_UPD_DMMA80, KID_UPD_T, KID_UPD_S, KID_UPD_CHOL, KID_UPD_TRSM, KID_UPD_INJECT,
   KID_UPD_DOWNDATE, KID_REMOVE_CAMS, KID_FINISH_FRAME, KID_RESET, KID_MISC, KID_COUNT
 };
 extern const char* const kKernelNames[KID_COUNT];
@@ -128,15 +128,15 @@ void launch_gate_dense(const Dev& d, int filter, const double* H, const double* 
                        double* scratch, double* out_gamma, int* out_pass, cudaStream_t st);
 
 // k_update.cu
-void launch_qr_build(const Dev& d, cudaStream_t st);
-void launch_qr_all(const Dev& d, cudaStream_t st);         // every compression class of a stage, concurrently
+void launch_qr_build(const Dev& d, int stage, cudaStream_t st);   // wide / tall / uncompressed stacks
+void launch_qr_wide(const Dev& d, cudaStream_t st);               // k_qr_wide.cu: TSQR over the grid
+int qr_wide_rows_per_chunk(int Nmax);
 void launch_qr_dmma(const Dev& d, Fork& fk);               // k_qr_dmma.cu
 void launch_qr_dmma_class(const Dev& d, int cls, cudaStream_t st);
 void launch_upd_dmma_class(const Dev& d, int cls, cudaStream_t st);   // k_update_dmma.cu
 void launch_compress_update(const Dev& d, int stage, cudaStream_t st); // QR + update of every class, each class on its own stream
 void launch_qr_tall(const Dev& d, cudaStream_t st);                    // k_qr_tall.cu
 void launch_qr_dense(const Dev& d, int filter, int mp_dense, cudaStream_t st);
-int qr_smem_doubles_for(int Nmax);
 void launch_update(const Dev& d, int stage, cudaStream_t st);
 void launch_update_tiled(const Dev& d, cudaStream_t st);
 void launch_update_dmma(const Dev& d, Fork& fk);             // k_update_dmma.cu

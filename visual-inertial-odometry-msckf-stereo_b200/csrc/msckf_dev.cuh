@@ -118,9 +118,11 @@ struct Dev {
   long long jac_scratch_stride;
   int jac_big_smem_doubles, jac_big_grid;
   int jac_rows_ok;         // short tracks go through the lane-per-row kernel (debug knob MSCKF_NO_JAC_ROWS)
-  int qr_smem_doubles;     // dynamic shared memory of k_qr_build
-  double* qr_scratch;      // [F][qr_scratch_stride] fallback for R + row chunk when they exceed shared memory (may be null)
-  long long qr_scratch_stride;
+  int qr_capcols;          // columns of a TSQR node: 6 Nmax + 1 rounded up to 8 (k_qr_wide)
+  int qr_leaf_cap;         // leaves per filter at most
+  int qr_levels;           // tree levels launched per stage: ceil(log2(qr_leaf_cap))
+  double* Rnode;           // [F][qr_leaf_cap][Rnode_stride] triangular factors of the TSQR nodes, row-major, ld = qr_capcols
+  long long Rnode_stride;
   double* A;               // [F][A_elems] compressed Jacobian H_thin | r_thin, column-major, ld = m_pad
   double* Adense;          // [Adense_elems] caller-supplied dense H of the measurement_update API (one filter at a time)
   long long Adense_elems;
@@ -141,7 +143,11 @@ struct Dev {
   int* wl_upd_dmma;        // [UPD_DMMA_CLASSES][F] filters of the tensor-pipe update classes
   int upd_dmma_ok[UPD_DMMA_CLASSES];   // class fits shared memory for this window size
   double* T;               // [F][Tk][ld+8]  H_thin P | r  -> W | y
-  double* S;               // [F][Tk][Tk]
+  double* S;               // [F][Tk][Sld]  innovation covariance -> its upper Cholesky factor (wide updates)
+  int Sld;                 // Tk rounded up to 8: rows are 64-byte aligned for the bulk copies
+  double* TactT;           // [F][Tk][Sld]  (H_thin P[act,act])^T, the operand of S
+  double* Uinv;            // [F][Uinv_stride] inverses of the 32 x 32 diagonal blocks of the factor
+  long long Uinv_stride;
   double* dx;              // [F][nmax]
   // ---- logs / counters / errors
   long long* log_id;       // [2][F][Fcap]

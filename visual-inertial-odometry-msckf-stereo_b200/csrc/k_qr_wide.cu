@@ -335,7 +335,7 @@ __global__ void __launch_bounds__(QW_T) k_qr_wide_finish(Dev d) {
 template <int RPL>
 static void launch_qw(const Dev& d, cudaStream_t st) {
   static DevOnce once;     // function attributes are per device
-  once.run([&] { cudaFuncSetAttribute(k_qr_wide<RPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); });
+  once.run([&] { cudaFuncSetAttribute(k_qr_wide<RPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024); });
   const int sms = sm_count();
   const size_t sm = qw_smem_bytes(d.qr_capcols, 32 * RPL);
   const int grid = (int)std::min<long long>((long long)d.F * d.qr_leaf_cap, 2LL * sms);

@@ -270,6 +270,22 @@ int msckf_undistort_stereo(int32_t device, int32_t n, const double* cam0_pts, co
                            const double* intr0, int32_t model0, const double* dist0, const double* intr1,
                            int32_t model1, const double* dist1, double* uv_out);
 
+/* ---- the step before that: synthetic message generator (replaces the host generator of the benchmark) ---- */
+/* One lock-step frame for n_filters Monte-Carlo filters, written in DEVICE memory in the layout msckf_feature_callback_dev
+ * takes.  Filter f adds the noise stream of seed (seed0 + f) to the frame's clean structure (host arrays: the n_imu samples
+ * ts / gyro_clean / acc_clean [.][3] selected for this frame, the n_features tracked ids and their noise-free normalised
+ * coordinates uv_clean [.][4]); every random number is a pure function of (seed, sample index or (frame, feature id)), so
+ * any filter or frame can be regenerated alone.  Noise model of SURVEY 8d: white IMU noise (discrete sigmas) on top of
+ * constant biases; pixel noise sigma_z plus, for outlier_frac of the observations, a gross error of outlier_sigma.
+ * sample0 = global index of the frame's first IMU sample.  Outputs (device): imu_off [F+1], ts_out [F*n_imu],
+ * gyro / acc [F*n_imu][3], cam_ids [F] (= cam_id), feat_off [F+1], ids_out [F*n_features], uv [F*n_features][4]. */
+int msckf_synth_frame(int32_t device, int32_t n_filters, uint64_t seed0, int64_t frame, int32_t n_imu, int64_t sample0,
+                      const double* ts, const double* gyro_clean, const double* acc_clean, const double* gyro_bias /*[3]*/,
+                      const double* acc_bias /*[3]*/, double sigma_gyro, double sigma_acc, int32_t n_features,
+                      const int64_t* ids, const double* uv_clean, double sigma_z, double outlier_frac, double outlier_sigma,
+                      int64_t cam_id, int32_t* imu_off, double* ts_out, double* gyro, double* acc, int64_t* cam_ids,
+                      int32_t* feat_off, int64_t* ids_out, double* uv);
+
 /* Timing of the last msckf_feature_callback*: device milliseconds per stage (CUDA events on the
  * context's stream): [0] propagate+augment [1] observe [2] remove_lost [3] prune [4] total. */
 int msckf_last_timing(msckf_ctx* ctx, float* ms /*[5]*/);

@@ -61,6 +61,35 @@ def rel_err(a, b):
     return d / s
 
 
+def block_rel_err(P, Pref):
+    """Per-block error of a covariance (IMU core 0:15, extrinsics 15:21, every camera state 6 wide; diagonal and cross
+    blocks).  Returns (scaled, strict):
+      scaled  max over blocks of |dP_ij|_F / sqrt(|Pref_ii|_F |Pref_jj|_F)  -- every block on its natural scale
+              (|P_ij| <= sqrt(P_ii P_jj)), so a small block next to a large one is not hidden by the norm of all of P;
+      strict  max over the blocks that are not numerically zero (|Pref_ij| >= 1e-6 of that scale) of |dP_ij|_F / |Pref_ij|_F.
+    """
+    P, Pref = np.asarray(P, float), np.asarray(Pref, float)
+    if P.shape != Pref.shape:
+        return float('inf'), float('inf')
+    n = P.shape[0]
+    edges = [0, 15, 21] + list(range(27, n + 1, 6))
+    nb = len(edges) - 1
+    D = P - Pref
+
+    def fro_blocks(M):
+        sq = np.add.reduceat(np.add.reduceat(M * M, edges[:-1], axis=0), edges[:-1], axis=1)
+        return np.sqrt(sq)
+
+    nd, nr = fro_blocks(D), fro_blocks(Pref)
+    diag = np.maximum(np.diag(nr), 1e-300)
+    scale = np.sqrt(np.outer(diag, diag))
+    scaled = float(np.max(nd / scale))
+    sig = nr >= 1e-6 * scale
+    strict = float(np.max(nd[sig] / nr[sig])) if sig.any() else 0.0
+    assert nb >= 2
+    return scaled, strict
+
+
 def compare_snapshots(a, b):
     """Returns dict of relative errors (state vector and P, norm-wise) + exact-match flags."""
     out = {
@@ -161,3 +190,109 @@ def device_filter_from_units(u, max_cam=12, feature_capacity=256):
     filt.is_first_img = False
     filt.tracking_rate = float(u['state_tracking_rate'])
     return filt
+
+
+def device_decisions(filt):
+    """(gate decisions, gammas, removed cam ids or None, [update rows]) of the frame just processed."""
+    from msckf_b200 import capi
+    dec, gam, upd = [], [], []
+    rm = None
+    for stage in (0, 1):
+        log = filt.stage_log(stage)
+        for s, g in zip(log['status'], log['gamma']):
+            if s in (capi.FEAT_GATE_PASS, capi.FEAT_GATE_FAIL):
+                dec.append(s == capi.FEAT_GATE_PASS)
+                gam.append(g)
+        if log['update_rows'] > 0:
+            upd.append(log['update_rows'])
+        if stage == 1 and log['removed_cam_ids'][0] >= 0:
+            rm = [int(x) for x in log['removed_cam_ids']]
+    return dec, gam, rm, upd
+
+
+def run_pair(stream, max_cam, n_frames, feature_capacity=1024, row_cap=None, before_frame=None, after_frame=None,
+             check_P_every=1):
+    """Steps the oracle and the device filter side by side through feature_callback; checks ids and decisions at every
+    frame and returns the worst errors seen.
+
+      worst['P']        |dP| / |P| over the whole covariance (north_star: 1e-9)
+      worst['P_block']  the same per block on its natural scale, worst['P_block_strict'] relative to the block itself
+                        (block_rel_err above)
+      worst['gate_margin']  smallest |gamma - threshold| / threshold over all gates: how close any decision came to flipping
+      counts['not_spd'] landmarks the device rejected because its innovation covariance was not SPD (must be 0: the
+                        reference's LU would have produced some gamma there)
+    before_frame(f, oracle_filter, device_filter) may perturb both filters before frame f (forced resets etc.);
+    after_frame(f, oracle_filter, device_filter) may read further diagnostics."""
+    from oracle import msckf_oracle as orc
+    from msckf_b200 import capi
+    from msckf_b200.config import ConfigEuRoC
+    from msckf_b200.msckf import MSCKF
+    ocfg = orc.ConfigEuRoC()
+    ocfg._vio_max_cam_state_size__ = max_cam
+    of = orc.MSCKF(ocfg)
+    if row_cap is not None:
+        of.ROW_CAP = row_cap
+    dcfg = ConfigEuRoC()
+    dcfg._vio_max_cam_state_size__ = max_cam
+    if row_cap is not None:
+        dcfg.row_cap = row_cap if row_cap < 10 ** 8 else 0      # <= 0 lifts the cap in the library
+    df = MSCKF(dcfg, feature_capacity=feature_capacity)
+    worst = {'imu': 0.0, 'P': 0.0, 'P_block': 0.0, 'P_block_strict': 0.0, 'cams': 0.0, 'extr': 0.0, 'pos_m': 0.0,
+             'gate_margin': float('inf')}
+    counts = {'gates': 0, 'pass': 0, 'prunes': 0, 'updates': 0, 'resets': 0, 'not_spd': 0, 'max_update_rows': 0}
+    msgs = stream.imu_msgs()
+    k = 0
+    try:
+        for f in range(n_frames):
+            if before_frame is not None:
+                before_frame(f, of, df)
+            t = stream.frame_ts[f]
+            while k < len(msgs) and msgs[k].vio_timestamp__ <= t:
+                of.imu_callback(msgs[k])
+                df.imu_callback(msgs[k])
+                k += 1
+            of.log = {}
+            ro = of.feature_callback(stream.feature_msg(f))
+            rd = df.feature_callback(stream.feature_msg(f))
+            assert (ro is None) == (rd is None)
+            with_P = (f % check_P_every == 0) or f == n_frames - 1
+            so, sd = snapshot(of, with_P), snapshot(df, with_P)
+            assert np.array_equal(sd['cam_ids'], so['cam_ids']), f
+            assert np.array_equal(sd['map_ids'], so['map_ids']), f
+            for key in ('imu', 'cams', 'extr'):
+                worst[key] = max(worst[key], rel_err(sd[key], so[key]))
+            if with_P:
+                worst['P'] = max(worst['P'], rel_err(sd['P'], so['P']))
+                bs, bt = block_rel_err(sd['P'], so['P'])
+                worst['P_block'] = max(worst['P_block'], bs)
+                worst['P_block_strict'] = max(worst['P_block_strict'], bt)
+            worst['pos_m'] = max(worst['pos_m'], float(np.linalg.norm(sd['imu'][13:16] - so['imu'][13:16])))
+            dec, gam, rm, upd = device_decisions(df)
+            ogates = of.log.get('gate', [])
+            assert dec == [x[2] for x in ogates], f
+            if ogates:
+                og = np.array([x[0] for x in ogates])
+                thr = np.array([x[1] for x in ogates])
+                assert np.all(np.abs(np.array(gam) - og) <= 1e-7 * np.abs(og)), f
+                worst['gate_margin'] = min(worst['gate_margin'], float(np.min(np.abs(og - thr) / thr)))
+            orm = of.log.get('rm_cam_ids', [])
+            assert (rm is None and not orm) or (orm and rm == [int(x) for x in orm[0]]), f
+            did_reset = bool(of.log.get('online_reset'))
+            assert bool(df.did_reset) == did_reset, f                     # online_reset decision (msckf.py:859-886)
+            counts['gates'] += len(dec)
+            counts['pass'] += sum(dec)
+            counts['prunes'] += int(rm is not None)
+            counts['updates'] += len(upd)
+            counts['resets'] += int(did_reset)
+            counts['max_update_rows'] = max([counts['max_update_rows']] + list(upd))
+            if after_frame is not None:
+                after_frame(f, of, df)
+            if ro is not None:
+                assert rel_err(rd.pose._vio_t__, ro.pose._vio_t__) < 1e-8 or np.linalg.norm(ro.pose._vio_t__) < 1e-6
+                assert rel_err(rd.cam0_pose._vio_R__, ro.cam0_pose._vio_R__) < 1e-9
+                assert rel_err(rd.velocity, ro.velocity) < 1e-8 or np.linalg.norm(ro.velocity) < 1e-6
+        counts['not_spd'] = int(df.ctx.counters()[:, capi.CNT_GATE_NOT_SPD].sum())
+    finally:
+        df.close()
+    assert counts['not_spd'] == 0, counts
+    return worst, counts

@@ -115,6 +115,8 @@ SIGNATURES = {
     'msckf_version': [],
     'msckf_undistort_points': [_I, _I, _P, _P, _I, _P, _P, _P, _P],
     'msckf_undistort_stereo': [_I, _I, _P, _P, _P, _I, _P, _P, _I, _P, _P],
+    'msckf_synth_frame': [_I, _I, C.c_uint64, _L, _I, _L, _P, _P, _P, _P, _P, C.c_double, C.c_double, _I, _P, _P, C.c_double,
+                          C.c_double, C.c_double, _L, _P, _P, _P, _P, _P, _P, _P, _P],
     'msckf_host_alloc': [C.c_size_t, _P],
     'msckf_host_free': [_P],
 }
@@ -520,6 +522,19 @@ def fp64_peak(device=0):
     if rc != 0:
         raise MsckfCudaError(rc, 'msckf_fp64_peak failed')
     return a.value, b.value
+
+
+def synth_frame(device, n_filters, seed0, frame, sample0, ts, gyro_clean, acc_clean, gyro_bias, acc_bias, sigma_gyro, sigma_acc,
+                ids, uv_clean, sigma_z, outlier_frac, outlier_sigma, cam_id, out_ptrs):
+    """msckf_synth_frame: ``out_ptrs`` = device addresses (ints) of imu_off, ts, gyro, acc, cam_ids, feat_off, ids, uv."""
+    ts, gyro_clean, acc_clean = _f64(ts), _f64(gyro_clean), _f64(acc_clean)
+    gyro_bias, acc_bias, ids, uv_clean = _f64(gyro_bias), _f64(acc_bias), _i64(ids), _f64(uv_clean)
+    rc = load_library().msckf_synth_frame(int(device), int(n_filters), int(seed0), int(frame), len(ts), int(sample0), _ptr(ts),
+                                          _ptr(gyro_clean), _ptr(acc_clean), _ptr(gyro_bias), _ptr(acc_bias), float(sigma_gyro),
+                                          float(sigma_acc), len(ids), _ptr(ids), _ptr(uv_clean), float(sigma_z), float(outlier_frac),
+                                          float(outlier_sigma), int(cam_id), *[int(p) for p in out_ptrs])
+    if rc != 0:
+        raise MsckfCudaError(rc, 'msckf_synth_frame failed')
 
 
 def version():

@@ -146,11 +146,13 @@ __global__ void k_zero_krows_except(Dev d, int keep) {
   }
 }
 
-// wide / tall / uncompressed stacks of a stage (work list wl_qrb).  The pruning stage only ever has n_a = 12: nothing wide.
+// wide / tall / uncompressed stacks of a stage (work list wl_qrb).  The pruning stage only ever has n_a = 12: nothing wide,
+// but when the batch leaves SMs idle (qr_leaf_cap > 1) k_plan_stack sends its tall stacks (m >= 2048: thousands of live
+// landmarks per filter) to the grid-wide TSQR as well.
 void launch_qr_build(const Dev& d, int stage, cudaStream_t st) {
   const int sms = sm_count();
   KLAUNCH(d, KID_QR, st, (k_qr_build<<<std::min(d.F, 2 * sms), QT, 0, st>>>(d)));
-  if (stage != 1) launch_qr_wide(d, st);
+  if (stage != 1 || d.qr_leaf_cap > 1) launch_qr_wide(d, st);
 }
 void launch_compress_update(const Dev& d, int stage, cudaStream_t st) {
   bool all_ok = true;

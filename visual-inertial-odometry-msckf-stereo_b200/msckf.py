@@ -174,6 +174,7 @@ class MSCKF(object):
         self.tracking_rate = None
         self.is_gravity_set = False
         self.is_first_img = True
+        self.did_reset = False
         self.ctx.set_imu_state(0, initial_imu_block(config))
 
     # ------------------------------------------------------------------ snapshots
@@ -260,6 +261,7 @@ class MSCKF(object):
         ids, uv = unpack_features(feature_msg)
         imu, did_reset = self.ctx.feature_callback([0, len(ts)], ts, gy, ac, [self._imu_id], [0, len(ids)], ids, uv)
         self.tracking_rate = float(imu[0, IMU_TRACKING_RATE])
+        self.did_reset = bool(did_reset[0])          # online_reset fired at the end of this frame (msckf.py:859-886)
         return self._publish_from_block(feature_msg.timestamp, imu[0])
 
     # ------------------------------------------------------------------ stage-by-stage API (same names as the reference)

@@ -16,6 +16,7 @@ from collections import namedtuple
 import numpy as np
 
 from .config import ConfigEuRoC
+from .utils import to_rotation
 
 ImuMsg = namedtuple('imu_msg', ['vio_timestamp__', 'angular_velocity', 'linear_acceleration'])
 FeatureMsg = namedtuple('vio_feature_msg__', ['timestamp', 'vio_features'])
@@ -34,18 +35,18 @@ T_START = 1.5          # static lead-in (>= 200 IMU messages for gravity/bias in
 GRAVITY = 9.81
 
 
-def _phase(t):
+def _phase(t, speed=1.0):
     tau = np.maximum(np.asarray(t, dtype=np.float64) - T_START, 0.0)
-    return 0.4 * (tau - np.tanh(tau))
+    return speed * 0.4 * (tau - np.tanh(tau))
 
 
-def truth_position(t):
-    ph = _phase(t)
+def truth_position(t, speed=1.0):
+    ph = _phase(t, speed)
     return np.stack([2.0 * np.cos(ph) - 2.0, 2.0 * np.sin(ph), 0.3 * np.sin(0.7 * ph)], axis=-1)
 
 
-def truth_yaw(t):
-    return 0.5 * _phase(t)
+def truth_yaw(t, speed=1.0):
+    return 0.5 * _phase(t, speed)
 
 
 def _rot_z(a):
@@ -61,7 +62,10 @@ class Structure(object):
 
 
 def make_structure(n_frames=200, feats_per_frame=300, structure_seed=0, mean_track_len=8.0,
-                   n_landmarks=40000, config=None):
+                   n_landmarks=40000, config=None, speed=1.0):
+    """``speed`` scales the trajectory's phase rate (1.0: about 0.8 m/s).  Above ~8 the camera moves more than the
+    reference's key-frame distance (0.4 m, msckf.py:717) between consecutive frames, so pruning removes the OLDEST
+    camera states instead of the ones next to the key frame and lost landmarks carry long tracks."""
     cfg = config or ConfigEuRoC()
     rng = np.random.default_rng(structure_seed)
     st = Structure()
@@ -70,9 +74,9 @@ def make_structure(n_frames=200, feats_per_frame=300, structure_seed=0, mean_tra
     n_imu = int(round(t_end / IMU_DT)) + 1
     ts = np.arange(n_imu) * IMU_DT
     h = 1e-4
-    acc_w = (truth_position(ts + h) - 2 * truth_position(ts) + truth_position(ts - h)) / (h * h)
-    yaw_rate = (truth_yaw(ts + h) - truth_yaw(ts - h)) / (2 * h)
-    R_wi = _rot_z(truth_yaw(ts))                       # IMU -> world
+    acc_w = (truth_position(ts + h, speed) - 2 * truth_position(ts, speed) + truth_position(ts - h, speed)) / (h * h)
+    yaw_rate = (truth_yaw(ts + h, speed) - truth_yaw(ts - h, speed)) / (2 * h)
+    R_wi = _rot_z(truth_yaw(ts, speed))                # IMU -> world
     g_w = np.array([0.0, 0.0, -GRAVITY])
     st.imu_ts = ts
     st.gyro_clean = np.stack([np.zeros(n_imu), np.zeros(n_imu), yaw_rate], axis=-1)
@@ -89,17 +93,19 @@ def make_structure(n_frames=200, feats_per_frame=300, structure_seed=0, mean_tra
     st.landmarks = lm
     st.frame_ts = T_START + FRAME_DT * (np.arange(n_frames) + 1)
     st.frame_ids, st.frame_lm, st.frame_uv = [], [], []
-    st.truth_p = truth_position(st.frame_ts)
-    st.truth_yaw = truth_yaw(st.frame_ts)
+    st.truth_p = truth_position(st.frame_ts, speed)
+    st.truth_yaw = truth_yaw(st.frame_ts, speed)
 
     tracked_lm = np.zeros(0, dtype=np.int64)
     tracked_id = np.zeros(0, dtype=np.int64)
     next_id = 0
     survive = 1.0 - 1.0 / mean_track_len
+    # a scalar, or one target per frame (e.g. a cheap lead-in that fills the camera window before the full-size frames)
+    target = np.broadcast_to(np.asarray(feats_per_frame, dtype=np.int64), (n_frames,))
     for f in range(n_frames):
         t = st.frame_ts[f]
-        R = _rot_z(truth_yaw(t))
-        p_i = (lm - truth_position(t)) @ R             # R^T (X - p)
+        R = _rot_z(truth_yaw(t, speed))
+        p_i = (lm - truth_position(t, speed)) @ R             # R^T (X - p)
         p_c0 = p_i @ R_ci.T + t_ci
         p_c1 = p_c0 @ R_01.T + t_01
         uv = np.concatenate([p_c0[:, :2] / p_c0[:, 2:3], p_c1[:, :2] / p_c1[:, 2:3]], axis=1)
@@ -108,7 +114,7 @@ def make_structure(n_frames=200, feats_per_frame=300, structure_seed=0, mean_tra
                & (np.abs(uv[:, 2]) < 0.75) & (np.abs(uv[:, 3]) < 0.5))
         keep = vis[tracked_lm] & (rng.random(len(tracked_lm)) < survive)
         tracked_lm, tracked_id = tracked_lm[keep], tracked_id[keep]
-        need = feats_per_frame - len(tracked_lm)
+        need = int(target[f]) - len(tracked_lm)
         if need > 0:
             cand = vis.copy()
             cand[tracked_lm] = False
@@ -187,3 +193,42 @@ def drive(filt, stream, n_frames=None, on_frame=None):
         if on_frame is not None:
             on_frame(f, filt, res)
     return out
+
+
+def stress_tracks(cam_q, cam_p, R01, t01, n_landmarks, rng, sigma_z=0.001, outlier_frac=0.05, outlier_sigma=0.05):
+    """BASELINE.json configs[2] (feature-update stress frame): ``n_landmarks`` synthetic tracks over the camera states
+    (cam_q [N][4] JPL world->cam0, cam_p [N][3]) except the newest one, so that every landmark is "lost" in the current
+    frame.  World points lie in front of the middle camera and are projected into cam0 / cam1 of every observing state
+    (msckf.py:443-457) plus pixel noise and gross outliers.  Track lengths M ~ U{3 .. N-1}; nine in ten tracks are
+    contiguous in time (as real tracks are), the rest observe a random subset of the window.
+    Returns (ids int64[n], masks uint64[n] with bit j = j-th camera state, obs [n][N][4])."""
+    cam_q, cam_p = np.asarray(cam_q, dtype=np.float64), np.asarray(cam_p, dtype=np.float64)
+    N = len(cam_q)
+    Rs = [to_rotation(q) for q in cam_q]
+    mid = (N - 1) // 2
+    depth = rng.uniform(3.0, 8.0, n_landmarks)
+    pc = np.stack([rng.uniform(-0.4, 0.4, n_landmarks) * depth, rng.uniform(-0.3, 0.3, n_landmarks) * depth, depth], axis=1)
+    pw = pc @ Rs[mid] + cam_p[mid]                         # R^T p_c + t
+    ids = 10 ** 6 + np.arange(n_landmarks, dtype=np.int64)
+    masks = np.zeros(n_landmarks, dtype=np.uint64)
+    obs = np.zeros((n_landmarks, N, 4))
+    Ms = rng.integers(3, N, n_landmarks)                   # 3 .. N-1
+    for j in range(n_landmarks):
+        M = int(Ms[j])
+        if rng.random() < 0.9:
+            s = int(rng.integers(0, N - 1 - M + 1))
+            sel = np.arange(s, s + M)
+        else:
+            sel = np.sort(rng.choice(N - 1, size=M, replace=False))
+        m = 0
+        for c in sel:
+            p0 = Rs[c] @ (pw[j] - cam_p[c])
+            p1 = R01 @ p0 + t01
+            z = np.array([p0[0] / p0[2], p0[1] / p0[2], p1[0] / p1[2], p1[1] / p1[2]])
+            z += sigma_z * rng.standard_normal(4)
+            if rng.random() < outlier_frac:
+                z += outlier_sigma * rng.standard_normal(4)
+            obs[j, c] = z
+            m |= 1 << int(c)
+        masks[j] = m
+    return ids, masks, obs

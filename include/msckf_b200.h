@@ -88,6 +88,8 @@ enum {
   MSCKF_CNT_K4_FLOPS = 11, MSCKF_CNT_K4_BYTES = 12, /* gain + correction + covariance               */
   MSCKF_CNT_IMU_STEPS = 13,      /* IMU samples integrated                                           */
   MSCKF_CNT_GATE_NOT_SPD = 14,   /* landmarks rejected because rounding made their innovation covariance indefinite */
+  MSCKF_CNT_K4_EXEC_FLOPS = 15,  /* flops the update kernels actually execute: triangular H_thin, active columns only,
+                                    upper triangles of S and of the downdate (the K4 contract counts dense GEMMs)    */
   MSCKF_N_COUNTERS = 16
 };
 

@@ -378,3 +378,56 @@ def test_undistort_points_vs_golden_and_oracle():
     msg = gimg.publish(1.5, np.arange(5), p0[:5], p1[:5], cfg)
     assert msg.timestamp == 1.5 and [f.id for f in msg.vio_features] == [0, 1, 2, 3, 4]
     assert np.allclose([[f.u0, f.v0, f.u1, f.v1] for f in msg.vio_features], uv[:5], rtol=0, atol=0)
+
+
+def test_synth_frame_generator():
+    """msckf_synth_frame: layout of msckf_feature_callback_dev, noise that is a pure function of
+    (seed, sample / frame, element) -- filter f of seed0 equals filter 0 of seed0 + f, a frame regenerated alone is
+    identical -- and the noise model of SURVEY 8d (sigmas, outlier fraction)."""
+    import torch
+    from msckf_b200 import capi
+    F, K, n = 6, 10, 4000
+    rng = np.random.default_rng(0)
+    ts = 1.5 + 0.005 * np.arange(K)
+    gyro_c, acc_c = rng.standard_normal((K, 3)) * 0.1, rng.standard_normal((K, 3))
+    gb, ab = np.array([0.002, -0.001, 0.0015]), np.array([0.02, -0.01, 0.015])
+    ids = np.arange(1000, 1000 + n, dtype=np.int64)
+    uv_c = rng.uniform(-0.5, 0.5, (n, 4))
+    sg, sa, sz, of, so = 0.07, 0.7, 0.001, 0.05, 0.05
+    dev = torch.device('cuda', 0)
+
+    def gen(nf, seed0, frame, sample0):
+        t = {'imu_off': torch.empty(nf + 1, dtype=torch.int32, device=dev), 'ts': torch.empty(nf * K, dtype=torch.float64, device=dev),
+             'gyro': torch.empty((nf, K, 3), dtype=torch.float64, device=dev), 'acc': torch.empty((nf, K, 3), dtype=torch.float64, device=dev),
+             'cam_ids': torch.empty(nf, dtype=torch.int64, device=dev), 'feat_off': torch.empty(nf + 1, dtype=torch.int32, device=dev),
+             'ids': torch.empty(nf * n, dtype=torch.int64, device=dev), 'uv': torch.empty((nf, n, 4), dtype=torch.float64, device=dev)}
+        keys = ['imu_off', 'ts', 'gyro', 'acc', 'cam_ids', 'feat_off', 'ids', 'uv']
+        capi.synth_frame(0, nf, seed0, frame, sample0, ts, gyro_c, acc_c, gb, ab, sg, sa, ids, uv_c, sz, of, so, 77, [t[k].data_ptr() for k in keys])
+        return dict((k, v.cpu().numpy()) for k, v in t.items())
+
+    a = gen(F, 10, 5, 300)
+    b = gen(F, 10, 5, 300)
+    for k in a:
+        assert np.array_equal(a[k], b[k]), k
+    assert np.array_equal(a['imu_off'], np.arange(F + 1) * K) and np.array_equal(a['feat_off'], np.arange(F + 1) * n)
+    assert np.array_equal(a['cam_ids'], np.full(F, 77)) and np.array_equal(a['ids'], np.tile(ids, F))
+    assert np.array_equal(a['ts'], np.tile(ts, F))
+    one = gen(1, 13, 5, 300)                             # filter 3 of the batch, alone
+    assert np.array_equal(one['uv'][0], a['uv'][3]) and np.array_equal(one['gyro'][0], a['gyro'][3])
+    other = gen(F, 10, 6, 310)                           # another frame: new pixel noise, new IMU samples
+    assert not np.array_equal(other['uv'], a['uv']) and not np.array_equal(other['gyro'], a['gyro'])
+    shifted = gen(F, 10, 5, 295)                         # IMU noise is keyed by the global sample index
+    assert np.allclose(shifted['gyro'][:, 5:] - gyro_c[5:], a['gyro'][:, :5] - gyro_c[:5], rtol=0, atol=1e-14)
+    # noise model
+    dg = (a['gyro'] - gyro_c - gb).ravel()
+    da = (a['acc'] - acc_c - ab).ravel()
+    assert abs(dg.std() / sg - 1) < 0.25 and abs(da.std() / sa - 1) < 0.25 and abs(dg.mean()) < 4 * sg / np.sqrt(dg.size)
+    duv = a['uv'] - uv_c
+    big = np.abs(duv).max(axis=2) > 6 * sz
+    assert 0.03 < big.mean() < 0.07                      # gross outliers (sigma 0.05) on ~5 % of the observations
+    inl = duv[~big].ravel()
+    assert abs(inl.std() / sz - 1) < 0.03 and abs(inl.mean()) < 5 * sz / np.sqrt(inl.size)
+    assert abs(duv[big].ravel().std() / so - 1) < 0.15
+    for f1 in range(F):                                  # independent streams per seed
+        for f2 in range(f1):
+            assert abs(np.corrcoef(duv[f1].ravel(), duv[f2].ravel())[0, 1]) < 0.05

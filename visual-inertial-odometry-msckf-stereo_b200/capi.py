@@ -22,7 +22,7 @@ IMU_NULL_ALIASED, IMU_TRACKING_RATE, IMU_STRIDE = 42, 43, 48
 CAM_STRIDE = 16
 N_COUNTERS = 16
 (CNT_FEATURE_UPDATES, CNT_TRIANGULATIONS, CNT_UPDATES, CNT_FRAMES, CNT_TRI_OBS, CNT_TRI_SOLVES, CNT_JAC_OBS, CNT_K2_FLOPS,
- CNT_K2_BYTES, CNT_QR_FLOPS, CNT_QR_BYTES, CNT_K4_FLOPS, CNT_K4_BYTES, CNT_IMU_STEPS, CNT_GATE_NOT_SPD) = range(15)
+ CNT_K2_BYTES, CNT_QR_FLOPS, CNT_QR_BYTES, CNT_K4_FLOPS, CNT_K4_BYTES, CNT_IMU_STEPS, CNT_GATE_NOT_SPD, CNT_K4_EXEC_FLOPS) = range(16)
 FEAT_FEW_OBS, FEAT_TRI_FAILED, FEAT_GATE_PASS, FEAT_GATE_FAIL, FEAT_AFTER_CAP = 1, 2, 3, 4, 5
 
 ERR_ARG, ERR_CUDA, ERR_CAPACITY, ERR_NUMERIC = -1, -2, -3, -4

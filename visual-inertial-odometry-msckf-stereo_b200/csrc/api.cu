@@ -293,11 +293,10 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   d.pool_cap = pool;
   {
     const long long M = d.Nmax;
-    const long long fixed = 88 * M + 16 + (4 * M - 3) + (M + 1) / 2 + 1;      // jac_fixed_doubles(Nmax), see k_jacobian.cu
-    d.jac_big_smem_doubles = (int)std::max<long long>(6144, fixed + 8);
-    const int per_sm = (int)std::max<long long>(1, std::min<long long>(8, (200 * 1024) / ((long long)d.jac_big_smem_doubles * 8 + 1024)));
-    d.jac_big_grid = prop.multiProcessorCount * per_sm;
-    d.jac_scratch_stride = 4 * M * (6 * M + 1) + (4 * M - 3) * (4 * M - 3);
+    d.jac_big_smem_doubles = 0;                             // (sized by the launcher, k_jacobian.cu)
+    d.jac_big_grid = prop.multiProcessorCount * 2;
+    const long long Rp = (4 * M - 3 + 7) & ~7LL;
+    d.jac_scratch_stride = Rp * (Rp + 4);                    // jb_S_doubles(Nmax): the innovation covariance of the longest track
     {   // stacked rows: the capped lost-landmark update, or the pruning update (5 rows per live landmark); everything when the cap is lifted
       const long long all = (long long)d.Fcap * (4 * M - 3);
       const long long capped = std::max<long long>(d.max_rows, 5LL * d.Fcap + 8);
@@ -358,7 +357,7 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   DA(d.item_dof, F * Fc); DA(d.item_gamma, F * Fc); DA(d.item_pass, F * Fc); DA(d.nitem, F);
   DA(d.rm_mask, F); DA(d.rm_idx, F * 2);
   DA(d.pool, (size_t)d.pool_cap); DA(d.stage_ctr, SC_COUNT); DA(d.item_lmask, F * Fc);
-  DA(d.wl_tri, F * Fc); DA(d.wl_jac_small, JAC_CLASSES * F * Fc); DA(d.wl_jac_big, F * Fc);
+  DA(d.wl_tri, F * Fc); DA(d.wl_jac_small, JAC_CLASSES * F * Fc); DA(d.wl_jac_big, F * Fc); DA(d.wl_jac_big2, F * Fc);
   DA(d.jac_scratch, (size_t)d.jac_big_grid * d.jac_scratch_stride);
   DA(d.Rnode, F * (size_t)d.qr_leaf_cap * (size_t)d.Rnode_stride);
   DA(d.Adense, (size_t)d.Adense_elems);
@@ -1138,10 +1137,11 @@ int msckf_feature_jacobian(msckf_ctx* ctx, int32_t f, int64_t feature_id, int32_
   CK(cudaMemcpyAsync(d.nitem + f, &one, sizeof(int), cudaMemcpyHostToDevice, ctx->st));
   {                                          // a one-entry work list for the matching Jacobian kernel
     unsigned long long ctr[SC_COUNT] = {0};
-    ctr[M <= JAC_SMALL_M ? SC_NJAC_SMALL + jac_class(M) : SC_NJAC_BIG] = 1;
+    ctr[M <= JAC_SMALL_M ? SC_NJAC_SMALL + jac_class(M) : (M <= JAC_BIG_SPLIT_M ? SC_NJAC_BIG : SC_NJAC_BIG2)] = 1;
     const int2 entry = make_int2(f, 0);
     CK(cudaMemcpyAsync(d.stage_ctr, ctr, sizeof ctr, cudaMemcpyHostToDevice, ctx->st));
-    CK(cudaMemcpyAsync(M <= JAC_SMALL_M ? d.wl_jac_small + (size_t)jac_class(M) * d.F * d.Fcap : d.wl_jac_big, &entry, sizeof entry, cudaMemcpyHostToDevice, ctx->st));
+    CK(cudaMemcpyAsync(M <= JAC_SMALL_M ? d.wl_jac_small + (size_t)jac_class(M) * d.F * d.Fcap : (M <= JAC_BIG_SPLIT_M ? d.wl_jac_big : d.wl_jac_big2), &entry,
+                       sizeof entry, cudaMemcpyHostToDevice, ctx->st));
     CK(cudaStreamSynchronize(ctx->st));      // the small host sources above live on this stack frame
   }
   launch_cam_prepare(d, ctx->st);

@@ -19,11 +19,13 @@
 #include <algorithm>
 #include "msckf_dev.cuh"
 #include "kernels.h"
+#include "dmma_tiles.cuh"
 
 namespace msckf {
 
 constexpr int JAC_WARPS = 4;          // warps per CTA of the small-M kernel
-constexpr int JAC_BIG_T = 128;        // threads per CTA of the long-track kernel
+constexpr int JB_T = 256;             // threads per CTA of the long-track kernel
+constexpr int JB_YLD = 12;            // leading dimension of the residual tile that rides along the Cholesky factorisation
 
 // Per-stage derived quantities of every camera state, shared by all landmarks it observes (msckf.py:436-447,
 // 483-485): R0 = R(q) world -> cam0, R1 = R_01 R0, t0, t1 = t0 - R1^T t_01, R(q_null) g, p_null.
@@ -173,10 +175,11 @@ __device__ __forceinline__ double gsum(double v, unsigned m) {
 }
 #define gsync gsync_m
 
-// One landmark through Jacobian, projection and gate by a group of NT threads.
+// Steps 1-4 of a landmark by a group of NT threads: per-observation blocks (msckf.py:429-498), the three Householder
+// reflectors on H_f with T and Q^T r, Z = T^T V^T E and Pcc Z^T.
 template <int NT>
-__device__ void jac_core(const Dev& d, int f, int k, int M, unsigned long long lmask, const JacBuf& B, int tid, int write_all,
-                         unsigned gmask_in) {
+__device__ __forceinline__ void jac_front(const Dev& d, int f, int k, int M, unsigned long long lmask, const JacBuf& B, int tid,
+                                          unsigned gmask_in) {
   constexpr int LW = NT < 32 ? NT : 32;
   const unsigned gmask = NT <= 32 ? gmask_in : 0xffffffffu;
   const int lane = tid;                 // index inside the leader part (only used when tid < LW)
@@ -186,7 +189,7 @@ __device__ void jac_core(const Dev& d, int f, int k, int M, unsigned long long l
   const int N = d.ncam[f];
   const Params& prm = *d.prm;
   const double* g = d.imu + (size_t)f * IMU_STRIDE + MSCKF_IMU_GRAVITY;
-  const int R4 = 4 * M, C6 = 6 * M, R = R4 - 3, ldT = C6 + 1;
+  const int R4 = 4 * M, C6 = 6 * M;
   const int* phys = d.cam_phys + (size_t)f * d.Nmax;
 
   for (int c = tid; c < N; c += NT)
@@ -300,6 +303,59 @@ __device__ void jac_core(const Dev& d, int f, int k, int M, unsigned long long l
     B.PZt[3 * c] = s0; B.PZt[3 * c + 1] = s1; B.PZt[3 * c + 2] = s2;
   }
   gsync<NT>(gmask);
+}
+
+// Gate result and the record for the stacking / QR kernel: projected rows (Q^T E - rows 3..) and residual, row-major
+// [R][6M+1].  `gamma` is valid on thread 0.
+template <int NT>
+__device__ __forceinline__ void jac_finish(const Dev& d, int f, int k, int M, unsigned long long lmask, const JacBuf& B, int tid,
+                                           int write_all, unsigned gmask, double gamma, bool spd) {
+  const size_t ik = (size_t)f * d.Fcap + k;
+  const int C6 = 6 * M, R = 4 * M - 3;
+  if (tid == 0) {
+    // S is positive definite in exact arithmetic; a landmark whose position is wildly off (a gross outlier) can make
+    // H P H^T so large that rounding produces a non-positive pivot.  The reference's LU returns noise there; the
+    // landmark is rejected (gamma = inf) and counted, it is not an error of the filter.
+    if (!spd) atomicAdd((unsigned long long*)(d.counters + (size_t)NCNT * f + MSCKF_CNT_GATE_NOT_SPD), 1ull);
+    const int pass = (gamma < d.prm->chi2[d.item_dof[ik]]) ? 1 : 0;
+    d.item_gamma[ik] = gamma;
+    d.item_pass[ik] = pass;
+    d.item_lmask[ik] = lmask;
+    B.Tm[8] = (double)pass;
+  }
+  gsync<NT>(gmask);
+  const int pass = (int)B.Tm[8];
+  if ((pass || write_all) && d.item_off[ik] + jac_record_doubles(M) <= d.pool_cap) {     // (pool overflow is reported by k_plan_items)
+    double* out = d.pool + d.item_off[ik];
+    const int ldr = C6 + 1;
+    for (int e = tid; e < R * ldr; e += NT) {
+      const int ii = e / ldr, c = e - ii * ldr, i = ii + 3;
+      double v;
+      if (c == C6) {
+        v = B.r[i];
+      } else {
+        const int a = c / 6;
+        v = (i >= 4 * a && i < 4 * a + 4) ? B.Hx[24 * a + 6 * (i - 4 * a) + (c - 6 * a)] : 0.0;
+        v -= B.V[3 * i] * B.Zt[3 * c] + B.V[3 * i + 1] * B.Zt[3 * c + 1] + B.V[3 * i + 2] * B.Zt[3 * c + 2];
+      }
+      out[e] = v;
+    }
+  }
+  gsync<NT>(gmask);
+}
+
+// One landmark through Jacobian, projection and gate by a group of NT <= 32 lanes (short tracks, everything in shared memory).
+template <int NT>
+__device__ void jac_core(const Dev& d, int f, int k, int M, unsigned long long lmask, const JacBuf& B, int tid, int write_all,
+                         unsigned gmask_in) {
+  constexpr int LW = NT < 32 ? NT : 32;
+  const unsigned gmask = NT <= 32 ? gmask_in : 0xffffffffu;
+  const int lane = tid;
+  const Params& prm = *d.prm;
+  const int R4 = 4 * M, C6 = 6 * M, R = R4 - 3, ldT = C6 + 1;
+  jac_front<NT>(d, f, k, M, lmask, B, tid, gmask_in);
+  const double* P = d.P + (size_t)f * d.ld * d.ld;
+  const int ld = d.ld;
   // ---- step 5: T1 = E Pcc - V PZt^T   (one (block a, column c) 4-vector per thread; P is exactly symmetric)
   for (int e2 = tid; e2 < M * C6; e2 += NT) {
     const int a = e2 / C6, c = e2 - a * C6;
@@ -376,38 +432,7 @@ __device__ void jac_core(const Dev& d, int f, int k, int M, unsigned long long l
     gamma = gsum<LW>(gamma, gmask);
   }
   if (!spd) gamma = INFINITY;
-  int pass = 0;
-  if (tid == 0) {
-    // S is positive definite in exact arithmetic; a landmark whose position is wildly off (a gross outlier) can make
-    // H P H^T so large that rounding produces a non-positive pivot.  The reference's LU returns noise there; the
-    // landmark is rejected (gamma = inf) and counted, it is not an error of the filter.
-    if (!spd) atomicAdd((unsigned long long*)(d.counters + (size_t)NCNT * f + MSCKF_CNT_GATE_NOT_SPD), 1ull);
-    pass = (gamma < prm.chi2[d.item_dof[ik]]) ? 1 : 0;
-    d.item_gamma[ik] = gamma;
-    d.item_pass[ik] = pass;
-    d.item_lmask[ik] = lmask;
-    B.Tm[8] = (double)pass;
-  }
-  gsync<NT>(gmask);
-  pass = (int)B.Tm[8];
-  // ---- record for the stacking / QR kernel: projected rows (Q^T E - rows 3..) and residual, row-major [R][6M+1]
-  if ((pass || write_all) && d.item_off[ik] + jac_record_doubles(M) <= d.pool_cap) {     // (pool overflow is reported by k_plan_items)
-    double* out = d.pool + d.item_off[ik];
-    const int ldr = C6 + 1;
-    for (int e = tid; e < R * ldr; e += NT) {
-      const int ii = e / ldr, c = e - ii * ldr, i = ii + 3;
-      double v;
-      if (c == C6) {
-        v = B.r[i];
-      } else {
-        const int a = c / 6;
-        v = (i >= 4 * a && i < 4 * a + 4) ? B.Hx[24 * a + 6 * (i - 4 * a) + (c - 6 * a)] : 0.0;
-        v -= B.V[3 * i] * B.Zt[3 * c] + B.V[3 * i + 1] * B.Zt[3 * c + 1] + B.V[3 * i + 2] * B.Zt[3 * c + 2];
-      }
-      out[e] = v;
-    }
-  }
-  gsync<NT>(gmask);
+  jac_finish<NT>(d, f, k, M, lmask, B, tid, write_all, gmask, gamma, spd);
 }
 
 // logical-order observation mask of a landmark, computed by a group of G lanes (gmask, first lane gbase)
@@ -448,20 +473,227 @@ __global__ void __launch_bounds__(JAC_WARPS * 32, 8) k_jacobian_gate_small(Dev d
   }
 }
 
-// Long tracks: one CTA per landmark; T1 and S live in shared memory when they fit, else in global scratch.
-__global__ void __launch_bounds__(JAC_BIG_T) k_jacobian_gate_big(Dev d, int smem_doubles, int write_all) {
-  extern __shared__ double smem[];
-  const int lane = threadIdx.x & 31;
-  const int n = (int)d.stage_ctr[SC_NJAC_BIG];
+// ------------------------------------------------------------------ long tracks (M > JAC_SMALL_M): one CTA per landmark
+// The same algebra as jac_core, organised for tracks of up to 64 observations (R = 4M - 3 up to 253 gate rows):
+//   * T1 = (E - V Z) Pcc is never stored: a group of lanes owns a row block a (the 4 rows of one observation), each lane a
+//     column block b; the lane forms the 4 x 6 block T1_ab = Hx_a Pcc[a,b] - V_a (Pcc Z^T)_b^T in registers, adds its share
+//     of (T1 Z^T)_a (reduced over the group by shuffles) and, for b <= a, the 4 x 4 block S_ab = T1_ab Hx_b^T - (T1 Z^T)_a V_b^T;
+//   * S = L L^T by a right-looking blocked Cholesky on the FP64 tensor pipe (8-row panels: the diagonal block is factored and
+//     inverted by one warp, panel solves and trailing updates are DMMA tiles), the projected residual riding along as one
+//     more column tile, gamma = |L^-1 r'|^2;
+//   * S lives in shared memory when it fits (tracks of up to ~38 observations), else in a per-CTA global scratch (L2).
+// Two launches share the code: tracks of up to JAC_BIG_SPLIT_M observations (small S, several CTAs per SM) and longer ones.
+__host__ __device__ inline int jb_rp(int M) { return (4 * M - 3 + 7) & ~7; }                       // gate rows padded to 8
+__host__ __device__ inline int jb_lds(int M) { return jb_rp(M) + 4; }                               // 4 (mod 8): conflict-free fragments
+__host__ __device__ inline long long jb_S_doubles(int M) { return (long long)jb_rp(M) * jb_lds(M); }
+__host__ __device__ inline int jb_fixed_doubles(int M) {                                           // everything but S
+  return ((jac_fixed_doubles(M) + 1) & ~1) + jb_rp(M) * JB_YLD + 8 * LDL;
+}
+
+template <int GS, int MAXR>
+__device__ __forceinline__ void jb_build_S(const double* __restrict__ P, int ld, int M, const JacBuf& B, double* S, int ldS,
+                                           double sigma2, int tid) {
+  constexpr int NG = JB_T / GS;
+  const int grp = tid / GS, gl = tid - grp * GS;
+  const unsigned gmask = GS == 32 ? 0xffffffffu : (0xffffu << (16 * ((tid >> 4) & 1)));
+  for (int a = grp; a < M; a += NG) {
+    double hxa[24], va[12], tz[12], s16[MAXR][16];
+#pragma unroll
+    for (int e = 0; e < 24; ++e) hxa[e] = B.Hx[24 * a + e];
+#pragma unroll
+    for (int e = 0; e < 12; ++e) { va[e] = B.V[12 * a + e]; tz[e] = 0.0; }
+    const double* prow = P + (size_t)(NI + 6 * B.cl[a]) * ld + NI;
+#pragma unroll
+    for (int rr = 0; rr < MAXR; ++rr) {
+      const int b = rr * GS + gl;
+      if (b < M) {
+        const double* pp = prow + 6 * B.cl[b];
+        double t1[24];
+#pragma unroll
+        for (int e = 0; e < 24; ++e) t1[e] = 0.0;
+#pragma unroll
+        for (int e = 0; e < 6; ++e) {
+          double p6[6];
+#pragma unroll
+          for (int c = 0; c < 6; ++c) p6[c] = pp[(size_t)e * ld + c];
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int c = 0; c < 6; ++c) t1[6 * i + c] += hxa[6 * i + e] * p6[c];
+        }
+        const double* pz = B.PZt + 18 * b;
+        const double* zt = B.Zt + 18 * b;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+          const double q0 = pz[3 * c], q1 = pz[3 * c + 1], q2 = pz[3 * c + 2];
+          const double z0 = zt[3 * c], z1 = zt[3 * c + 1], z2 = zt[3 * c + 2];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const double t = t1[6 * i + c] - (va[3 * i] * q0 + va[3 * i + 1] * q1 + va[3 * i + 2] * q2);
+            t1[6 * i + c] = t;
+            tz[3 * i] += t * z0; tz[3 * i + 1] += t * z1; tz[3 * i + 2] += t * z2;
+          }
+        }
+        if (b <= a) {
+          const double* hxb = B.Hx + 24 * b;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            double h6[6];
+#pragma unroll
+            for (int c = 0; c < 6; ++c) h6[c] = hxb[6 * j + c];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              double acc = 0.0;
+#pragma unroll
+              for (int c = 0; c < 6; ++c) acc += t1[6 * i + c] * h6[c];
+              s16[rr][4 * i + j] = acc;
+            }
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int o = GS / 2; o > 0; o >>= 1) {
+#pragma unroll
+      for (int e = 0; e < 12; ++e) tz[e] += __shfl_xor_sync(gmask, tz[e], o);
+    }
+#pragma unroll
+    for (int rr = 0; rr < MAXR; ++rr) {
+      const int b = rr * GS + gl;
+      if (b < M && b <= a) {
+        const double* vb = B.V + 12 * b;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const double v0 = vb[3 * j], v1 = vb[3 * j + 1], v2 = vb[3 * j + 2];
+          const int col = 4 * b + j - 3;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int row = 4 * a + i - 3;
+            if (row >= 0 && col >= 0) {
+              double v = s16[rr][4 * i + j] - (tz[3 * i] * v0 + tz[3 * i + 1] * v1 + tz[3 * i + 2] * v2);
+              if (row == col) v += sigma2;
+              S[(size_t)row * ldS + col] = v;
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
+// S (lower tiles, nkt x nkt tiles of 8) = L L^T in place, Y <- L^-1 Y.  Returns true when a pivot is not positive.
+__device__ __forceinline__ bool jb_cholesky(double* S, int ldS, int nkt, double* sY, double* sLinv, int* s_bad, int tid) {
+  constexpr int NW = JB_T / 32;
+  const int lane = tid & 31, warp = tid >> 5, g = lane >> 2, tg = lane & 3;
+  for (int p = 0; p < nkt; ++p) {
+    const int p0 = 8 * p;
+    if (warp == 0) {
+      if (chol8_inverse(S, ldS, p0, sLinv, lane) && lane == 0) *s_bad = 1;
+    }
+    __syncthreads();
+    if (*s_bad) return true;
+    const double li0 = sLinv[g * LDL + tg], li1 = sLinv[g * LDL + 4 + tg];   // A fragment of L^-1 == B fragment of L^-T
+    const int nbelow = nkt - p - 1;
+    // panel: Y_p = L_pp^-1 Y_p, L_ip = S_ip L_pp^-T (row tiles below)
+    for (int item = warp; item < 1 + nbelow; item += NW) {
+      double c0 = 0.0, c1 = 0.0;
+      if (item == 0) {
+        double* base = sY + p0 * JB_YLD;
+        const double b0 = base[tg * JB_YLD + g], b1 = base[(4 + tg) * JB_YLD + g];
+        dmma884(c0, c1, li0, b0);
+        dmma884(c0, c1, li1, b1);
+        base[g * JB_YLD + 2 * tg] = c0;
+        base[g * JB_YLD + 2 * tg + 1] = c1;
+      } else {
+        double* base = S + (size_t)(8 * (p + item)) * ldS + p0;
+        const double a0 = base[(size_t)g * ldS + tg], a1 = base[(size_t)g * ldS + 4 + tg];
+        dmma884(c0, c1, a0, li0);
+        dmma884(c0, c1, a1, li1);
+        *(double2*)(base + (size_t)g * ldS + 2 * tg) = make_double2(c0, c1);
+      }
+    }
+    __syncthreads();
+    // trailing update: Y_i -= L_ip Y_p ;  S_ij -= L_ip L_jp^T  (p < j <= i)
+    const int nS = nbelow * (nbelow + 1) / 2;
+    for (int item = warp; item < nbelow; item += NW) {
+      const int it = p + 1 + item;
+      const double* lrow = S + (size_t)(8 * it + g) * ldS + p0 + tg;
+      const double a0 = -lrow[0], a1 = -lrow[4];
+      const double* wb = sY + p0 * JB_YLD;
+      const double b0 = wb[tg * JB_YLD + g], b1 = wb[(4 + tg) * JB_YLD + g];
+      double* cp = sY + (8 * it + g) * JB_YLD + 2 * tg;
+      double c0 = cp[0], c1 = cp[1];
+      dmma884(c0, c1, a0, b0);
+      dmma884(c0, c1, a1, b1);
+      cp[0] = c0;
+      cp[1] = c1;
+    }
+    if (warp < nS) {
+      int ib, jb;
+      tri_decode(warp, ib, jb);
+      for (int item = warp; item < nS; item += NW) {
+        const int it = p + 1 + ib, jt = p + 1 + jb;
+        const double* lrow = S + (size_t)(8 * it + g) * ldS + p0 + tg;
+        const double a0 = -lrow[0], a1 = -lrow[4];
+        const double* lcol = S + (size_t)(8 * jt + g) * ldS + p0 + tg;
+        const double b0 = lcol[0], b1 = lcol[4];
+        double2* cp = (double2*)(S + (size_t)(8 * it + g) * ldS + 8 * jt + 2 * tg);
+        double2 c = *cp;
+        dmma884(c.x, c.y, a0, b0);
+        dmma884(c.x, c.y, a1, b1);
+        *cp = c;
+        tri_advance(ib, jb, NW);
+      }
+    }
+    __syncthreads();
+  }
+  return false;
+}
+
+// cls 0: tracks of JAC_SMALL_M < M <= JAC_BIG_SPLIT_M (work list wl_jac_big), cls 1: longer tracks (wl_jac_big2)
+template <int GS, int MAXR, int MINB>
+__global__ void __launch_bounds__(JB_T, MINB) k_jacobian_gate_big(Dev d, int cls, int smem_doubles, int write_all) {
+  extern __shared__ __align__(16) double smem[];
+  __shared__ int s_bad;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int n = (int)d.stage_ctr[cls == 0 ? SC_NJAC_BIG : SC_NJAC_BIG2];
+  const int2* wl = cls == 0 ? d.wl_jac_big : d.wl_jac_big2;
+  const double sigma2 = d.prm->obs_noise;
   for (int w = blockIdx.x; w < n; w += gridDim.x) {
-    const int2 it = d.wl_jac_big[w];
-    const size_t ik = (size_t)it.x * d.Fcap + it.y;
-    const unsigned long long lmask = logical_mask<32>(d, it.x, d.item_mask[ik], lane, 0xffffffffu, 0);
+    const int2 it = wl[w];
+    const int f = it.x, k = it.y;
+    const size_t ik = (size_t)f * d.Fcap + k;
+    const unsigned long long lmask = logical_mask<32>(d, f, d.item_mask[ik], lane, 0xffffffffu, 0);
     const int M = __popcll(lmask);
+    const int R = 4 * M - 3, Rp = jb_rp(M), nkt = Rp >> 3;
     JacBuf B;
-    const bool fits = jac_small_doubles(M) <= smem_doubles;
-    jac_carve(B, smem, M, fits ? nullptr : d.jac_scratch + (size_t)blockIdx.x * d.jac_scratch_stride);
-    jac_core<JAC_BIG_T>(d, it.x, it.y, M, lmask, B, threadIdx.x, write_all, 0xffffffffu);
+    jac_carve(B, smem, M, smem);                       // (T1 / S pointers of the short-track layout are not used here)
+    double* sY = smem + ((jac_fixed_doubles(M) + 1) & ~1);
+    double* sLinv = sY + Rp * JB_YLD;
+    const bool fits = jb_fixed_doubles(M) + jb_S_doubles(M) <= smem_doubles;
+    double* S = fits ? sLinv + 8 * LDL : d.jac_scratch + (size_t)blockIdx.x * d.jac_scratch_stride;
+    const int ldS = jb_lds(M);
+    __syncthreads();                                    // the previous landmark's record has been written
+    if (tid == 0) s_bad = 0;
+    jac_front<JB_T>(d, f, k, M, lmask, B, tid, 0xffffffffu);
+    // S: zero, unit diagonal on the padding rows; Y: the projected residual in column 0
+    for (int e = tid; e < Rp * (ldS / 2); e += JB_T) ((double2*)S)[e] = make_double2(0.0, 0.0);
+    for (int e = tid; e < Rp * JB_YLD; e += JB_T) {
+      const int i = e / JB_YLD, c = e - i * JB_YLD;
+      sY[e] = (c == 0 && i < R) ? B.r[i + 3] : 0.0;
+    }
+    __syncthreads();
+    for (int i = R + tid; i < Rp; i += JB_T) S[(size_t)i * ldS + i] = 1.0;
+    jb_build_S<GS, MAXR>(d.P + (size_t)f * d.ld * d.ld, d.ld, M, B, S, ldS, sigma2, tid);
+    __syncthreads();
+    const bool bad = jb_cholesky(S, ldS, nkt, sY, sLinv, &s_bad, tid);
+    double gamma = 0.0;
+    if (tid < 32) {
+      for (int i = lane; i < R; i += 32) gamma += sY[i * JB_YLD] * sY[i * JB_YLD];
+      gamma = gsum<32>(gamma, 0xffffffffu);
+    }
+    if (bad) gamma = INFINITY;
+    jac_finish<JB_T>(d, f, k, M, lmask, B, tid, write_all, 0xffffffffu, gamma, !bad);
   }
 }
 
@@ -581,7 +813,8 @@ static void launch_small(const Dev& d, int cls, int write_all, cudaStream_t st) 
 void launch_jacobian_gate(const Dev& d, int class_mask, int with_big, int write_all, cudaStream_t st) {
   static DevOnce once;     // function attributes are per device
   once.run([&] {
-    cudaFuncSetAttribute(k_jacobian_gate_big, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaFuncSetAttribute(k_jacobian_gate_big<16, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    cudaFuncSetAttribute(k_jacobian_gate_big<32, 2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   });
   Fork fk(d, st);
   if (class_mask & 1) {
@@ -599,9 +832,19 @@ void launch_jacobian_gate(const Dev& d, int class_mask, int with_big, int write_
   if (class_mask & 8) launch_small<32>(d, 3, write_all, fk.lane(3));
   if (with_big) {
     st = fk.lane(4);
-    const int smem_doubles = d.jac_big_smem_doubles;
-    KLAUNCH(d, KID_JACOBIAN_BIG, st,
-            (k_jacobian_gate_big<<<d.jac_big_grid, JAC_BIG_T, (size_t)smem_doubles * sizeof(double), st>>>(d, smem_doubles, write_all)));
+    const int sms = sm_count();
+    {   // tracks of up to JAC_BIG_SPLIT_M observations: S always fits, two CTAs per SM
+      const int Mm = std::min(d.Nmax, JAC_BIG_SPLIT_M);
+      const int sd = (int)(jb_fixed_doubles(Mm) + jb_S_doubles(Mm));
+      KLAUNCH(d, KID_JACOBIAN_BIG, st,
+              (k_jacobian_gate_big<16, 1, 2><<<std::min(d.jac_big_grid, 2 * sms), JB_T, (size_t)sd * sizeof(double), st>>>(d, 0, sd, write_all)));
+    }
+    if (d.Nmax > JAC_BIG_SPLIT_M) {   // longer tracks: one CTA per SM, S in shared memory up to ~38 observations, else in L2
+      const long long want = jb_fixed_doubles(d.Nmax) + jb_S_doubles(d.Nmax);
+      const int sd = (int)std::min<long long>(want, (200 * 1024) / 8);
+      KLAUNCH(d, KID_JACOBIAN_BIG, st,
+              (k_jacobian_gate_big<32, 2, 1><<<std::min(d.jac_big_grid, sms), JB_T, (size_t)sd * sizeof(double), st>>>(d, 1, sd, write_all)));
+    }
   }
 }
 void launch_cam_prepare(const Dev& d, cudaStream_t st) { KLAUNCH(d, KID_CAM_PREPARE, st, (k_cam_prepare<<<d.F, 64, 0, st>>>(d))); }

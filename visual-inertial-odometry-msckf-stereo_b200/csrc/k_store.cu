@@ -370,20 +370,22 @@ __global__ void __launch_bounds__(ST) k_plan_items(Dev d, int stage) {
     }
     // queue the item for its Jacobian kernel class: one atomic per warp and class instead of one per item
     {
-      const int cls = !isitem ? -1 : (M <= JAC_SMALL_M ? jac_class(M) : JAC_CLASSES);
+      const int cls = !isitem ? -1 : (M <= JAC_SMALL_M ? jac_class(M) : (M <= JAC_BIG_SPLIT_M ? JAC_CLASSES : JAC_CLASSES + 1));
       const unsigned lane = tid & 31;
 #pragma unroll
-      for (int c = 0; c <= JAC_CLASSES; ++c) {
+      for (int c = 0; c <= JAC_CLASSES + 1; ++c) {
         const unsigned bal = __ballot_sync(0xffffffffu, cls == c);
         if (bal == 0) continue;
         unsigned long long base = 0;
         if (lane == (unsigned)(__ffs(bal) - 1))
-          base = atomicAdd(d.stage_ctr + (c < JAC_CLASSES ? SC_NJAC_SMALL + c : SC_NJAC_BIG), (unsigned long long)__popc(bal));
+          base = atomicAdd(d.stage_ctr + (c < JAC_CLASSES ? SC_NJAC_SMALL + c : (c == JAC_CLASSES ? SC_NJAC_BIG : SC_NJAC_BIG2)),
+                           (unsigned long long)__popc(bal));
         base = __shfl_sync(0xffffffffu, base, __ffs(bal) - 1);
         if (cls == c) {
           const unsigned long long pos = base + __popc(bal & ((1u << lane) - 1u));
           if (c < JAC_CLASSES) d.wl_jac_small[(size_t)c * d.F * d.Fcap + pos] = make_int2(f, ni + r);
-          else d.wl_jac_big[pos] = make_int2(f, ni + r);
+          else if (c == JAC_CLASSES) d.wl_jac_big[pos] = make_int2(f, ni + r);
+          else d.wl_jac_big2[pos] = make_int2(f, ni + r);
         }
       }
     }
@@ -537,6 +539,11 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
       }
       cnt[MSCKF_CNT_K4_FLOPS] += 4 * k * n * n + 3 * k * k * n + (k * k * k) / 3;   // K4: 4kn^2 + 3k^2n + k^3/3
       cnt[MSCKF_CNT_K4_BYTES] += 16 * n * n + 8 * k * n;
+      // what the kernels execute: T = H_thin P[act,:] over the active columns only (half of it when H_thin = R is
+      // triangular), the upper triangle of S, Cholesky, W = U^-T [T | r], dx, the upper triangle of the downdate
+      const bool tri = mm > a;
+      cnt[MSCKF_CNT_K4_EXEC_FLOPS] += (tri ? 1 : 2) * k * a * (n + 1) + (tri ? (k * k * a) / 3 : k * k * a) + (k * k * k) / 3 +
+                                      k * k * (n + 1) + k * n * n + 2 * k * n;
     }
   }
 }

@@ -15,15 +15,9 @@
 #include <algorithm>
 #include "msckf_dev.cuh"
 #include "kernels.h"
+#include "dmma_tiles.cuh"
 
 namespace msckf {
-
-constexpr unsigned FULL = 0xffffffffu;
-constexpr int LDL = 12;            // leading dimension of the inverted diagonal block
-
-__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
-}
 
 __host__ __device__ inline int dmma_ldT(int nmax) {       // smallest ld >= nmax + 1 with ld = 4 (mod 16)
   int l = (nmax + 15) & ~15;                              // 16-wide downdate tiles stay inside a row
@@ -34,55 +28,6 @@ __host__ __device__ inline int dmma_ldT(int nmax) {       // smallest ld >= nmax
 size_t upd_dmma_smem_bytes(int nmax, int KC) {
   const size_t dbl = (size_t)KC * (KC + 4) + (size_t)KC * dmma_ldT(nmax) + 8 * LDL + ((nmax + 7) & ~7) + KC / 2 + 8;
   return dbl * sizeof(double);
-}
-
-// Cholesky of the 8x8 diagonal block at (p0, p0) of X (lower part) and the inverse of its factor, by one warp.
-// Lane r (mod 8) owns row r; entries travel by shuffle.  Linv (lower triangular) goes to sLinv [8][LDL].
-__device__ __forceinline__ bool chol8_inverse(const double* sX, int LDX, int p0, double* sLinv, int lane) {
-  const int r = lane & 7;
-  double a[8], il[8];
-#pragma unroll
-  for (int c = 0; c < 8; ++c) a[c] = sX[(p0 + r) * LDX + p0 + c];
-  bool bad = false;
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const double djj = __shfl_sync(FULL, a[j], j);
-    if (!(djj > 0.0)) bad = true;                      // warp-uniform
-    il[j] = rsqrt(djj);                                // one reciprocal square root instead of a square root and a divide
-    const double lrj = (r == j) ? djj * il[j] : a[j] * il[j];
-    a[j] = lrj;
-#pragma unroll
-    for (int c = j + 1; c < 8; ++c) {
-      const double lcj = __shfl_sync(FULL, lrj, c);
-      if (r >= c) a[c] -= lrj * lcj;
-    }
-  }
-  // column c = lane & 7 of L^-1 by forward substitution; L[r2][m] is broadcast from its owner lane
-  double x[8];
-#pragma unroll
-  for (int r2 = 0; r2 < 8; ++r2) {
-    double s = (r2 == r) ? 1.0 : 0.0;
-#pragma unroll
-    for (int m = 0; m < r2; ++m) {
-      const double lrm = __shfl_sync(FULL, a[m], r2);
-      s -= lrm * x[m];
-    }
-    x[r2] = s * il[r2];
-  }
-  if (lane < 8) {
-#pragma unroll
-    for (int r2 = 0; r2 < 8; ++r2) sLinv[r2 * LDL + r] = x[r2];
-  }
-  return bad;
-}
-
-
-// triangular index t -> (i, j), j <= i, row by row
-__device__ __forceinline__ void tri_decode(int t, int& i, int& j) {
-  i = (int)((sqrtf(8.0f * (float)t + 1.0f) - 1.0f) * 0.5f);
-  while ((i + 1) * (i + 2) / 2 <= t) ++i;
-  while (i * (i + 1) / 2 > t) --i;
-  j = t - i * (i + 1) / 2;
 }
 
 template <int KC, int DT>

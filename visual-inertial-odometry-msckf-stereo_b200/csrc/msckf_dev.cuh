@@ -30,7 +30,7 @@ constexpr unsigned ERRBIT_NOT_SPD = 8u;
 constexpr unsigned ERRBIT_CAM_CAP = 16u;
 
 // per-stage device counters (one memset per stage): pool bump pointer and work-list lengths
-constexpr int SC_POOL = 0, SC_NTRI = 1, SC_NJAC_BIG = 2, SC_NUPD_BIG = 3, SC_NJAC_SMALL = 4 /* .. 7: one per size class */, SC_NQR = 12 /* .. 16: tensor-pipe QR classes */, SC_NUPD_DMMA = 17 /* .. 21: tensor-pipe update classes */, SC_NQR_BUILD = 22 /* wide / uncompressed stacks (k_qr_build) */, SC_NQR_TALL = 23 /* pruning stacks (k_qr_tall) */, SC_COUNT = 24;
+constexpr int SC_POOL = 0, SC_NTRI = 1, SC_NJAC_BIG = 2, SC_NUPD_BIG = 3, SC_NJAC_SMALL = 4 /* .. 7: one per size class */, SC_NQR = 12 /* .. 16: tensor-pipe QR classes */, SC_NUPD_DMMA = 17 /* .. 21: tensor-pipe update classes */, SC_NQR_BUILD = 22 /* wide / uncompressed stacks (k_qr_build) */, SC_NQR_TALL = 23 /* pruning stacks (k_qr_tall) */, SC_NJAC_BIG2 = 24 /* tracks longer than JAC_BIG_SPLIT_M */, SC_COUNT = 26;
 // stacked-Jacobian compression classes: 0..3 = compressed (m > n_a) with n_a + 1 <= 16 / 32 / 48 / 64 columns (k_qr_dmma), 4 = general CTA kernel
 constexpr int QR_DMMA_CLASSES = 5;
 // one-CTA tensor-pipe update classes, aligned with the compression classes: max(k, n_a) + 1 <= 16 / 32 / 48 / 64
@@ -41,6 +41,8 @@ __host__ __device__ inline int jac_class(int M) { return M <= 2 ? 0 : (M == 3 ? 
 __host__ __device__ inline int jac_class_maxM(int c) { return c == 0 ? 2 : (c == 1 ? 3 : (c == 2 ? 4 : 6)); }
 // landmarks with at most this many observations go through the warp-per-landmark Jacobian kernel
 constexpr int JAC_SMALL_M = 6;
+// longer tracks go through the CTA-per-landmark kernel, in two size classes split at this track length
+constexpr int JAC_BIG_SPLIT_M = 16;
 
 struct Params {
   double Qc[4];            // gyro, gyro-bias, acc, acc-bias noise variances (msckf.py:132-137)
@@ -113,8 +115,9 @@ struct Dev {
   long long pool_cap;      // elements
   int2* wl_tri;            // [F*Fcap] (filter, candidate) pairs that need triangulation
   int2* wl_jac_small;      // [JAC_CLASSES][F*Fcap] (filter, item) pairs, M <= JAC_SMALL_M, binned by size class
-  int2* wl_jac_big;        // [F*Fcap] (filter, item) pairs, longer tracks
-  double* jac_scratch;     // T1 / S of long tracks that do not fit shared memory, per CTA of the big kernel
+  int2* wl_jac_big;        // [F*Fcap] (filter, item) pairs, tracks of JAC_SMALL_M < M <= JAC_BIG_SPLIT_M observations
+  int2* wl_jac_big2;       // [F*Fcap] (filter, item) pairs, longer tracks
+  double* jac_scratch;     // innovation covariance of tracks too long for shared memory, per CTA of the long-track kernel
   long long jac_scratch_stride;
   int jac_big_smem_doubles, jac_big_grid;
   int jac_rows_ok;         // short tracks go through the lane-per-row kernel (debug knob MSCKF_NO_JAC_ROWS)

@@ -294,6 +294,52 @@ def test_two_frames_in_flight_equal_sequential():
         assert np.array_equal(outs['blocking'][1][k], outs['pipelined'][1][k])
 
 
+def test_graph_replay_equals_eager_on_ragged_frames(monkeypatch):
+    """The captured frame graph is replayed with new message pointers every frame; its launch dimensions must not depend
+    on the message.  Filters of one batch receive different numbers of features and IMU samples per frame (ragged
+    offsets of the C ABI) and the counts change from frame to frame: the replayed graph returns, bit for bit, what
+    eager launches return."""
+    F, n_frames, max_cam = 3, 26, 6
+    st = synth.make_structure(n_frames, 70, structure_seed=9)
+    streams = [synth.realize(st, noise_seed=300 + k) for k in range(F)]
+    dcfg = ConfigEuRoC()
+    dcfg._vio_max_cam_state_size__ = max_cam
+    s0 = streams[0]
+
+    def run():
+        batch = MSCKFBatch(dcfg, F, feature_capacity=256)
+        try:
+            batch.initialize_gravity_and_bias(np.stack([s.gyro[:200] for s in streams]), np.stack([s.acc[:200] for s in streams]))
+            out = []
+            for f in range(n_frames):
+                a, b = s0.imu_range_for_frame(f)
+                take = np.flatnonzero(batch.select_imu(float(s0.frame_ts[f]), s0.imu_ts[a:b])) + a
+                ids = s0.frame_ids[f].astype(np.int64)
+                imu_off, feat_off, ts, gy, ac, fid, uv = [0], [0], [], [], [], [], []
+                for k in range(F):
+                    tk = take[(k + f) % 2:] if len(take) > 3 else take          # some filters skip their first sample
+                    nk = len(ids) - ((3 * k + f) % 11)                          # and see fewer features
+                    ts.append(s0.imu_ts[tk]); gy.append(streams[k].gyro[tk]); ac.append(streams[k].acc[tk])
+                    fid.append(ids[:nk]); uv.append(streams[k].frame_uv[f][:nk])
+                    imu_off.append(imu_off[-1] + len(tk)); feat_off.append(feat_off[-1] + nk)
+                cam_ids = np.full(F, batch.next_imu_id, dtype=np.int64)
+                batch.next_imu_id += 1
+                imu, rst = batch.ctx.feature_callback(imu_off, np.concatenate(ts), np.concatenate(gy), np.concatenate(ac), cam_ids,
+                                                      feat_off, np.concatenate(fid), np.concatenate(uv))
+                out.append(imu)
+            return np.array(out), [batch.ctx.get_cov(k) for k in range(F)], [batch.ctx.get_features(k, with_obs=False)[0] for k in range(F)]
+        finally:
+            batch.close()
+
+    g_imu, g_P, g_ids = run()
+    monkeypatch.setenv('MSCKF_NO_GRAPH', '1')
+    e_imu, e_P, e_ids = run()
+    assert np.array_equal(g_imu, e_imu)
+    for k in range(F):
+        assert np.array_equal(g_P[k], e_P[k]) and np.array_equal(g_ids[k], e_ids[k])
+    assert not np.array_equal(g_P[0], g_P[1])                  # the filters really did see different messages
+
+
 @pytest.mark.parametrize('knob', ['MSCKF_NO_DMMA', 'MSCKF_NO_LANES', 'MSCKF_NO_JAC_ROWS', 'MSCKF_NO_QR_TALL', 'MSCKF_NO_GRAPH'])
 def test_alternative_kernel_paths(knob, monkeypatch):
     """The library's debugging knobs route the same work through its other kernels: the tiled update kernels instead of

@@ -328,6 +328,53 @@ def test_remove_lost_features_vs_oracle(units, dev):
     assert rel_err(sd['P'], so['P']) < TOL_STATE
 
 
+def test_gate_with_indefinite_innovation_covariance_uses_lu(units, dev):
+    """gating_test as the reference writes it (msckf.py:606-614) solves with LU, which also answers when H P H^T + sigma^2 I
+    is not positive definite.  With P replaced by -P on both sides every gate of the mid-stream state is indefinite: the
+    device's Cholesky gate must hand those landmarks to its LU kernel and arrive at the reference's gamma and decision.
+    (The update that follows is a different matter: its indefinite S is an error by design, like a LinAlgError.)"""
+    from msckf_b200 import capi
+    u = units
+    of = oracle_filter_from_units(u)
+    Pneg = -np.array(of.state_server._vio_state_cov__)
+    of.state_server._vio_state_cov__ = Pneg.copy()
+    dev.ctx.set_cov(0, Pneg)
+    of.log = {}
+    of.remove_lost_features()
+    try:
+        dev.remove_lost_features()          # gates first; the update then meets an indefinite S of its own and reports it
+    except np.linalg.LinAlgError:
+        pass
+    log = dev.stage_log(0)
+    st = log['status']
+    gates = of.log.get('gate', [])
+    sel = [i for i, s in enumerate(st) if s in (capi.FEAT_GATE_PASS, capi.FEAT_GATE_FAIL)]
+    assert len(sel) == len(gates) and len(gates) >= 10
+    gam = log['gamma'][sel]
+    ref = np.array([g[0] for g in gates])
+    assert np.all(np.isfinite(gam))
+    assert np.all(np.abs(gam - ref) <= 1e-7 * np.abs(ref)), np.max(np.abs(gam - ref) / np.abs(ref))
+    assert [st[i] == capi.FEAT_GATE_PASS for i in sel] == [g[2] for g in gates]
+    assert (ref < 0).any()                                    # indefinite: some gammas are negative (and pass)
+    assert int(dev.ctx.counters()[0, capi.CNT_GATE_NOT_SPD]) >= 1
+
+
+def test_duplicate_feature_ids_are_rejected(units):
+    """add_feature_observations requires unique ids inside one message (the front end guarantees it, image.py:425-438):
+    a repeated id is reported as an argument error instead of silently creating two landmarks."""
+    from msckf_b200 import capi
+    dev = device_filter_from_units(units)
+    try:
+        ids = np.array([900001, 900002, 900001, 900003], dtype=np.int64)
+        uv = np.zeros((4, 4))
+        dev.ctx.add_observations([0, 4], ids, uv)
+        with pytest.raises(capi.MsckfCudaError) as ei:
+            dev.ctx.sync()
+        assert ei.value.code == capi.ERR_ARG and 'duplicate' in str(ei.value)
+    finally:
+        dev.close()
+
+
 def test_errors_are_loud(units):
     from msckf_b200 import capi
     from msckf_b200.config import ConfigEuRoC

@@ -143,6 +143,7 @@ static int check_device_errors(msckf_ctx* ctx, unsigned* h_err = nullptr) {
   if (e & ERRBIT_POOL) s += " jacobian pool exhausted (raise jacobian_pool_bytes);";
   if (e & ERRBIT_ROWS) s += " stacked-Jacobian rows exceed max_rows;";
   if (e & ERRBIT_CAM_CAP) s += " camera-state window full (augment without prune);";
+  if (e & ERRBIT_DUP_ID) { s += " duplicate feature id inside one message (ids must be unique, msckf_add_observations);"; rc = MSCKF_ERR_ARG; }
   if (e & ERRBIT_NOT_SPD) { s += " innovation covariance not positive definite;" + det; rc = MSCKF_ERR_NUMERIC; }
   ctx->err = s;
   return rc;
@@ -237,7 +238,7 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   }
   cudaDeviceProp prop;
   cudaGetDeviceProperties(&prop, cfg->device);
-  if (prop.major < 10) {
+  if (prop.major != 10) {
     g_create_error = std::string("device is not sm_100-class: ") + prop.name + " (this library ships sm_100a code only, no fallback)";
     return MSCKF_ERR_CUDA;
   }
@@ -357,7 +358,8 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   DA(d.item_dof, F * Fc); DA(d.item_gamma, F * Fc); DA(d.item_pass, F * Fc); DA(d.nitem, F);
   DA(d.rm_mask, F); DA(d.rm_idx, F * 2);
   DA(d.pool, (size_t)d.pool_cap); DA(d.stage_ctr, SC_COUNT); DA(d.item_lmask, F * Fc);
-  DA(d.wl_tri, F * Fc); DA(d.wl_jac_small, JAC_CLASSES * F * Fc); DA(d.wl_jac_big, F * Fc); DA(d.wl_jac_big2, F * Fc);
+  DA(d.wl_tri, F * Fc); DA(d.wl_jac_small, JAC_CLASSES * F * Fc); DA(d.wl_jac_big, F * Fc); DA(d.wl_jac_big2, F * Fc); DA(d.wl_lu, F * Fc);
+  { const size_t Rm = 4 * Nm - 3; DA(d.lu_scratch, Rm * 6 * Nm + Rm * Rm + 3 * Rm + 8); }
   DA(d.jac_scratch, (size_t)d.jac_big_grid * d.jac_scratch_stride);
   DA(d.Rnode, F * (size_t)d.qr_leaf_cap * (size_t)d.Rnode_stride);
   DA(d.Adense, (size_t)d.Adense_elems);

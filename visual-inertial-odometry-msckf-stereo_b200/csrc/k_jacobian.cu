@@ -314,14 +314,17 @@ __device__ __forceinline__ void jac_finish(const Dev& d, int f, int k, int M, un
   const int C6 = 6 * M, R = 4 * M - 3;
   if (tid == 0) {
     // S is positive definite in exact arithmetic; a landmark whose position is wildly off (a gross outlier) can make
-    // H P H^T so large that rounding produces a non-positive pivot.  The reference's LU returns noise there; the
-    // landmark is rejected (gamma = inf) and counted, it is not an error of the filter.
-    if (!spd) atomicAdd((unsigned long long*)(d.counters + (size_t)NCNT * f + MSCKF_CNT_GATE_NOT_SPD), 1ull);
+    // H P H^T so large that rounding produces a non-positive pivot.  The reference's LU (msckf.py:609) still returns
+    // some gamma there: the landmark is counted and its gate is redone by k_gate_lu from the record written below.
+    if (!spd) {
+      atomicAdd((unsigned long long*)(d.counters + (size_t)NCNT * f + MSCKF_CNT_GATE_NOT_SPD), 1ull);
+      queue_gate_lu(d.wl_lu, d.stage_ctr, f, k);
+    }
     const int pass = (gamma < d.prm->chi2[d.item_dof[ik]]) ? 1 : 0;
     d.item_gamma[ik] = gamma;
     d.item_pass[ik] = pass;
     d.item_lmask[ik] = lmask;
-    B.Tm[8] = (double)pass;
+    B.Tm[8] = (double)(pass || !spd);
   }
   gsync<NT>(gmask);
   const int pass = (int)B.Tm[8];
@@ -433,6 +436,115 @@ __device__ void jac_core(const Dev& d, int f, int k, int M, unsigned long long l
   }
   if (!spd) gamma = INFINITY;
   jac_finish<NT>(d, f, k, M, lmask, B, tid, write_all, gmask, gamma, spd);
+}
+
+// ------------------------------------------------------------------ gate by LU (msckf.py:606-614 as written)
+// gamma = r^T S^-1 r through Gaussian elimination with partial pivoting (what np.linalg.solve / dgesv does) for an
+// n x n system in global memory (row-major, ld = n); S and y are overwritten, x receives the solution.  One CTA.
+__device__ double lu_gamma(double* S, int n, double* y, double* x, const double* r0, int tid, int nthr, double* s_val, int* s_idx) {
+  for (int j = 0; j < n; ++j) {
+    double best = -1.0;
+    int bi = j;
+    for (int i = j + tid; i < n; i += nthr) {
+      const double a = fabs(S[(size_t)i * n + j]);
+      if (a > best) { best = a; bi = i; }
+    }
+    s_val[tid] = best;
+    s_idx[tid] = bi;
+    __syncthreads();
+    if (tid == 0) {
+      for (int t = 1; t < nthr; ++t)
+        if (s_val[t] > s_val[0] || (s_val[t] == s_val[0] && s_idx[t] < s_idx[0])) { s_val[0] = s_val[t]; s_idx[0] = s_idx[t]; }
+    }
+    __syncthreads();
+    const int p = s_idx[0];
+    if (p != j) {
+      for (int c = tid; c < n; c += nthr) {
+        const double a = S[(size_t)j * n + c];
+        S[(size_t)j * n + c] = S[(size_t)p * n + c];
+        S[(size_t)p * n + c] = a;
+      }
+      if (tid == 0) { const double a = y[j]; y[j] = y[p]; y[p] = a; }
+    }
+    __syncthreads();
+    const double piv = S[(size_t)j * n + j], yj = y[j];
+    for (int i = j + 1 + tid; i < n; i += nthr) {
+      const double l = S[(size_t)i * n + j] / piv;
+      y[i] -= l * yj;
+      for (int c = j + 1; c < n; ++c) S[(size_t)i * n + c] -= l * S[(size_t)j * n + c];
+    }
+    __syncthreads();
+  }
+  for (int i = n - 1; i >= 0; --i) {            // back substitution, one row at a time
+    double s = 0.0;
+    for (int c = i + 1 + tid; c < n; c += nthr) s += S[(size_t)i * n + c] * x[c];
+    s_val[tid] = s;
+    __syncthreads();
+    if (tid == 0) {
+      double t = 0.0;
+      for (int q = 0; q < nthr; ++q) t += s_val[q];
+      x[i] = (y[i] - t) / S[(size_t)i * n + i];
+    }
+    __syncthreads();
+  }
+  double g = 0.0;
+  if (tid == 0)
+    for (int i = 0; i < n; ++i) g += r0[i] * x[i];
+  return g;                                      // valid on thread 0
+}
+
+// Redoes the gate of the landmarks queued in wl_lu from their records (projected rows H' [R][6M] and residual r'):
+// T1 = H' Pcc, S = T1 H'^T + sigma^2 I, gamma by LU.  Rare (a gross outlier among ~1e8 gates): one CTA walks the list.
+__global__ void __launch_bounds__(256) k_gate_lu(Dev d) {
+  __shared__ double s_val[256];
+  __shared__ int s_idx[256];
+  __shared__ int s_cl[64];
+  const int tid = threadIdx.x;
+  const int n = (int)d.stage_ctr[SC_NLU];
+  for (int w = 0; w < n; ++w) {
+    const int2 it = d.wl_lu[w];
+    const int f = it.x, k = it.y;
+    const size_t ik = (size_t)f * d.Fcap + k;
+    const int R = d.item_rows[ik], M = (R + 3) / 4, C6 = 6 * M, ldr = C6 + 1, ld = d.ld;
+    const unsigned long long lmask = d.item_lmask[ik];
+    if (d.item_off[ik] + jac_record_doubles(M) > d.pool_cap) continue;
+    const double* rec = d.pool + d.item_off[ik];
+    const double* P = d.P + (size_t)f * ld * ld;
+    double* T1 = d.lu_scratch;                  // [R][C6]
+    double* S = T1 + (size_t)R * C6;            // [R][R]
+    double* y = S + (size_t)R * R;              // [R]
+    double* x = y + R;                          // [R]
+    __syncthreads();
+    for (int c = tid; c < 64; c += 256)
+      if ((lmask >> c) & 1ull) s_cl[__popcll(lmask & ((1ull << c) - 1ull))] = c;
+    __syncthreads();
+    for (int e = tid; e < R * C6; e += 256) {
+      const int i = e / C6, c = e - i * C6;
+      const double* pcol = P + (size_t)(NI + 6 * s_cl[c / 6] + c % 6) * ld + NI;     // row of P = column (P is symmetric)
+      double acc = 0.0;
+      for (int b = 0; b < M; ++b)
+        for (int e6 = 0; e6 < 6; ++e6) acc += rec[(size_t)i * ldr + 6 * b + e6] * pcol[6 * s_cl[b] + e6];
+      T1[e] = acc;
+    }
+    __syncthreads();
+    for (int e = tid; e < R * R; e += 256) {
+      const int i = e / R, j = e - i * R;
+      double acc = (i == j) ? d.prm->obs_noise : 0.0;
+      for (int c = 0; c < C6; ++c) acc += T1[(size_t)i * C6 + c] * rec[(size_t)j * ldr + c];
+      S[e] = acc;
+    }
+    for (int i = tid; i < R; i += 256) { y[i] = rec[(size_t)i * ldr + C6]; x[i] = 0.0; }
+    __syncthreads();
+    // r0 = the residual column of the record (strided): gather it behind x
+    double* r0 = x + R;
+    for (int i = tid; i < R; i += 256) r0[i] = rec[(size_t)i * ldr + C6];
+    __syncthreads();
+    const double gamma = lu_gamma(S, R, y, x, r0, tid, 256, s_val, s_idx);
+    if (tid == 0) {
+      d.item_gamma[ik] = gamma;
+      d.item_pass[ik] = (gamma < d.prm->chi2[d.item_dof[ik]]) ? 1 : 0;    // (NaN compares false: rejected)
+    }
+  }
 }
 
 // logical-order observation mask of a landmark, computed by a group of G lanes (gmask, first lane gbase)
@@ -816,6 +928,8 @@ void launch_jacobian_gate(const Dev& d, int class_mask, int with_big, int write_
     cudaFuncSetAttribute(k_jacobian_gate_big<16, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
     cudaFuncSetAttribute(k_jacobian_gate_big<32, 2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   });
+  cudaStream_t main_st = st;
+  {
   Fork fk(d, st);
   if (class_mask & 1) {
     if (d.jac_rows_ok) launch_jacobian_rows(d, 0, write_all, fk.lane(0));
@@ -846,7 +960,10 @@ void launch_jacobian_gate(const Dev& d, int class_mask, int with_big, int write_
               (k_jacobian_gate_big<32, 2, 1><<<std::min(d.jac_big_grid, sms), JB_T, (size_t)sd * sizeof(double), st>>>(d, 1, sd, write_all)));
     }
   }
+  }
+  launch_gate_lu(d, main_st);          // after the join: gates whose innovation covariance was not positive definite to rounding
 }
+void launch_gate_lu(const Dev& d, cudaStream_t st) { KLAUNCH(d, KID_MISC, st, (k_gate_lu<<<1, 256, 0, st>>>(d))); }
 void launch_cam_prepare(const Dev& d, cudaStream_t st) { KLAUNCH(d, KID_CAM_PREPARE, st, (k_cam_prepare<<<d.F, 64, 0, st>>>(d))); }
 void launch_measurement_jacobian(const Dev& d, int filter, int cam_logical, int slot, double* out, cudaStream_t st) {
   KLAUNCH(d, KID_MISC, st, (k_measurement_jacobian<<<1, 32, 0, st>>>(d, filter, cam_logical, slot, out)));

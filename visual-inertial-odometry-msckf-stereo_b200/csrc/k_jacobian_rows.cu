@@ -262,14 +262,18 @@ __global__ void __launch_bounds__(JR_T, jr_ctas_per_sm<M>()) k_jacobian_rows(Dev
     if (!spd) gamma = INFINITY;
     const int pass = (gamma < prm.chi2[d.item_dof[ik]]) ? 1 : 0;
     if (active && r == 0) {
-      // a landmark whose S is not positive definite to rounding (gross outlier) is rejected and counted, see k_jacobian.cu
-      if (!spd) atomicAdd((unsigned long long*)(d.counters + (size_t)NCNT * f + MSCKF_CNT_GATE_NOT_SPD), 1ull);
+      // a landmark whose S is not positive definite to rounding (gross outlier) is counted and its gate redone with an
+      // LU solve, as the reference computes it (k_gate_lu, k_jacobian.cu)
+      if (!spd) {
+        atomicAdd((unsigned long long*)(d.counters + (size_t)NCNT * f + MSCKF_CNT_GATE_NOT_SPD), 1ull);
+        queue_gate_lu(d.wl_lu, d.stage_ctr, f, k);
+      }
       d.item_gamma[ik] = gamma;
       d.item_pass[ik] = pass;
       d.item_lmask[ik] = lmask;
     }
     // ---- record for the stacking / QR kernel: the projected rows and residual, row-major [R][6M+1]
-    if (active && (pass || write_all) && d.item_off[ik] + jac_record_doubles(M) <= d.pool_cap) {
+    if (active && (pass || write_all || !spd) && d.item_off[ik] + jac_record_doubles(M) <= d.pool_cap) {
       double* out = d.pool + d.item_off[ik];
       for (int e = r; e < R * LDR; e += G) out[e] = sH[e];
     }

@@ -12,6 +12,8 @@
 //                                                   Y = T^T W                                   (DMMA)
 //                                                   R(panel rows, tile) -= Y,  C(:, tile) -= V Y (DMMA, K = 8).
 // Rows of C and R have a leading dimension of 4 (mod 16) doubles: every fragment load is bank-conflict free.
+// Look-ahead: the panel warp first applies panel p to the columns of panel p+1 and factors it while the other warps
+// finish the trailing tiles of panel p (T is double-buffered) -- one CTA barrier per panel, nobody waits for the panel.
 #include <algorithm>
 #include "msckf_dev.cuh"
 #include "kernels.h"
@@ -34,7 +36,7 @@ __device__ __forceinline__ double qd_allsum(double v) {
 
 size_t qr_dmma_smem_bytes(int cap) {
   const size_t ldr = cap + 4;
-  const size_t dbl = (size_t)(cap + QD_CR) * ldr + 8 * QD_LDL + 8 * 8 * QD_LDL + 8;
+  const size_t dbl = (size_t)(cap + QD_CR) * ldr + 2 * 8 * QD_LDL + 8 * 8 * QD_LDL + 8;
   return dbl * sizeof(double) + 64 * sizeof(int) + 16;
 }
 
@@ -138,14 +140,56 @@ __device__ __forceinline__ void qd_panel(double* sR, double* sC, double* sTm, in
   }
 }
 
+// Applies the block reflector of panel j0 (V in the chunk, T in sTm) to the 8-column tile at c0 (R rows and chunk columns).
+__device__ __forceinline__ void qd_apply(double* sR, double* sC, const double* sTm, double* sYw, int ldr, int j0, int c0, int crk, int crt,
+                                         int g, int tg) {
+  double* rp = sR + (j0 + g) * ldr + c0 + 2 * tg;
+  const double r_old0 = rp[0], r_old1 = rp[1];
+  double w0[4] = {r_old0, 0.0, 0.0, 0.0}, w1[4] = {r_old1, 0.0, 0.0, 0.0};
+  const double* va = sC + tg * ldr + j0 + g;
+  const double* cb = sC + tg * ldr + c0 + g;
+  int ks = 0;
+  for (; ks + 4 <= crk; ks += 4) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) qd_dmma(w0[u], w1[u], va[(4 * (ks + u)) * ldr], cb[(4 * (ks + u)) * ldr]);
+  }
+  for (; ks < crk; ++ks) qd_dmma(w0[0], w1[0], va[4 * ks * ldr], cb[4 * ks * ldr]);
+  const double ww0 = (w0[0] + w0[1]) + (w0[2] + w0[3]), ww1 = (w1[0] + w1[1]) + (w1[2] + w1[3]);
+  // Y = T^T W
+  sYw[g * QD_LDL + 2 * tg] = ww0;
+  sYw[g * QD_LDL + 2 * tg + 1] = ww1;
+  __syncwarp();
+  const double wb0 = sYw[tg * QD_LDL + g], wb1 = sYw[(4 + tg) * QD_LDL + g];
+  const double ta0 = sTm[tg * QD_LDL + g], ta1 = sTm[(4 + tg) * QD_LDL + g];
+  double y0 = 0.0, y1 = 0.0;
+  qd_dmma(y0, y1, ta0, wb0);
+  qd_dmma(y0, y1, ta1, wb1);
+  rp[0] = r_old0 - y0;
+  rp[1] = r_old1 - y1;
+  __syncwarp();
+  sYw[g * QD_LDL + 2 * tg] = y0;
+  sYw[g * QD_LDL + 2 * tg + 1] = y1;
+  __syncwarp();
+  const double yb0 = sYw[tg * QD_LDL + g], yb1 = sYw[(4 + tg) * QD_LDL + g];
+  // C(:, tile) -= V Y
+  for (int rt = 0; rt < crt; ++rt) {
+    const double* vr = sC + (8 * rt + g) * ldr + j0 + tg;
+    double2* cp = (double2*)(sC + (8 * rt + g) * ldr + c0 + 2 * tg);
+    double2 cv = *cp;
+    qd_dmma(cv.x, cv.y, -vr[0], yb0);
+    qd_dmma(cv.x, cv.y, -vr[4], yb1);
+    *cp = cv;
+  }
+  __syncwarp();
+}
 
 __global__ void __launch_bounds__(QD_T, 2) k_qr_dmma(Dev d, int cls, int cap) {
   extern __shared__ __align__(16) double qs[];
   const int ldr = cap + 4;
   double* sR = qs;                                   // [cap][ldr]
   double* sC = sR + cap * ldr;                       // [QD_CR][ldr]
-  double* sTm = sC + QD_CR * ldr;                    // [8][QD_LDL]
-  double* sY = sTm + 8 * QD_LDL;                     // [8 warps][8][QD_LDL]
+  double* sTm = sC + QD_CR * ldr;                    // [2][8][QD_LDL]  T of the panel being applied / being factored
+  double* sY = sTm + 2 * 8 * QD_LDL;                 // [8 warps][8][QD_LDL]
   int* camcol = (int*)(sY + 8 * 8 * QD_LDL);         // [64] logical camera -> active column block
   __shared__ int s_c0;
   const int tid = threadIdx.x, nthr = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarp = nthr >> 5;
@@ -193,51 +237,20 @@ __global__ void __launch_bounds__(QD_T, 2) k_qr_dmma(Dev d, int cls, int cap) {
       }
       __syncthreads();
       const int pb0 = s_c0 >> 3;                      // columns before the chunk's first non-zero column need no elimination
+      if (warp == 0) qd_panel(sR, sC, sTm + (pb0 & 1) * 8 * QD_LDL, ldr, 8 * pb0, min(8, na - 8 * pb0), pb0 + 1 < nct, lane);
+      __syncthreads();
       for (int pb = pb0; pb < npan; ++pb) {
         const int j0 = 8 * pb;
-        if (warp == 0) qd_panel(sR, sC, sTm, ldr, j0, min(8, na - j0), pb + 1 < nct, lane);
-        __syncthreads();
-        // ---- trailing tiles: one 8-column tile per warp
-        for (int ct = pb + 1 + warp; ct < nct; ct += nwarp) {
-          const int c0 = 8 * ct;
-          double* rp = sR + (j0 + g) * ldr + c0 + 2 * tg;
-          const double r_old0 = rp[0], r_old1 = rp[1];
-          double w0[4] = {r_old0, 0.0, 0.0, 0.0}, w1[4] = {r_old1, 0.0, 0.0, 0.0};
-          const double* va = sC + tg * ldr + j0 + g;
-          const double* cb = sC + tg * ldr + c0 + g;
-          int ks = 0;
-          for (; ks + 4 <= crk; ks += 4) {
-#pragma unroll
-            for (int u = 0; u < 4; ++u) qd_dmma(w0[u], w1[u], va[(4 * (ks + u)) * ldr], cb[(4 * (ks + u)) * ldr]);
+        const double* Tm = sTm + (pb & 1) * 8 * QD_LDL;
+        if (pb + 1 < npan) {                          // another panel follows: warp 0 looks ahead
+          if (warp == 0) {
+            qd_apply(sR, sC, Tm, sYw, ldr, j0, j0 + 8, crk, crt, g, tg);
+            qd_panel(sR, sC, sTm + ((pb + 1) & 1) * 8 * QD_LDL, ldr, j0 + 8, min(8, na - j0 - 8), pb + 2 < nct, lane);
+          } else {
+            for (int ct = pb + 2 + (warp - 1); ct < nct; ct += nwarp - 1) qd_apply(sR, sC, Tm, sYw, ldr, j0, 8 * ct, crk, crt, g, tg);
           }
-          for (; ks < crk; ++ks) qd_dmma(w0[0], w1[0], va[4 * ks * ldr], cb[4 * ks * ldr]);
-          const double ww0 = (w0[0] + w0[1]) + (w0[2] + w0[3]), ww1 = (w1[0] + w1[1]) + (w1[2] + w1[3]);
-          // Y = T^T W
-          sYw[g * QD_LDL + 2 * tg] = ww0;
-          sYw[g * QD_LDL + 2 * tg + 1] = ww1;
-          __syncwarp();
-          const double wb0 = sYw[tg * QD_LDL + g], wb1 = sYw[(4 + tg) * QD_LDL + g];
-          const double ta0 = sTm[tg * QD_LDL + g], ta1 = sTm[(4 + tg) * QD_LDL + g];
-          double y0 = 0.0, y1 = 0.0;
-          qd_dmma(y0, y1, ta0, wb0);
-          qd_dmma(y0, y1, ta1, wb1);
-          rp[0] = r_old0 - y0;
-          rp[1] = r_old1 - y1;
-          __syncwarp();
-          sYw[g * QD_LDL + 2 * tg] = y0;
-          sYw[g * QD_LDL + 2 * tg + 1] = y1;
-          __syncwarp();
-          const double yb0 = sYw[tg * QD_LDL + g], yb1 = sYw[(4 + tg) * QD_LDL + g];
-          // C(:, tile) -= V Y
-          for (int rt = 0; rt < crt; ++rt) {
-            const double* vr = sC + (8 * rt + g) * ldr + j0 + tg;
-            double2* cp = (double2*)(sC + (8 * rt + g) * ldr + c0 + 2 * tg);
-            double2 cv = *cp;
-            qd_dmma(cv.x, cv.y, -vr[0], yb0);
-            qd_dmma(cv.x, cv.y, -vr[4], yb1);
-            *cp = cv;
-          }
-          __syncwarp();
+        } else {
+          for (int ct = pb + 1 + warp; ct < nct; ct += nwarp) qd_apply(sR, sC, Tm, sYw, ldr, j0, 8 * ct, crk, crt, g, tg);
         }
         __syncthreads();
       }

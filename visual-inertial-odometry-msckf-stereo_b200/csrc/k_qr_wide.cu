@@ -36,9 +36,16 @@ __host__ __device__ inline int qw_rows_per_leaf(int m, int leaf_cap, int CR) {
   return (per + CR - 1) / CR * CR;
 }
 
-static size_t qw_smem_bytes(int capmax, int CR) {
-  const size_t LP = capmax + 4;
+__host__ __device__ inline size_t qw_smem_bytes(int cap, int CR) {
+  const size_t LP = cap + 4;
   return ((size_t)CR * LP + 2 * 8 * LP + 2 * 8 * QW_LDL + 8 * 8 * QW_LDL) * sizeof(double) + 64 * sizeof(int) + 64;
+}
+// rows per chunk of a stack with `cap` columns: as many as the shared memory of the launch holds next to the slabs
+// (128, 64 or 32: the panel warp keeps 4, 2 or 1 rows per lane)
+__host__ __device__ inline int qw_chunk_rows(int cap, size_t smem_bytes) {
+  for (int cr = 128; cr > 32; cr >>= 1)
+    if (qw_smem_bytes(cap, cr) <= smem_bytes) return cr;
+  return 32;
 }
 
 // Panel factorisation by one warp.  x[t][c] = C(lane + 32 t, j0 + c).  The 8 x 8 diagonal block of R comes from the
@@ -182,20 +189,19 @@ __device__ __forceinline__ void qw_apply(const double* slab, double* Rg, int ldg
   __syncwarp();
 }
 
-template <int RPL>
-__global__ void __launch_bounds__(QW_T, 1) k_qr_wide(Dev d, int level) {
-  constexpr int CR = 32 * RPL;
+__device__ __forceinline__ void qw_panel_rows(int rpl, const double* slab, double* Rg, int ldg, double* sC, double* sTm, int LP, int j0,
+                                              int nrefl, bool need_T, int lane) {
+  if (rpl == 4) qw_panel<4>(slab, Rg, ldg, sC, sTm, LP, j0, nrefl, need_T, lane);
+  else if (rpl == 2) qw_panel<2>(slab, Rg, ldg, sC, sTm, LP, j0, nrefl, need_T, lane);
+  else qw_panel<1>(slab, Rg, ldg, sC, sTm, LP, j0, nrefl, need_T, lane);
+}
+
+__global__ void __launch_bounds__(QW_T, 1) k_qr_wide(Dev d, int level, unsigned smem_bytes) {
   extern __shared__ __align__(128) double qs[];
   __shared__ uint64_t s_slab[2], s_rows;
   __shared__ int s_c0;
-  const int capmax = d.qr_capcols, LP = capmax + 4, ldg = capmax;
-  double* sC = qs;                                    // [CR][LP]   chunk of stacked rows
-  double* sSlab = sC + (size_t)CR * LP;               // [2][8][LP] the 8 rows of R a panel step reads
-  double* sTm = sSlab + 2 * 8 * LP;                   // [2][8][QW_LDL]
-  double* sY = sTm + 2 * 8 * QW_LDL;                  // [8 warps][8][QW_LDL]
-  int* camcol = (int*)(sY + 8 * 8 * QW_LDL);          // [64] logical camera -> active column block
+  const int ldg = d.qr_capcols;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, tg = lane & 3;
-  double* sYw = sY + warp * 8 * QW_LDL;
   if (tid == 0) {
     mbar_init(&s_slab[0], 1);
     mbar_init(&s_slab[1], 1);
@@ -212,6 +218,14 @@ __global__ void __launch_bounds__(QW_T, 1) k_qr_wide(Dev d, int level) {
     const int m = d.m_rows[f], na = d.n_act[f];
     if (m <= na) continue;                            // not compressed (msckf.py:549): k_qr_build copies the rows out
     const int cap = qw_cap(na), nct = cap >> 3, npan = (na + 7) >> 3;
+    // shared-memory layout of this stack: the chunk is as tall as its own width allows
+    const int LP = cap + 4, CR = qw_chunk_rows(cap, smem_bytes), RPL = CR >> 5;
+    double* sC = qs;                                    // [CR][LP]   chunk of stacked rows
+    double* sSlab = sC + (size_t)CR * LP;               // [2][8][LP] the 8 rows of R a panel step reads
+    double* sTm = sSlab + 2 * 8 * LP;                   // [2][8][QW_LDL]
+    double* sY = sTm + 2 * 8 * QW_LDL;                  // [8 warps][8][QW_LDL]
+    int* camcol = (int*)(sY + 8 * 8 * QW_LDL);          // [64] logical camera -> active column block
+    double* sYw = sY + warp * 8 * QW_LDL;
     const int rpl = qw_rows_per_leaf(m, leaf_cap, CR), nleaf = (m + rpl - 1) / rpl;
     int rb = 0, re = 0;
     const double* Rb = nullptr;
@@ -239,7 +253,6 @@ __global__ void __launch_bounds__(QW_T, 1) k_qr_wide(Dev d, int level) {
 
     for (int r0 = rb; r0 < re; r0 += CR) {
       const int cr = min(CR, re - r0);
-      const int crk = (cr + 3) >> 2, crt = (cr + 7) >> 3;
       int pb0;
       __syncthreads();                                // the previous chunk is folded (and its R stores fenced)
       if (level < 0) {
@@ -286,11 +299,15 @@ __global__ void __launch_bounds__(QW_T, 1) k_qr_wide(Dev d, int level) {
       if (warp == 1) issue_slab(pb0);
       if (warp == 0) {
         mbar_wait(&s_slab[pb0 & 1], su[pb0 & 1] & 1u);
-        qw_panel<RPL>(sSlab + (size_t)(pb0 & 1) * 8 * LP, Rg, ldg, sC, sTm + (pb0 & 1) * 8 * QW_LDL, LP, 8 * pb0, min(8, na - 8 * pb0), pb0 + 1 < nct, lane);
+        qw_panel_rows(RPL, sSlab + (size_t)(pb0 & 1) * 8 * LP, Rg, ldg, sC, sTm + (pb0 & 1) * 8 * QW_LDL, LP, 8 * pb0, min(8, na - 8 * pb0), pb0 + 1 < nct, lane);
       }
       __syncthreads();
       for (int pb = pb0; pb < npan; ++pb) {
         const int cur = pb & 1, j0 = 8 * pb;
+        // rows of the chunk that can be non-zero in this panel: all of them for stacked landmark rows; a triangular factor
+        // being folded (tree levels) has nothing below its diagonal, so row r0 + i only matters once 8 pb + 7 >= r0 + i
+        const int rows_nz = level < 0 ? cr : min(cr, j0 + 8 - r0);
+        const int crk = (rows_nz + 3) >> 2, crt = (rows_nz + 7) >> 3;
         const double* slab = sSlab + (size_t)cur * 8 * LP;
         const double* Tm = sTm + cur * 8 * QW_LDL;
         const bool ahead = pb + 1 < npan;             // another panel follows: warp 0 looks ahead
@@ -300,7 +317,7 @@ __global__ void __launch_bounds__(QW_T, 1) k_qr_wide(Dev d, int level) {
           if (warp == 0) {
             qw_apply(slab, Rg, ldg, sC, Tm, sYw, LP, j0, j0 + 8, crk, crt, g, tg);
             mbar_wait(&s_slab[cur ^ 1], su[cur ^ 1] & 1u);
-            qw_panel<RPL>(sSlab + (size_t)(cur ^ 1) * 8 * LP, Rg, ldg, sC, sTm + (cur ^ 1) * 8 * QW_LDL, LP, j0 + 8, min(8, na - j0 - 8), pb + 2 < nct, lane);
+            qw_panel_rows(RPL, sSlab + (size_t)(cur ^ 1) * 8 * LP, Rg, ldg, sC, sTm + (cur ^ 1) * 8 * QW_LDL, LP, j0 + 8, min(8, na - j0 - 8), pb + 2 < nct, lane);
           } else {
             for (int ct = pb + 2 + (warp - 1); ct < nct; ct += QW_T / 32 - 1) qw_apply(slab, Rg, ldg, sC, Tm, sYw, LP, j0, 8 * ct, crk, crt, g, tg);
           }
@@ -332,31 +349,21 @@ __global__ void __launch_bounds__(QW_T) k_qr_wide_finish(Dev d) {
   }
 }
 
-template <int RPL>
-static void launch_qw(const Dev& d, cudaStream_t st) {
-  static DevOnce once;     // function attributes are per device
-  once.run([&] { cudaFuncSetAttribute(k_qr_wide<RPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024); });
-  const int sms = sm_count();
-  const size_t sm = qw_smem_bytes(d.qr_capcols, 32 * RPL);
-  const int grid = (int)std::min<long long>((long long)d.F * d.qr_leaf_cap, 2LL * sms);
-  for (int level = -1; level < d.qr_levels; ++level)
-    KLAUNCH(d, KID_QR_WIDE, st, (k_qr_wide<RPL><<<grid, QW_T, sm, st>>>(d, level)));
-  KLAUNCH(d, KID_QR_WIDE, st, (k_qr_wide_finish<<<std::min(d.F, 2 * sms), QW_T, 0, st>>>(d)));
-}
-
-int qr_wide_rows_per_chunk(int Nmax) {
-  const int capmax = qw_cap(6 * Nmax);
-  for (int rpl = 4; rpl >= 1; rpl >>= 1)
-    if (qw_smem_bytes(capmax, 32 * rpl) <= 226 * 1024) return 32 * rpl;
-  return 0;
+int qr_wide_rows_per_chunk(int Nmax) {                // of the widest possible stack; narrower stacks get taller chunks
+  return qw_chunk_rows(qw_cap(6 * Nmax), 226 * 1024);
 }
 int qr_wide_leaf_rows(int m, int leaf_cap, int CR) { return qw_rows_per_leaf(m, leaf_cap, CR); }
 
 void launch_qr_wide(const Dev& d, cudaStream_t st) {
-  const int cr = qr_wide_rows_per_chunk(d.Nmax);
-  if (cr == 128) launch_qw<4>(d, st);
-  else if (cr == 64) launch_qw<2>(d, st);
-  else launch_qw<1>(d, st);
+  static DevOnce once;     // function attributes are per device
+  once.run([&] { cudaFuncSetAttribute(k_qr_wide, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024); });
+  const int sms = sm_count();
+  // a 128-row chunk of the widest stack if that fits, else everything the SM has: every stack then sizes its own chunk
+  const size_t sm = std::min<size_t>(qw_smem_bytes(d.qr_capcols, 128), 226 * 1024);
+  const int grid = (int)std::min<long long>((long long)d.F * d.qr_leaf_cap, 2LL * sms);
+  for (int level = -1; level < d.qr_levels; ++level)
+    KLAUNCH(d, KID_QR_WIDE, st, (k_qr_wide<<<grid, QW_T, sm, st>>>(d, level, (unsigned)sm)));
+  KLAUNCH(d, KID_QR_WIDE, st, (k_qr_wide_finish<<<std::min(d.F, 2 * sms), QW_T, 0, st>>>(d)));
 }
 
 }  // namespace msckf

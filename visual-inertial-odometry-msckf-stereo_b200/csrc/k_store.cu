@@ -110,10 +110,11 @@ __global__ void __launch_bounds__(ST) k_observe(Dev d, const int* __restrict__ f
       while (true) {
         const long long k = hk[h];
         if (k == EMPTY_KEY) break;
-        if (k == key) { slot = hv[h]; break; }
+        if (k == key) { slot = hv[h]; break; }     // (-2: the id was new earlier in this message -> reported below)
         h = (h + 1) & hmask;
       }
     }
+    if (slot == -2) { atomicOr(d.err, ERRBIT_DUP_ID); slot = -1; }
     const int isnew = valid && slot < 0;
     int total;
     const int rank = block_rank(isnew, s_warp, total);
@@ -130,6 +131,15 @@ __global__ void __launch_bounds__(ST) k_observe(Dev d, const int* __restrict__ f
         d.f_pos[fs * 3 + 0] = 0; d.f_pos[fs * 3 + 1] = 0; d.f_pos[fs * 3 + 2] = 0;
         ord[n0 + idx] = slot;
       }
+      // the new id joins the frame's table (value -2: "new in this message"): a second occurrence of the same id, which
+      // also found no live landmark, meets it here and is reported (the message contract requires unique ids)
+      unsigned h = hash64(key) & hmask;
+      while (true) {
+        const unsigned long long old = atomicCAS((unsigned long long*)&hk[h], (unsigned long long)EMPTY_KEY, (unsigned long long)key);
+        if (old == (unsigned long long)EMPTY_KEY) { hv[h] = -2; break; }
+        if (old == (unsigned long long)key) { atomicOr(d.err, ERRBIT_DUP_ID); break; }
+        h = (h + 1) & hmask;
+      }
     } else if (valid) {
       d.f_mask[(size_t)f * d.Fcap + slot] |= bit;
       atomicAdd(&s_tracked, 1);
@@ -140,6 +150,7 @@ __global__ void __launch_bounds__(ST) k_observe(Dev d, const int* __restrict__ f
       o[0] = z[0]; o[1] = z[1]; o[2] = z[2]; o[3] = z[3];
     }
     base_new += total;
+    __syncthreads();                                  // this tile's insertions are complete before the next tile looks ids up
   }
   __syncthreads();
   if (tid == 0) {

@@ -122,6 +122,7 @@ void launch_jacobian_gate(const Dev& d, int class_mask, int with_big, int write_
 int sm_count();
 void launch_jacobian_rows(const Dev& d, int cls, int write_all, cudaStream_t st);   // k_jacobian_rows.cu (lane-per-row kernel, short tracks)
 void launch_cam_prepare(const Dev& d, cudaStream_t st);
+void launch_gate_lu(const Dev& d, cudaStream_t st);
 void launch_measurement_jacobian(const Dev& d, int filter, int cam_logical, int slot, double* out /*[4*6+4*3+4]*/, cudaStream_t st);
 void launch_export_item_dense(const Dev& d, int filter, double* H, double* r, int n_state, cudaStream_t st);
 void launch_gate_dense(const Dev& d, int filter, const double* H, const double* r, int m, int n_state, int dof,

@@ -28,9 +28,10 @@ constexpr unsigned ERRBIT_POOL = 2u;
 constexpr unsigned ERRBIT_ROWS = 4u;
 constexpr unsigned ERRBIT_NOT_SPD = 8u;
 constexpr unsigned ERRBIT_CAM_CAP = 16u;
+constexpr unsigned ERRBIT_DUP_ID = 32u;     // a feature id occurs twice in one message
 
 // per-stage device counters (one memset per stage): pool bump pointer and work-list lengths
-constexpr int SC_POOL = 0, SC_NTRI = 1, SC_NJAC_BIG = 2, SC_NUPD_BIG = 3, SC_NJAC_SMALL = 4 /* .. 7: one per size class */, SC_NQR = 12 /* .. 16: tensor-pipe QR classes */, SC_NUPD_DMMA = 17 /* .. 21: tensor-pipe update classes */, SC_NQR_BUILD = 22 /* wide / uncompressed stacks (k_qr_build) */, SC_NQR_TALL = 23 /* pruning stacks (k_qr_tall) */, SC_NJAC_BIG2 = 24 /* tracks longer than JAC_BIG_SPLIT_M */, SC_COUNT = 26;
+constexpr int SC_POOL = 0, SC_NTRI = 1, SC_NJAC_BIG = 2, SC_NUPD_BIG = 3, SC_NJAC_SMALL = 4 /* .. 7: one per size class */, SC_NQR = 12 /* .. 16: tensor-pipe QR classes */, SC_NUPD_DMMA = 17 /* .. 21: tensor-pipe update classes */, SC_NQR_BUILD = 22 /* wide / uncompressed stacks (k_qr_build) */, SC_NQR_TALL = 23 /* pruning stacks (k_qr_tall) */, SC_NJAC_BIG2 = 24 /* tracks longer than JAC_BIG_SPLIT_M */, SC_NLU = 25 /* gates to be redone with an LU solve */, SC_COUNT = 26;
 // stacked-Jacobian compression classes: 0..3 = compressed (m > n_a) with n_a + 1 <= 16 / 32 / 48 / 64 columns (k_qr_dmma), 4 = general CTA kernel
 constexpr int QR_DMMA_CLASSES = 5;
 // one-CTA tensor-pipe update classes, aligned with the compression classes: max(k, n_a) + 1 <= 16 / 32 / 48 / 64
@@ -117,6 +118,9 @@ struct Dev {
   int2* wl_jac_small;      // [JAC_CLASSES][F*Fcap] (filter, item) pairs, M <= JAC_SMALL_M, binned by size class
   int2* wl_jac_big;        // [F*Fcap] (filter, item) pairs, tracks of JAC_SMALL_M < M <= JAC_BIG_SPLIT_M observations
   int2* wl_jac_big2;       // [F*Fcap] (filter, item) pairs, longer tracks
+  int2* wl_lu;             // [F*Fcap] (filter, item) pairs whose innovation covariance was not positive definite to rounding: the
+                           // gate is redone with an LU solve as in the reference (msckf.py:609)
+  double* lu_scratch;      // T1 | S | y | x of one such landmark
   double* jac_scratch;     // innovation covariance of tracks too long for shared memory, per CTA of the long-track kernel
   long long jac_scratch_stride;
   int jac_big_smem_doubles, jac_big_grid;
@@ -173,6 +177,11 @@ __host__ __device__ inline int Tld(const Dev& d) { return d.ld + 8; }
 // Pool record of a landmark that passed the gate: its projected Jacobian rows, row-major [4M-3][6M+1]
 // (six columns per observation in logical camera order, last column = projected residual).
 __host__ __device__ inline long long jac_record_doubles(int M) { return (long long)(4 * M - 3) * (6 * M + 1); }
+
+// A gate whose Cholesky factorisation met a non-positive pivot is queued for k_gate_lu
+__device__ __forceinline__ void queue_gate_lu(int2* wl_lu, unsigned long long* stage_ctr, int f, int k) {
+  wl_lu[atomicAdd(stage_ctr + SC_NLU, 1ull)] = make_int2(f, k);
+}
 
 // records where the first non-positive-definite innovation covariance was met (where: 1 gate, 2 dense gate, 3 tiled update,
 // 4 fused update), then raises the error bit

@@ -330,13 +330,13 @@ def test_remove_lost_features_vs_oracle(units, dev):
 
 def test_gate_with_indefinite_innovation_covariance_uses_lu(units, dev):
     """gating_test as the reference writes it (msckf.py:606-614) solves with LU, which also answers when H P H^T + sigma^2 I
-    is not positive definite.  With P replaced by -P on both sides every gate of the mid-stream state is indefinite: the
+    is not positive definite.  With P replaced by -1e4 P on both sides every gate of the mid-stream state is indefinite: the
     device's Cholesky gate must hand those landmarks to its LU kernel and arrive at the reference's gamma and decision.
     (The update that follows is a different matter: its indefinite S is an error by design, like a LinAlgError.)"""
     from msckf_b200 import capi
     u = units
     of = oracle_filter_from_units(u)
-    Pneg = -np.array(of.state_server._vio_state_cov__)
+    Pneg = -1e4 * np.array(of.state_server._vio_state_cov__)      # H P H^T far below -sigma^2 in some directions
     of.state_server._vio_state_cov__ = Pneg.copy()
     dev.ctx.set_cov(0, Pneg)
     of.log = {}
@@ -349,7 +349,7 @@ def test_gate_with_indefinite_innovation_covariance_uses_lu(units, dev):
     st = log['status']
     gates = of.log.get('gate', [])
     sel = [i for i, s in enumerate(st) if s in (capi.FEAT_GATE_PASS, capi.FEAT_GATE_FAIL)]
-    assert len(sel) == len(gates) and len(gates) >= 10
+    assert len(sel) == len(gates) and len(gates) >= 5
     gam = log['gamma'][sel]
     ref = np.array([g[0] for g in gates])
     assert np.all(np.isfinite(gam))

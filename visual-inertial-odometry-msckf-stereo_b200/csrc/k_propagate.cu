@@ -27,6 +27,14 @@ __device__ __forceinline__ void quat_step_coeffs(double dt, const double* gyro, 
     out[3] = c2 * (dt * 0.25);
   }
 }
+// 1 / |q| through one reciprocal square root (MUFU.RSQ64H + Newton) instead of a square root and a divide: the
+// normalisations sit on the sequential part of the RK4 chain.  Differs from sqrt-then-divide by at most an ulp.
+__device__ __forceinline__ double rnorm4(const double* q) { return rsqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]); }
+__device__ __forceinline__ void to_rotation_rs(const double* q_in, double* R) {       // utils.py:14-27
+  const double rn = rnorm4(q_in);
+  const double q[4] = {q_in[0] * rn, q_in[1] * rn, q_in[2] * rn, q_in[3] * rn};
+  rot_from_parts(q, q[3], q, R);
+}
 __device__ void predict_new_state(double dt, const double* gyro, const double* acc, const double* cf, const double* g,
                                   double* q, double* v, double* p) {
   const double Om[16] = {0, gyro[2], -gyro[1], gyro[0],
@@ -42,15 +50,15 @@ __device__ void predict_new_state(double dt, const double* gyro, const double* a
     dq[i] = cf[0] * q[i] + cf[1] * oq;
     dq2[i] = cf[2] * q[i] + cf[3] * oq;
   }
-  double n = 1.0 / norm4(dq);
+  double n = rnorm4(dq);
   for (int i = 0; i < 4; ++i) dq[i] *= n;
   const double stale[3] = {dq[0], dq[1], dq[2]};
   double RdT[9], Rd2T[9], R[9];
   rot_from_parts(dq, dq[3], stale, RdT);            // dR_dt (transposed when applied)
-  n = 1.0 / norm4(dq2);
+  n = rnorm4(dq2);
   for (int i = 0; i < 4; ++i) dq2[i] *= n;
   rot_from_parts(dq2, dq2[3], stale, Rd2T);
-  n = 1.0 / norm4(q);
+  n = rnorm4(q);
   const double qn[4] = {q[0] * n, q[1] * n, q[2] * n, q[3] * n};
   rot_from_parts(qn, qn[3], stale, R);
 
@@ -69,7 +77,7 @@ __device__ void predict_new_state(double dt, const double* gyro, const double* a
     k3p[i] = v[i] + k2v[i] * dt / 2;
     k4p[i] = v[i] + k2v[i] * dt;
   }
-  n = 1.0 / norm4(dq);
+  n = rnorm4(dq);
   for (int i = 0; i < 4; ++i) q[i] = dq[i] * n;
   for (int i = 0; i < 3; ++i) {
     const double vi = v[i];
@@ -107,7 +115,7 @@ __device__ void build_phi(const double* x0, const double* x1, const double* qn, 
   const double* w = smp + 1;
   const double* a = smp + 4;
   double R[9], Sa[9], A00[9], A20[9], A23[9], RtS[9], Sw[9];
-  to_rotation(x0, R);
+  to_rotation_rs(x0, R);
   skew3(a, Sa);
   mat3_mul_tn(R, Sa, RtS);
   skew3(w, Sw);
@@ -118,6 +126,7 @@ __device__ void build_phi(const double* x0, const double* x1, const double* qn, 
       A23[3 * i + j] = -R[3 * j + i] * dt;
     }
   const double mdt = -1.0 * dt, pdt = 1.0 * dt;
+  constexpr double i6 = 1.0 / 6.0;            // the reference divides by 6 (jit_utils.py:41); a product differs by at most an ulp
   // (F dt)^2 and (F dt)^3, block by block (the skipped terms of the dense products are exact zeros)
   double B00[9], B20[9], C00[9], C20[9], C40[9], P00[9], P20[9], P40[9];
   mat3_mul(A00, A00, B00);                                   // sq[0,0] = A00 A00
@@ -131,13 +140,13 @@ __device__ void build_phi(const double* x0, const double* x1, const double* qn, 
     for (int j = 0; j < 3; ++j) {
       const int e = 3 * i + j;
       const double I = (i == j) ? 1.0 : 0.0;
-      P00[e] = (I + A00[e]) + B00[e] / 2. + C00[e] / 6.;
-      out[9 + e] = (0.0 + I * mdt) + (A00[e] * mdt) / 2. + (B00[e] * mdt) / 6.;     // Phi01
-      P20[e] = (0.0 + A20[e]) + B20[e] / 2. + C20[e] / 6.;
-      out[27 + e] = (A20[e] * mdt) / 2. + (B20[e] * mdt) / 6.;                       // Phi21
+      P00[e] = (I + A00[e]) + B00[e] / 2. + C00[e] * i6;
+      out[9 + e] = (0.0 + I * mdt) + (A00[e] * mdt) / 2. + (B00[e] * mdt) * i6;     // Phi01
+      P20[e] = (0.0 + A20[e]) + B20[e] / 2. + C20[e] * i6;
+      out[27 + e] = (A20[e] * mdt) / 2. + (B20[e] * mdt) * i6;                       // Phi21
       out[36 + e] = A23[e];                                                            // Phi23
-      P40[e] = B40[e] / 2. + C40[e] / 6.;
-      out[54 + e] = (B40[e] * mdt) / 6.;                                               // Phi41
+      P40[e] = B40[e] / 2. + C40[e] * i6;
+      out[54 + e] = (B40[e] * mdt) * i6;                                               // Phi41
       out[63 + e] = (pdt * A23[e]) / 2.;                                               // Phi43
     }
   out[72] = dt;
@@ -153,13 +162,14 @@ __device__ void build_phi(const double* x0, const double* x1, const double* qn, 
   }
   // observability-constrained blocks (msckf.py:328-344)
   double Rk[9], Rn[9];
-  to_rotation(qn, Rk);
-  to_rotation(x1, Rn);
+  to_rotation_rs(qn, Rk);
+  to_rotation_rs(x1, Rn);
   mat3_mul_nt(Rn, Rk, P00);
   double u[3], sv[3];
   mat3_vec(Rk, g, u);
   const double uu = u[0] * u[0] + u[1] * u[1] + u[2] * u[2];
-  for (int i = 0; i < 3; ++i) sv[i] = u[i] / uu;
+  const double iuu = 1.0 / uu;
+  for (int i = 0; i < 3; ++i) sv[i] = u[i] * iuu;
   double dv[3], dp[3], w1[3], w2[3];
   for (int i = 0; i < 3; ++i) {
     dv[i] = vn[i] - x1[4 + i];

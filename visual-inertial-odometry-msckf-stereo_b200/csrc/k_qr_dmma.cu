@@ -17,6 +17,7 @@
 #include <algorithm>
 #include "msckf_dev.cuh"
 #include "kernels.h"
+#include "qr_panel.cuh"
 
 namespace msckf {
 
@@ -40,104 +41,10 @@ size_t qr_dmma_smem_bytes(int cap) {
   return dbl * sizeof(double) + 64 * sizeof(int) + 16;
 }
 
-// Panel factorisation by one warp.  x[t][c] = C(lane + 32 t, j0 + c); reflector jj is applied to the panel columns
-// c > jj only (the other tiles get the blocked update).  Returns V in x, writes R(j0 + jj, j0 + jj ..) and T.
+// Panel factorisation by one warp (qr_panel.cuh): the diagonal block of R is read and written in place.
 __device__ __forceinline__ void qd_panel(double* sR, double* sC, double* sTm, int ldr, int j0, int nrefl, bool need_T, int lane) {
-  double x[4][8];
-#pragma unroll
-  for (int t = 0; t < 4; ++t) {
-    const double* row = sC + (lane + 32 * t) * ldr + j0;
-#pragma unroll
-    for (int c = 0; c < 8; c += 2) {
-      const double2 v = *(const double2*)(row + c);
-      x[t][c] = v.x;
-      x[t][c + 1] = v.y;
-    }
-  }
-  double tau[8];
-#pragma unroll
-  for (int jj = 0; jj < 8; ++jj) {
-    tau[jj] = 0.0;
-    if (jj < nrefl) {                                     // warp-uniform
-      double s[8];
-#pragma unroll
-      for (int c = jj; c < 8; ++c) {
-        double a = 0.0;
-#pragma unroll
-        for (int t = 0; t < 4; ++t) a += x[t][jj] * x[t][c];
-        s[c] = a;
-      }
-      double rrow[8];
-#pragma unroll
-      for (int c = jj; c < 8; ++c) rrow[c] = sR[(j0 + jj) * ldr + j0 + c];
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-        for (int c = jj; c < 8; ++c) s[c] += __shfl_xor_sync(QFULL, s[c], o);
-      }
-      if (s[jj] != 0.0) {
-        const double alpha = rrow[jj];
-        const double n2 = alpha * alpha + s[jj];
-        const double rn = rsqrt(n2);                       // 1 / |beta|: one reciprocal square root instead of a square root and a divide
-        const double nrm = n2 * rn;
-        const double beta = (alpha >= 0) ? -nrm : nrm;
-        const double tj = (beta - alpha) * ((alpha >= 0) ? -rn : rn), sc = 1.0 / (alpha - beta);
-        tau[jj] = tj;
-#pragma unroll
-        for (int t = 0; t < 4; ++t) x[t][jj] *= sc;
-#pragma unroll
-        for (int c = jj + 1; c < 8; ++c) {
-          const double w = tj * (rrow[c] + s[c] * sc);
-          if (lane == 0) sR[(j0 + jj) * ldr + j0 + c] = rrow[c] - w;
-#pragma unroll
-          for (int t = 0; t < 4; ++t) x[t][c] -= w * x[t][jj];
-        }
-        if (lane == 0) sR[(j0 + jj) * ldr + j0 + jj] = beta;
-      }
-    } else {
-      // not a reflector column (residual / padding): it carries data of the last panel, which has no trailing tiles
-    }
-  }
-  if (!need_T) return;       // last panel of the chunk: nothing reads V, T or the chunk again
-  // V back to the chunk (only the reflector columns changed meaning; the others hold the updated data)
-#pragma unroll
-  for (int t = 0; t < 4; ++t) {
-    double* row = sC + (lane + 32 * t) * ldr + j0;
-#pragma unroll
-    for (int c = 0; c < 8; c += 2) *(double2*)(row + c) = make_double2(x[t][c], x[t][c + 1]);
-  }
-  // T (8 x 8 upper): T(i,i) = tau_i, T(i,j) = -tau_j sum_{l=i}^{j-1} T(i,l) (v_l . v_j); lane i < 8 owns row i.
-  // All 28 dot products of V^T V go through one batched warp reduction.
-  double gm[8][8];
-#pragma unroll
-  for (int j = 1; j < 8; ++j)
-#pragma unroll
-    for (int l = 0; l < j; ++l) {
-      double a = 0.0;
-#pragma unroll
-      for (int t = 0; t < 4; ++t) a += x[t][l] * x[t][j];
-      gm[l][j] = a;
-    }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-    for (int j = 1; j < 8; ++j)
-#pragma unroll
-      for (int l = 0; l < j; ++l) gm[l][j] += __shfl_xor_sync(QFULL, gm[l][j], o);
-  }
-  double trow[8];
-  const int ri = lane & 7;
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    double acc = 0.0;
-#pragma unroll
-    for (int l = 0; l < j; ++l) acc += trow[l] * gm[l][j];
-    trow[j] = (ri == j) ? tau[j] : ((ri < j) ? -tau[j] * acc : 0.0);
-  }
-  if (lane < 8) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) sTm[ri * QD_LDL + j] = trow[j];
-  }
+  double* Rd = sR + j0 * ldr + j0;
+  qr_panel<4>(Rd, ldr, Rd, ldr, sC + j0, ldr, sTm, QD_LDL, nrefl, need_T, lane);
 }
 
 // Applies the block reflector of panel j0 (V in the chunk, T in sTm) to the 8-column tile at c0 (R rows and chunk columns).

@@ -12,6 +12,7 @@
 #include <algorithm>
 #include "msckf_dev.cuh"
 #include "kernels.h"
+#include "warp_reduce.cuh"
 
 namespace msckf {
 
@@ -24,22 +25,32 @@ constexpr unsigned TQ_FULL = 0xffffffffu;
 __device__ __forceinline__ void tq_fold(double (&x)[4][TQ_NC], double* R, int lane) {
 #pragma unroll
   for (int jj = 0; jj < TQ_NC - 1; ++jj) {
-    double s[TQ_NC];
+    // dots of column jj with itself and the columns right of it, compacted to s[0 .. 13 - jj): folded warp reductions
+    // for the wide ones (warp_reduce.cuh), a plain butterfly once only a few values are left
+    double s[16];
 #pragma unroll
-    for (int c = jj; c < TQ_NC; ++c) {
+    for (int c = 0; c < 16; ++c) {
       double a = 0.0;
+      if (c + jj < TQ_NC) {
 #pragma unroll
-      for (int t = 0; t < 4; ++t) a += x[t][jj] * x[t][c];
+        for (int t = 0; t < 4; ++t) a += x[t][jj] * x[t][c + jj];
+      }
       s[c] = a;
     }
+    if (TQ_NC - jj > 8) {
+      warp_allsum16(s, TQ_NC - jj, lane);
+    } else if (TQ_NC - jj > 4) {
+      warp_allsum8(s, lane);
+    } else {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
+      for (int o = 16; o > 0; o >>= 1) {
 #pragma unroll
-      for (int c = jj; c < TQ_NC; ++c) s[c] += __shfl_xor_sync(TQ_FULL, s[c], o);
+        for (int c = 0; c < TQ_NC - jj; ++c) s[c] += __shfl_xor_sync(TQ_FULL, s[c], o);
+      }
     }
-    if (s[jj] != 0.0) {                                    // warp-uniform (the butterfly leaves identical sums in every lane)
+    if (s[0] != 0.0) {                                     // warp-uniform (the reduction leaves identical sums in every lane)
       const double alpha = R[jj * TQ_LDR + jj];
-      const double n2 = alpha * alpha + s[jj];
+      const double n2 = alpha * alpha + s[0];
       const double rn = rsqrt(n2);                         // 1 / |beta|: one reciprocal square root instead of a square root and a divide
       const double nrm = n2 * rn;
       const double beta = (alpha >= 0) ? -nrm : nrm;
@@ -49,7 +60,7 @@ __device__ __forceinline__ void tq_fold(double (&x)[4][TQ_NC], double* R, int la
 #pragma unroll
       for (int c = jj + 1; c < TQ_NC; ++c) {
         const double rjc = R[jj * TQ_LDR + c];
-        const double w = tj * (rjc + s[c] * sc);
+        const double w = tj * (rjc + s[c - jj] * sc);
         if (lane == 0) R[jj * TQ_LDR + c] = rjc - w;
 #pragma unroll
         for (int t = 0; t < 4; ++t) x[t][c] -= w * x[t][jj];

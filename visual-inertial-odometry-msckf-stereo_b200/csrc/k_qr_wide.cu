@@ -11,7 +11,7 @@
 //   finish   k_qr_wide_finish: H_thin = R of node 0, r_thin = its last column, into the filter's compressed slot.
 //
 // The running factor R does not fit shared memory next to a chunk (185 x 185 doubles at a 30-state window, 393 x 393 at
-// 64), so it lives in L2 / HBM and only the 8-row slab a panel step touches is resident: slab p+1 is fetched by the TMA
+// 64), so it lives in L2 / HBM and only the 8-row slab a panel step touches is resident: slabs p+1 and p+2 are fetched by the TMA
 // engine (cp.async.bulk + mbarrier, two buffers) while panel p is applied, updated R tiles go straight back to global.
 // Look-ahead: the warp that factors panels first applies panel p to the columns of panel p+1 and factors it while the
 // other warps finish the trailing tiles of panel p -- one CTA barrier per panel and no warp waits for the factorisation.
@@ -20,12 +20,14 @@
 #include "msckf_dev.cuh"
 #include "kernels.h"
 #include "tma.cuh"
+#include "qr_panel.cuh"
 
 namespace msckf {
 
 constexpr int QW_T = 256;
 constexpr int QW_LDL = 12;         // leading dimension of T and of the per-warp W / Y staging tiles
 constexpr unsigned QWFULL = 0xffffffffu;
+constexpr int QW_NSLAB = 3;       // slabs of R in flight: the one being applied, the one the look-ahead panel needs, one more on its way
 
 __host__ __device__ inline int qw_cap(int na) { return (na + 1 + 7) & ~7; }          // columns of [H | r], padded to 8
 // leaves of a stack of m rows: pieces of at least 512 rows, at most leaf_cap of them
@@ -38,7 +40,7 @@ __host__ __device__ inline int qw_rows_per_leaf(int m, int leaf_cap, int CR) {
 
 __host__ __device__ inline size_t qw_smem_bytes(int cap, int CR) {
   const size_t LP = cap + 4;
-  return ((size_t)CR * LP + 2 * 8 * LP + 2 * 8 * QW_LDL + 8 * 8 * QW_LDL) * sizeof(double) + 64 * sizeof(int) + 64;
+  return ((size_t)CR * LP + QW_NSLAB * 8 * LP + 2 * 8 * QW_LDL + 8 * 8 * QW_LDL) * sizeof(double) + 64 * sizeof(int) + 64;
 }
 // rows per chunk of a stack with `cap` columns: as many as the shared memory of the launch holds next to the slabs
 // (128, 64 or 32: the panel warp keeps 4, 2 or 1 rows per lane)
@@ -48,103 +50,12 @@ __host__ __device__ inline int qw_chunk_rows(int cap, size_t smem_bytes) {
   return 32;
 }
 
-// Panel factorisation by one warp.  x[t][c] = C(lane + 32 t, j0 + c).  The 8 x 8 diagonal block of R comes from the
-// shared-memory slab (row jj of the slab = row j0 + jj of R), its new values go to global memory.  V replaces the
-// panel columns of the chunk, T goes to sTm.
+// Panel factorisation by one warp (qr_panel.cuh).  The 8 x 8 diagonal block of R comes from the shared-memory slab (row jj
+// of the slab = row j0 + jj of R), its new values go to global memory.  V replaces the panel columns of the chunk.
 template <int RPL>
 __device__ __forceinline__ void qw_panel(const double* slab, double* Rg, int ldg, double* sC, double* sTm, int LP, int j0, int nrefl,
                                          bool need_T, int lane) {
-  double x[RPL][8];
-#pragma unroll
-  for (int t = 0; t < RPL; ++t) {
-    const double* row = sC + (size_t)(lane + 32 * t) * LP + j0;
-#pragma unroll
-    for (int c = 0; c < 8; c += 2) {
-      const double2 v = *(const double2*)(row + c);
-      x[t][c] = v.x;
-      x[t][c + 1] = v.y;
-    }
-  }
-  double tau[8];
-#pragma unroll
-  for (int jj = 0; jj < 8; ++jj) {
-    tau[jj] = 0.0;
-    if (jj < nrefl) {                                     // warp-uniform
-      double s[8];
-#pragma unroll
-      for (int c = jj; c < 8; ++c) {
-        double a = 0.0;
-#pragma unroll
-        for (int t = 0; t < RPL; ++t) a += x[t][jj] * x[t][c];
-        s[c] = a;
-      }
-      double rrow[8];
-#pragma unroll
-      for (int c = jj; c < 8; ++c) rrow[c] = slab[jj * LP + j0 + c];
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-        for (int c = jj; c < 8; ++c) s[c] += __shfl_xor_sync(QWFULL, s[c], o);
-      }
-      if (s[jj] != 0.0) {
-        const double alpha = rrow[jj];
-        const double n2 = alpha * alpha + s[jj];
-        const double rn = rsqrt(n2);                       // 1 / |beta|
-        const double nrm = n2 * rn;
-        const double beta = (alpha >= 0) ? -nrm : nrm;
-        const double tj = (beta - alpha) * ((alpha >= 0) ? -rn : rn), sc = 1.0 / (alpha - beta);
-        tau[jj] = tj;
-#pragma unroll
-        for (int t = 0; t < RPL; ++t) x[t][jj] *= sc;
-#pragma unroll
-        for (int c = jj + 1; c < 8; ++c) {
-          const double w = tj * (rrow[c] + s[c] * sc);
-          if (lane == 0) Rg[(size_t)(j0 + jj) * ldg + j0 + c] = rrow[c] - w;
-#pragma unroll
-          for (int t = 0; t < RPL; ++t) x[t][c] -= w * x[t][jj];
-        }
-        if (lane == 0) Rg[(size_t)(j0 + jj) * ldg + j0 + jj] = beta;
-      }
-    }
-  }
-  if (!need_T) return;
-#pragma unroll
-  for (int t = 0; t < RPL; ++t) {
-    double* row = sC + (size_t)(lane + 32 * t) * LP + j0;
-#pragma unroll
-    for (int c = 0; c < 8; c += 2) *(double2*)(row + c) = make_double2(x[t][c], x[t][c + 1]);
-  }
-  // T (8 x 8 upper): T(i,i) = tau_i, T(i,j) = -tau_j sum_{l=i}^{j-1} T(i,l) (v_l . v_j); lane i < 8 owns row i
-  double gm[8][8];
-#pragma unroll
-  for (int j = 1; j < 8; ++j)
-#pragma unroll
-    for (int l = 0; l < j; ++l) {
-      double a = 0.0;
-#pragma unroll
-      for (int t = 0; t < RPL; ++t) a += x[t][l] * x[t][j];
-      gm[l][j] = a;
-    }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-    for (int j = 1; j < 8; ++j)
-#pragma unroll
-      for (int l = 0; l < j; ++l) gm[l][j] += __shfl_xor_sync(QWFULL, gm[l][j], o);
-  }
-  double trow[8];
-  const int ri = lane & 7;
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    double acc = 0.0;
-#pragma unroll
-    for (int l = 0; l < j; ++l) acc += trow[l] * gm[l][j];
-    trow[j] = (ri == j) ? tau[j] : ((ri < j) ? -tau[j] * acc : 0.0);
-  }
-  if (lane < 8) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) sTm[ri * QW_LDL + j] = trow[j];
-  }
+  qr_panel<RPL>(slab + j0, LP, Rg + (size_t)j0 * ldg + j0, ldg, sC + j0, LP, sTm, QW_LDL, nrefl, need_T, lane);
 }
 
 // Applies the block reflector of panel j0 (V in the chunk, T in sTm) to the 8-column tile at c0: R rows from the slab,
@@ -198,18 +109,17 @@ __device__ __forceinline__ void qw_panel_rows(int rpl, const double* slab, doubl
 
 __global__ void __launch_bounds__(QW_T, 1) k_qr_wide(Dev d, int level, unsigned smem_bytes) {
   extern __shared__ __align__(128) double qs[];
-  __shared__ uint64_t s_slab[2], s_rows;
+  __shared__ uint64_t s_slab[QW_NSLAB], s_rows;
   __shared__ int s_c0;
   const int ldg = d.qr_capcols;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, tg = lane & 3;
   if (tid == 0) {
-    mbar_init(&s_slab[0], 1);
-    mbar_init(&s_slab[1], 1);
+    for (int b = 0; b < QW_NSLAB; ++b) mbar_init(&s_slab[b], 1);
     mbar_init(&s_rows, 1);
     fence_mbar_init();
   }
   __syncthreads();
-  unsigned su[2] = {0u, 0u}, srows = 0u;              // completed uses of each barrier (phase parity)
+  unsigned su[QW_NSLAB] = {0u, 0u, 0u}, srows = 0u;   // completed uses of each barrier (phase parity)
   const int nlist = (int)d.stage_ctr[SC_NQR_BUILD];
   const int leaf_cap = d.qr_leaf_cap;
 
@@ -221,8 +131,8 @@ __global__ void __launch_bounds__(QW_T, 1) k_qr_wide(Dev d, int level, unsigned 
     // shared-memory layout of this stack: the chunk is as tall as its own width allows
     const int LP = cap + 4, CR = qw_chunk_rows(cap, smem_bytes), RPL = CR >> 5;
     double* sC = qs;                                    // [CR][LP]   chunk of stacked rows
-    double* sSlab = sC + (size_t)CR * LP;               // [2][8][LP] the 8 rows of R a panel step reads
-    double* sTm = sSlab + 2 * 8 * LP;                   // [2][8][QW_LDL]
+    double* sSlab = sC + (size_t)CR * LP;               // [QW_NSLAB][8][LP] the 8 rows of R a panel step reads
+    double* sTm = sSlab + QW_NSLAB * 8 * LP;            // [2][8][QW_LDL]
     double* sY = sTm + 2 * 8 * QW_LDL;                  // [8 warps][8][QW_LDL]
     int* camcol = (int*)(sY + 8 * 8 * QW_LDL);          // [64] logical camera -> active column block
     double* sYw = sY + warp * 8 * QW_LDL;
@@ -291,40 +201,44 @@ __global__ void __launch_bounds__(QW_T, 1) k_qr_wide(Dev d, int level, unsigned 
         srows += 1;
       }
       auto issue_slab = [&](int pb) {                 // warp 1, lanes 0..7: row i of slab pb, columns 8 pb .. cap
-        const int b = pb & 1;
+        const int b = pb % QW_NSLAB;
         if (lane == 0) mbar_arrive_expect_tx(&s_slab[b], (unsigned)(8 * (cap - 8 * pb) * sizeof(double)));
         __syncwarp();
         if (lane < 8) bulk_g2s(sSlab + (size_t)(b * 8 + lane) * LP + 8 * pb, Rg + (size_t)(8 * pb + lane) * ldg + 8 * pb, (cap - 8 * pb) * sizeof(double), &s_slab[b]);
       };
-      if (warp == 1) issue_slab(pb0);
+      if (warp == 1) {
+        issue_slab(pb0);
+        if (pb0 + 1 < npan) issue_slab(pb0 + 1);
+      }
       if (warp == 0) {
-        mbar_wait(&s_slab[pb0 & 1], su[pb0 & 1] & 1u);
-        qw_panel_rows(RPL, sSlab + (size_t)(pb0 & 1) * 8 * LP, Rg, ldg, sC, sTm + (pb0 & 1) * 8 * QW_LDL, LP, 8 * pb0, min(8, na - 8 * pb0), pb0 + 1 < nct, lane);
+        const int sb = pb0 % QW_NSLAB;
+        mbar_wait(&s_slab[sb], su[sb] & 1u);
+        qw_panel_rows(RPL, sSlab + (size_t)sb * 8 * LP, Rg, ldg, sC, sTm + (pb0 & 1) * 8 * QW_LDL, LP, 8 * pb0, min(8, na - 8 * pb0), pb0 + 1 < nct, lane);
       }
       __syncthreads();
       for (int pb = pb0; pb < npan; ++pb) {
-        const int cur = pb & 1, j0 = 8 * pb;
+        const int cur = pb & 1, j0 = 8 * pb, sb = pb % QW_NSLAB, sbn = (pb + 1) % QW_NSLAB;
         // rows of the chunk that can be non-zero in this panel: all of them for stacked landmark rows; a triangular factor
         // being folded (tree levels) has nothing below its diagonal, so row r0 + i only matters once 8 pb + 7 >= r0 + i
         const int rows_nz = level < 0 ? cr : min(cr, j0 + 8 - r0);
         const int crk = (rows_nz + 3) >> 2, crt = (rows_nz + 7) >> 3;
-        const double* slab = sSlab + (size_t)cur * 8 * LP;
+        const double* slab = sSlab + (size_t)sb * 8 * LP;
         const double* Tm = sTm + cur * 8 * QW_LDL;
         const bool ahead = pb + 1 < npan;             // another panel follows: warp 0 looks ahead
-        if (ahead && warp == 1) issue_slab(pb + 1);
-        mbar_wait(&s_slab[cur], su[cur] & 1u);        // (already complete for warp 0)
+        if (warp == 1 && pb + 2 < npan) issue_slab(pb + 2);   // two slabs ahead: the look-ahead panel never waits for its slab
+        mbar_wait(&s_slab[sb], su[sb] & 1u);          // (already complete for warp 0)
         if (ahead) {
           if (warp == 0) {
             qw_apply(slab, Rg, ldg, sC, Tm, sYw, LP, j0, j0 + 8, crk, crt, g, tg);
-            mbar_wait(&s_slab[cur ^ 1], su[cur ^ 1] & 1u);
-            qw_panel_rows(RPL, sSlab + (size_t)(cur ^ 1) * 8 * LP, Rg, ldg, sC, sTm + (cur ^ 1) * 8 * QW_LDL, LP, j0 + 8, min(8, na - j0 - 8), pb + 2 < nct, lane);
+            mbar_wait(&s_slab[sbn], su[sbn] & 1u);
+            qw_panel_rows(RPL, sSlab + (size_t)sbn * 8 * LP, Rg, ldg, sC, sTm + (cur ^ 1) * 8 * QW_LDL, LP, j0 + 8, min(8, na - j0 - 8), pb + 2 < nct, lane);
           } else {
             for (int ct = pb + 2 + (warp - 1); ct < nct; ct += QW_T / 32 - 1) qw_apply(slab, Rg, ldg, sC, Tm, sYw, LP, j0, 8 * ct, crk, crt, g, tg);
           }
         } else {
           for (int ct = pb + 1 + warp; ct < nct; ct += QW_T / 32) qw_apply(slab, Rg, ldg, sC, Tm, sYw, LP, j0, 8 * ct, crk, crt, g, tg);
         }
-        su[cur] += 1;
+        su[sb] += 1;
         if (pb + 1 == npan) fence_proxy_async();      // R rows written with ordinary stores are read back by the TMA engine
         __syncthreads();
       }

@@ -523,10 +523,21 @@ __global__ void __launch_bounds__(WT) k_upd_inject(Dev d) {
     const int n = NI + 6 * d.ncam[f], tld = Tld(d);
     const double* T = d.T + (size_t)f * d.Tk * tld;
     double* dx = d.dx + (size_t)f * d.nmax;
-    for (int j = tid; j < n; j += WT) {
-      double s = 0;
-      for (int i = 0; i < k; ++i) s += T[(size_t)i * tld + j] * T[(size_t)i * tld + n];
-      dx[j] = s;
+    __shared__ double s_y[NI + 6 * 64 + 8];                 // y = L^-1 r_thin, read by every column
+    __syncthreads();
+    for (int i = tid; i < k; i += WT) s_y[i] = T[(size_t)i * tld + n];
+    __syncthreads();
+    for (int j = tid; j < n; j += WT) {                      // four independent chains: the loads of a column overlap
+      double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+      int i = 0;
+      for (; i + 4 <= k; i += 4) {
+        s0 += T[(size_t)i * tld + j] * s_y[i];
+        s1 += T[(size_t)(i + 1) * tld + j] * s_y[i + 1];
+        s2 += T[(size_t)(i + 2) * tld + j] * s_y[i + 2];
+        s3 += T[(size_t)(i + 3) * tld + j] * s_y[i + 3];
+      }
+      for (; i < k; ++i) s0 += T[(size_t)i * tld + j] * s_y[i];
+      dx[j] = (s0 + s1) + (s2 + s3);
     }
     __syncthreads();
     inject_state(d, f, dx, tid, WT);

@@ -1,14 +1,15 @@
 """Turn the two ncu exports of a round into the committed artefacts under profiles/:
    launch list (gpu__time_duration per launch)  -> per-kernel table (markdown)
    --set full raw page (csv)                    -> condensed per-launch lines + dram bytes per launch per kernel family (json)
-usage: python tools/ncu_profiles.py <launches.csv> <raw.csv> <tag>"""
+usage: python tools/ncu_profiles.py <launches.csv> <raw.csv> <tag> [traffic json name, e.g. traffic_r2.json]"""
 import csv, json, os, re, subprocess, sys
 from collections import defaultdict
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 launches, raw, tag = sys.argv[1:4]
+traffic_name = sys.argv[4] if len(sys.argv) > 4 else None
 
 FAMILY = [('triangulate', r'k_triangulate'), ('jacobian_nullspace_gate', r'k_jacobian'), ('stacked_qr', r'k_qr'),
-          ('gain_update', r'k_upd'), ('propagate', r'k_propagate')]
+          ('gain_update', r'k_upd|k_wupd'), ('propagate', r'k_propagate')]
 
 
 def family(name):
@@ -21,7 +22,7 @@ def family(name):
 def short(name):
     name = re.sub(r'^void ', '', name)
     name = re.sub(r'\(.*$', '', name)
-    return name.replace('msckf::', '')
+    return re.sub(r'\(int\)', '', name.replace('msckf::', ''))
 
 
 rows = [r for r in csv.reader(l for l in open(launches) if l.startswith('"'))]
@@ -61,6 +62,7 @@ for r in data:
 js = {'source': 'ncu --set full --clock-control none, %s (bench.py default workload, 2 frames)' % os.path.basename(raw),
       'dram_bytes_per_launch': dict((f, v[1] / v[0]) for f, v in fam.items()),
       'profiled_launches': dict((f, v[0]) for f, v in fam.items())}
-json.dump(js, open(os.path.join(REPO, 'profiles', 'traffic_r1.json'), 'w'), indent=1)
+if traffic_name:
+    json.dump(js, open(os.path.join(REPO, 'profiles', traffic_name), 'w'), indent=1)
 print('\n'.join(out[:14]))
 print(json.dumps(js, indent=1))

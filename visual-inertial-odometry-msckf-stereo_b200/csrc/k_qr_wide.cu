@@ -17,6 +17,7 @@
 // other warps finish the trailing tiles of panel p -- one CTA barrier per panel and no warp waits for the factorisation.
 // Row signs of R differ from a sequential Householder QR; the update is invariant to them (as in k_qr_tall.cu).
 #include <algorithm>
+#include <cstdlib>
 #include "msckf_dev.cuh"
 #include "kernels.h"
 #include "tma.cuh"
@@ -27,7 +28,7 @@ namespace msckf {
 constexpr int QW_T = 256;
 constexpr int QW_LDL = 12;         // leading dimension of T and of the per-warp W / Y staging tiles
 constexpr unsigned QWFULL = 0xffffffffu;
-constexpr int QW_NSLAB = 3;       // slabs of R in flight: the one being applied, the one the look-ahead panel needs, one more on its way
+constexpr int QW_NSLAB = 3;       // slabs of R in flight at most: the one being applied, the one the look-ahead panel needs, one more on its way
 
 __host__ __device__ inline int qw_cap(int na) { return (na + 1 + 7) & ~7; }          // columns of [H | r], padded to 8
 // leaves of a stack of m rows: pieces of at least 512 rows, at most leaf_cap of them
@@ -52,10 +53,10 @@ __host__ __device__ inline int qw_chunk_rows(int cap, size_t smem_bytes) {
 
 // Panel factorisation by one warp (qr_panel.cuh).  The 8 x 8 diagonal block of R comes from the shared-memory slab (row jj
 // of the slab = row j0 + jj of R), its new values go to global memory.  V replaces the panel columns of the chunk.
-template <int RPL>
+template <int RPL, bool FOLD>
 __device__ __forceinline__ void qw_panel(const double* slab, double* Rg, int ldg, double* sC, double* sTm, int LP, int j0, int nrefl,
                                          bool need_T, int lane) {
-  qr_panel<RPL>(slab + j0, LP, Rg + (size_t)j0 * ldg + j0, ldg, sC + j0, LP, sTm, QW_LDL, nrefl, need_T, lane);
+  qr_panel<RPL, FOLD>(slab + j0, LP, Rg + (size_t)j0 * ldg + j0, ldg, sC + j0, LP, sTm, QW_LDL, nrefl, need_T, lane);
 }
 
 // Applies the block reflector of panel j0 (V in the chunk, T in sTm) to the 8-column tile at c0: R rows from the slab,
@@ -100,14 +101,16 @@ __device__ __forceinline__ void qw_apply(const double* slab, double* Rg, int ldg
   __syncwarp();
 }
 
+template <bool FOLD>
 __device__ __forceinline__ void qw_panel_rows(int rpl, const double* slab, double* Rg, int ldg, double* sC, double* sTm, int LP, int j0,
                                               int nrefl, bool need_T, int lane) {
-  if (rpl == 4) qw_panel<4>(slab, Rg, ldg, sC, sTm, LP, j0, nrefl, need_T, lane);
-  else if (rpl == 2) qw_panel<2>(slab, Rg, ldg, sC, sTm, LP, j0, nrefl, need_T, lane);
-  else qw_panel<1>(slab, Rg, ldg, sC, sTm, LP, j0, nrefl, need_T, lane);
+  if (rpl == 4) qw_panel<4, FOLD>(slab, Rg, ldg, sC, sTm, LP, j0, nrefl, need_T, lane);
+  else if (rpl == 2) qw_panel<2, FOLD>(slab, Rg, ldg, sC, sTm, LP, j0, nrefl, need_T, lane);
+  else qw_panel<1, FOLD>(slab, Rg, ldg, sC, sTm, LP, j0, nrefl, need_T, lane);
 }
 
-__global__ void __launch_bounds__(QW_T, 1) k_qr_wide(Dev d, int level, unsigned smem_bytes) {
+template <bool FOLD>
+__global__ void __launch_bounds__(QW_T, 1) k_qr_wide(Dev d, int level, unsigned smem_bytes, int nslab) {
   extern __shared__ __align__(128) double qs[];
   __shared__ uint64_t s_slab[QW_NSLAB], s_rows;
   __shared__ int s_c0;
@@ -201,23 +204,23 @@ __global__ void __launch_bounds__(QW_T, 1) k_qr_wide(Dev d, int level, unsigned 
         srows += 1;
       }
       auto issue_slab = [&](int pb) {                 // warp 1, lanes 0..7: row i of slab pb, columns 8 pb .. cap
-        const int b = pb % QW_NSLAB;
+        const int b = pb % nslab;
         if (lane == 0) mbar_arrive_expect_tx(&s_slab[b], (unsigned)(8 * (cap - 8 * pb) * sizeof(double)));
         __syncwarp();
         if (lane < 8) bulk_g2s(sSlab + (size_t)(b * 8 + lane) * LP + 8 * pb, Rg + (size_t)(8 * pb + lane) * ldg + 8 * pb, (cap - 8 * pb) * sizeof(double), &s_slab[b]);
       };
       if (warp == 1) {
         issue_slab(pb0);
-        if (pb0 + 1 < npan) issue_slab(pb0 + 1);
+        if (nslab > 2 && pb0 + 1 < npan) issue_slab(pb0 + 1);
       }
       if (warp == 0) {
-        const int sb = pb0 % QW_NSLAB;
+        const int sb = pb0 % nslab;
         mbar_wait(&s_slab[sb], su[sb] & 1u);
-        qw_panel_rows(RPL, sSlab + (size_t)sb * 8 * LP, Rg, ldg, sC, sTm + (pb0 & 1) * 8 * QW_LDL, LP, 8 * pb0, min(8, na - 8 * pb0), pb0 + 1 < nct, lane);
+        qw_panel_rows<FOLD>(RPL, sSlab + (size_t)sb * 8 * LP, Rg, ldg, sC, sTm + (pb0 & 1) * 8 * QW_LDL, LP, 8 * pb0, min(8, na - 8 * pb0), pb0 + 1 < nct, lane);
       }
       __syncthreads();
       for (int pb = pb0; pb < npan; ++pb) {
-        const int cur = pb & 1, j0 = 8 * pb, sb = pb % QW_NSLAB, sbn = (pb + 1) % QW_NSLAB;
+        const int cur = pb & 1, j0 = 8 * pb, sb = pb % nslab, sbn = (pb + 1) % nslab;
         // rows of the chunk that can be non-zero in this panel: all of them for stacked landmark rows; a triangular factor
         // being folded (tree levels) has nothing below its diagonal, so row r0 + i only matters once 8 pb + 7 >= r0 + i
         const int rows_nz = level < 0 ? cr : min(cr, j0 + 8 - r0);
@@ -225,13 +228,13 @@ __global__ void __launch_bounds__(QW_T, 1) k_qr_wide(Dev d, int level, unsigned 
         const double* slab = sSlab + (size_t)sb * 8 * LP;
         const double* Tm = sTm + cur * 8 * QW_LDL;
         const bool ahead = pb + 1 < npan;             // another panel follows: warp 0 looks ahead
-        if (warp == 1 && pb + 2 < npan) issue_slab(pb + 2);   // two slabs ahead: the look-ahead panel never waits for its slab
+        if (warp == 1 && pb + nslab - 1 < npan) issue_slab(pb + nslab - 1);   // nslab - 1 slabs ahead
         mbar_wait(&s_slab[sb], su[sb] & 1u);          // (already complete for warp 0)
         if (ahead) {
           if (warp == 0) {
             qw_apply(slab, Rg, ldg, sC, Tm, sYw, LP, j0, j0 + 8, crk, crt, g, tg);
             mbar_wait(&s_slab[sbn], su[sbn] & 1u);
-            qw_panel_rows(RPL, sSlab + (size_t)sbn * 8 * LP, Rg, ldg, sC, sTm + (cur ^ 1) * 8 * QW_LDL, LP, j0 + 8, min(8, na - j0 - 8), pb + 2 < nct, lane);
+            qw_panel_rows<FOLD>(RPL, sSlab + (size_t)sbn * 8 * LP, Rg, ldg, sC, sTm + (cur ^ 1) * 8 * QW_LDL, LP, j0 + 8, min(8, na - j0 - 8), pb + 2 < nct, lane);
           } else {
             for (int ct = pb + 2 + (warp - 1); ct < nct; ct += QW_T / 32 - 1) qw_apply(slab, Rg, ldg, sC, Tm, sYw, LP, j0, 8 * ct, crk, crt, g, tg);
           }
@@ -270,13 +273,19 @@ int qr_wide_leaf_rows(int m, int leaf_cap, int CR) { return qw_rows_per_leaf(m, 
 
 void launch_qr_wide(const Dev& d, cudaStream_t st) {
   static DevOnce once;     // function attributes are per device
-  once.run([&] { cudaFuncSetAttribute(k_qr_wide, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024); });
+  once.run([&] {
+    cudaFuncSetAttribute(k_qr_wide<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+    cudaFuncSetAttribute(k_qr_wide<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+  });
+  const bool fold = getenv("MSCKF_QW_NOFOLD") == nullptr;                  // development knobs (A/B on one box)
+  const int nslab = getenv("MSCKF_QW_SLABS") ? std::max(2, std::min(QW_NSLAB, atoi(getenv("MSCKF_QW_SLABS")))) : QW_NSLAB;
   const int sms = sm_count();
   // a 128-row chunk of the widest stack if that fits, else everything the SM has: every stack then sizes its own chunk
   const size_t sm = std::min<size_t>(qw_smem_bytes(d.qr_capcols, 128), 226 * 1024);
   const int grid = (int)std::min<long long>((long long)d.F * d.qr_leaf_cap, 2LL * sms);
   for (int level = -1; level < d.qr_levels; ++level)
-    KLAUNCH(d, KID_QR_WIDE, st, (k_qr_wide<<<grid, QW_T, sm, st>>>(d, level, (unsigned)sm)));
+    if (fold) KLAUNCH(d, KID_QR_WIDE, st, (k_qr_wide<true><<<grid, QW_T, sm, st>>>(d, level, (unsigned)sm, nslab)));
+    else KLAUNCH(d, KID_QR_WIDE, st, (k_qr_wide<false><<<grid, QW_T, sm, st>>>(d, level, (unsigned)sm, nslab)));
   KLAUNCH(d, KID_QR_WIDE, st, (k_qr_wide_finish<<<std::min(d.F, 2 * sms), QW_T, 0, st>>>(d)));
 }
 

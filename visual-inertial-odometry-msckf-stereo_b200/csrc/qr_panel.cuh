@@ -11,7 +11,7 @@ namespace msckf {
 // Rin(jj, c) = Rin[jj * ldin + c]: the diagonal block of the factor as it is (shared memory); Rout(jj, c) receives the new
 // values (may alias Rin).  sC: the chunk, leading dimension ldc, panel columns at sC[row * ldc + 0 .. 7]; V replaces them.
 // sTm: [8][ldt].  nrefl < 8 on the last panel: the remaining columns carry data (residual / padding), not reflectors.
-template <int RPL>
+template <int RPL, bool FOLD = true>
 __device__ __forceinline__ void qr_panel(const double* Rin, int ldin, double* Rout, int ldout, double* sC, int ldc, double* sTm, int ldt,
                                          int nrefl, bool need_T, int lane) {
   double x[RPL][8];
@@ -43,7 +43,7 @@ __device__ __forceinline__ void qr_panel(const double* Rin, int ldin, double* Ro
       double rrow[8];
 #pragma unroll
       for (int c = jj; c < 8; ++c) rrow[c] = Rin[jj * ldin + c];
-      if (jj < 4) {
+      if (FOLD && jj < 4) {
         warp_allsum8(s, lane);                            // 5 .. 8 values: folded while they travel
       } else {
 #pragma unroll
@@ -95,7 +95,15 @@ __device__ __forceinline__ void qr_panel(const double* Rin, int ldin, double* Ro
       for (int t = 0; t < RPL; ++t) a += x[t][l] * x[t][j];
       gv[j * (j - 1) / 2 + l] = a;
     }
-  warp_allsum32(gv, lane);
+  if (FOLD) {
+    warp_allsum32(gv, lane);
+  } else {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+      for (int i = 0; i < 28; ++i) gv[i] += __shfl_xor_sync(WR_FULL, gv[i], o);
+    }
+  }
   double trow[8];
   const int ri = lane & 7;
 #pragma unroll

@@ -348,7 +348,7 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   CKC(cudaMemcpyAsync(dprm, &hp, sizeof hp, cudaMemcpyHostToDevice, ctx->st));
   d.prm = dprm;
   DA(d.imu, F * IMU_STRIDE);
-  DA(d.cam_id, F * Nm); DA(d.cam_phys, F * Nm); DA(d.cam, F * Nm * CAM_STRIDE); DA(d.ncam, F); DA(d.phys_used, F); DA(d.cam_pre, F * Nm * CAM_PRE);
+  DA(d.cam_id, F * Nm); DA(d.cam_phys, F * Nm); DA(d.cam, F * Nm * CAM_STRIDE); DA(d.ncam, F); DA(d.phys_used, F); DA(d.obs_N, F); DA(d.obs_phys, F); DA(d.cam_pre, F * Nm * CAM_PRE);
   DA(d.P, F * (size_t)d.ld * d.ld);
   DA(d.f_id, F * Fc); DA(d.f_mask, F * Fc); DA(d.f_flags, F * Fc); DA(d.f_pos, F * Fc * 3); DA(d.f_obs, F * Fc * Nm * 4);
   DA(d.ord, F * Fc); DA(d.ord_tmp, F * Fc); DA(d.nlive, F); DA(d.free_stack, F * Fc); DA(d.nfree, F);
@@ -793,10 +793,16 @@ static void enqueue_frame_eager(msckf_ctx* ctx, const FrameIn& in, const FrameIn
   const Dev& d = ctx->d;
   const bool tm = ctx->timing && !fin;
   if (tm) cudaEventRecord(ctx->ev[0], ctx->st);
-  launch_propagate(d, in.imu_off, in.ts, in.gyro, in.acc, ctx->st, fin);
-  launch_augment(d, in.cam_ids, ctx->st, fin);
+  // add_feature_observations only needs to know where the new camera state will sit (k_cam_slot): it runs on its own lane
+  // beside propagation and augmentation
+  launch_cam_slot(d, ctx->st);
+  {
+    Fork fk(d, ctx->st);
+    launch_observe(d, in.feat_off, in.ids, in.uv, fk.lane(1), fin, 1);
+    launch_propagate(d, in.imu_off, in.ts, in.gyro, in.acc, ctx->st, fin);
+    launch_augment(d, in.cam_ids, ctx->st, fin, true);
+  }
   if (tm) cudaEventRecord(ctx->ev[1], ctx->st);
-  launch_observe(d, in.feat_off, in.ids, in.uv, ctx->st, fin);
   if (tm) cudaEventRecord(ctx->ev[2], ctx->st);
   enqueue_lost_stage(ctx);
   if (tm) cudaEventRecord(ctx->ev[3], ctx->st);

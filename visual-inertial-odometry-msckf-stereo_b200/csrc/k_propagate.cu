@@ -305,9 +305,16 @@ __global__ void __launch_bounds__(PW * 32, 7) k_propagate(Dev d, const int* __re
         if (job < 18) {
           const int t = job % 9, it = t / 3, jt = t - 3 * it;
           const double* B = (job < 9) ? sPII : sAcc;
+          if (it < 2) {
+            // rows 0..15 of Phi have nothing right of column 15 (phi_row_width): four 4-deep steps instead of six
 #pragma unroll
-          for (int ks = 0; ks < 6; ++ks)
-            pdmma(ac0[u], ac1[u], sPhi[(8 * it + g) * PLD + 4 * ks + tg], B[(4 * ks + tg) * PLD + 8 * jt + g]);
+            for (int ks = 0; ks < 4; ++ks)
+              pdmma(ac0[u], ac1[u], sPhi[(8 * it + g) * PLD + 4 * ks + tg], B[(4 * ks + tg) * PLD + 8 * jt + g]);
+          } else {
+            // rows 16..20 of Phi are identity rows (extrinsics), 21..23 padding: the product tile is a copy of B's tile
+            ac0[u] = B[(16 + g) * PLD + 8 * jt + 2 * tg];
+            ac1[u] = B[(16 + g) * PLD + 8 * jt + 2 * tg + 1];
+          }
         }
       }
 #pragma unroll
@@ -330,10 +337,20 @@ __global__ void __launch_bounds__(PW * 32, 7) k_propagate(Dev d, const int* __re
         xc0[u] = xc1[u] = xe0[u] = xe1[u] = 0.0;
         if (t < 9) {
           const int it = t / 3, jt = t - 3 * it;
+          // X = T Phi^T and its mirror Phi T^T: a tile whose Phi operand is the identity tile row (16..23) is a copy of T
+          if (jt < 2) {
 #pragma unroll
-          for (int ks = 0; ks < 6; ++ks) {
-            pdmma(xc0[u], xc1[u], sT[(8 * it + g) * PLD + 4 * ks + tg], sPhi[(8 * jt + g) * PLD + 4 * ks + tg]);
-            pdmma(xe0[u], xe1[u], sPhi[(8 * it + g) * PLD + 4 * ks + tg], sT[(8 * jt + g) * PLD + 4 * ks + tg]);
+            for (int ks = 0; ks < 4; ++ks) pdmma(xc0[u], xc1[u], sT[(8 * it + g) * PLD + 4 * ks + tg], sPhi[(8 * jt + g) * PLD + 4 * ks + tg]);
+          } else {
+            xc0[u] = (16 + 2 * tg < 21) ? sT[(8 * it + g) * PLD + 16 + 2 * tg] : 0.0;
+            xc1[u] = (17 + 2 * tg < 21) ? sT[(8 * it + g) * PLD + 17 + 2 * tg] : 0.0;
+          }
+          if (it < 2) {
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) pdmma(xe0[u], xe1[u], sPhi[(8 * it + g) * PLD + 4 * ks + tg], sT[(8 * jt + g) * PLD + 4 * ks + tg]);
+          } else {
+            xe0[u] = (16 + g < 21) ? sT[(8 * jt + 2 * tg) * PLD + 16 + g] : 0.0;
+            xe1[u] = (16 + g < 21) ? sT[(8 * jt + 2 * tg + 1) * PLD + 16 + g] : 0.0;
           }
         }
       }
@@ -360,7 +377,9 @@ __global__ void __launch_bounds__(PW * 32, 7) k_propagate(Dev d, const int* __re
   }
 
   // ---- write back: IMU state, P_II, P_IC = Phi_acc P_IC and its mirror
-  for (int e = lane; e < IMU_STRIDE; e += NT) imu[e] = sx[e];
+  // (the tracking rate belongs to add_feature_observations, which runs beside this kernel inside a frame)
+  for (int e = lane; e < IMU_STRIDE; e += NT)
+    if (e != MSCKF_IMU_TRACKING_RATE) imu[e] = sx[e];
   if (lane == 0) d.counters[NCNT * f + MSCKF_CNT_IMU_STEPS] += k1 - k0;
   for (int e = lane; e < 441; e += NT) {
     const int i = e / 21, j = e - 21 * i;
@@ -397,15 +416,29 @@ __global__ void __launch_bounds__(PW * 32, 7) k_propagate(Dev d, const int* __re
 }
 
 // ------------------------------------------------------------------ state augmentation
+// Where the camera state of this frame will sit: its index in the window and the physical observation slot (lowest free
+// bit).  Neither depends on the propagation, so add_feature_observations (k_observe) can run beside k_propagate / k_augment
+// inside a frame; both read the slot from here.
+__global__ void __launch_bounds__(256) k_cam_slot(Dev d) {
+  const int f = blockIdx.x * 256 + threadIdx.x;
+  if (f >= d.F) return;
+  const int N = d.ncam[f];
+  if (N >= d.Nmax) {
+    atomicOr(d.err, ERRBIT_CAM_CAP);
+    d.obs_N[f] = N;
+    d.obs_phys[f] = -1;
+    return;
+  }
+  d.obs_N[f] = N + 1;
+  d.obs_phys[f] = __ffsll((long long)~d.phys_used[f]) - 1;
+}
+
 // msckf.py:385-407 + jit_utils.py:137-167.  One CTA per filter.
 __global__ void __launch_bounds__(PT) k_augment(Dev d, const long long* __restrict__ new_ids, const FrameIn* fin) {
   if (fin) new_ids = fin->cam_ids;
   const int f = blockIdx.x, tid = threadIdx.x;
   const int N = d.ncam[f];
-  if (N >= d.Nmax) {
-    if (tid == 0) atomicOr(d.err, ERRBIT_CAM_CAP);
-    return;
-  }
+  if (N >= d.Nmax || d.obs_phys[f] < 0) return;     // window full: reported by k_cam_slot
   __shared__ double sJ[6 * 21];
   __shared__ double sB[6 * 21];   // J P[:21,:21]
   const double* imu = d.imu + (size_t)f * IMU_STRIDE;
@@ -423,11 +456,10 @@ __global__ void __launch_bounds__(PT) k_augment(Dev d, const long long* __restri
     for (int i = 0; i < 4; ++i) { c[i] = q[i]; c[7 + i] = q[i]; }
     for (int i = 0; i < 3; ++i) { const double pi = imu[MSCKF_IMU_P + i] + tw[i]; c[4 + i] = pi; c[11 + i] = pi; }
     d.cam_id[(size_t)f * d.Nmax + N] = new_ids[f];
-    // physical observation slot: lowest free bit
-    const unsigned long long used = d.phys_used[f];
-    const int slot = __ffsll((long long)~used) - 1;
+    // physical observation slot: lowest free bit (k_cam_slot)
+    const int slot = d.obs_phys[f];
     d.cam_phys[(size_t)f * d.Nmax + N] = slot;
-    d.phys_used[f] = used | (1ull << slot);
+    d.phys_used[f] |= 1ull << slot;
     for (int e = 0; e < 126; ++e) sJ[e] = 0.0;
     double St[9];
     skew3(tw, St);
@@ -602,7 +634,9 @@ void launch_propagate(const Dev& d, const int* imu_off, const double* ts, const 
   });
   KLAUNCH(d, KID_PROPAGATE, st, (k_propagate<<<d.F, PW * 32, smem, st>>>(d, imu_off, ts, gyro, acc, fin)));
 }
-void launch_augment(const Dev& d, const long long* ids, cudaStream_t st, const FrameIn* fin) {
+void launch_cam_slot(const Dev& d, cudaStream_t st) { KLAUNCH(d, KID_MISC, st, (k_cam_slot<<<(d.F + 255) / 256, 256, 0, st>>>(d))); }
+void launch_augment(const Dev& d, const long long* ids, cudaStream_t st, const FrameIn* fin, bool slot_done) {
+  if (!slot_done) launch_cam_slot(d, st);
   KLAUNCH(d, KID_AUGMENT, st, (k_augment<<<d.F, PT, 0, st>>>(d, ids, fin)));
 }
 void launch_finish_frame(const Dev& d, int do_reset_check, cudaStream_t st) {

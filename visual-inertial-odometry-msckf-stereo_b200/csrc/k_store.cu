@@ -65,14 +65,16 @@ __device__ __forceinline__ unsigned hash64(long long k) {
 
 // ------------------------------------------------------------------ add_feature_observations (msckf.py:409-427)
 __global__ void __launch_bounds__(ST) k_observe(Dev d, const int* __restrict__ feat_off, const long long* __restrict__ ids,
-                                                 const double* __restrict__ uv, const FrameIn* fin, int use_smem) {
+                                                 const double* __restrict__ uv, const FrameIn* fin, int use_smem, int pending_augment) {
   if (fin) { feat_off = fin->feat_off; ids = fin->ids; uv = fin->uv; }
   const int f = blockIdx.x, tid = threadIdx.x;
   __shared__ int s_warp[ST / 32];
   __shared__ int s_tracked;
   const int n0 = d.nlive[f];
   const int off = feat_off[f], cnt = feat_off[f + 1] - off;
-  const int N = d.ncam[f];
+  // inside a frame this kernel runs beside propagation / augmentation: the camera state being added is not in the window
+  // yet, its index and observation slot come from k_cam_slot
+  const int N = pending_augment ? d.obs_N[f] : d.ncam[f];
   // the per-frame id -> slot table lives in shared memory when it fits (launch_observe), else in its global scratch
   extern __shared__ __align__(16) unsigned char obs_sm[];
   long long* hk = use_smem ? (long long*)obs_sm : d.h_key + (size_t)f * d.Hs;
@@ -82,7 +84,8 @@ __global__ void __launch_bounds__(ST) k_observe(Dev d, const int* __restrict__ f
   for (int e = tid; e < d.Hs; e += ST) hk[e] = EMPTY_KEY;
   __syncthreads();
   if (N == 0) return;
-  const int phys = d.cam_phys[(size_t)f * d.Nmax + N - 1];
+  const int phys = pending_augment ? d.obs_phys[f] : d.cam_phys[(size_t)f * d.Nmax + N - 1];
+  if (phys < 0) return;                              // window full (reported)
   const unsigned long long bit = 1ull << phys;
   int* ord = d.ord + (size_t)f * d.Fcap;
   for (int j = tid; j < n0; j += ST) {
@@ -559,14 +562,15 @@ __global__ void __launch_bounds__(ST) k_plan_stack(Dev d, int stage) {
   }
 }
 
-void launch_observe(const Dev& d, const int* feat_off, const long long* ids, const double* uv, cudaStream_t st, const FrameIn* fin) {
+void launch_observe(const Dev& d, const int* feat_off, const long long* ids, const double* uv, cudaStream_t st, const FrameIn* fin,
+                    int pending_augment) {
   const size_t table = (size_t)d.Hs * (sizeof(long long) + sizeof(int));
   const int use_smem = table <= 96 * 1024;
   static DevOnce once;     // function attributes are per device
   once.run([&] {
     cudaFuncSetAttribute(k_observe, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
   });
-  KLAUNCH(d, KID_OBSERVE, st, (k_observe<<<d.F, ST, use_smem ? table : 0, st>>>(d, feat_off, ids, uv, fin, use_smem)));
+  KLAUNCH(d, KID_OBSERVE, st, (k_observe<<<d.F, ST, use_smem ? table : 0, st>>>(d, feat_off, ids, uv, fin, use_smem, pending_augment)));
 }
 void launch_classify_lost(const Dev& d, cudaStream_t st) {
   KLAUNCH(d, KID_CLASSIFY_LOST, st, (k_classify_lost<<<d.F, ST, 0, st>>>(d)));

@@ -98,14 +98,15 @@ struct Fork {
 // k_propagate.cu
 void launch_propagate(const Dev& d, const int* imu_off, const double* ts, const double* gyro, const double* acc, cudaStream_t st,
                       const FrameIn* fin = nullptr);
-void launch_augment(const Dev& d, const long long* ids, cudaStream_t st, const FrameIn* fin = nullptr);
+void launch_cam_slot(const Dev& d, cudaStream_t st);
+void launch_augment(const Dev& d, const long long* ids, cudaStream_t st, const FrameIn* fin = nullptr, bool slot_done = false);
 void launch_finish_frame(const Dev& d, int do_reset_check, cudaStream_t st);
 void launch_reset(const Dev& d, int only_filter, int reset_imu, cudaStream_t st);
 void launch_remove_cams(const Dev& d, cudaStream_t st);
 
 // k_store.cu  (landmark store = map_server bookkeeping)
 void launch_observe(const Dev& d, const int* feat_off, const long long* ids, const double* uv, cudaStream_t st,
-                    const FrameIn* fin = nullptr);
+                    const FrameIn* fin = nullptr, int pending_augment = 0);
 void launch_classify_lost(const Dev& d, cudaStream_t st);
 void launch_plan_items(const Dev& d, int stage, cudaStream_t st);
 void launch_plan_stack(const Dev& d, int stage, cudaStream_t st);

@@ -81,6 +81,8 @@ struct Dev {
   int* ncam;               // [F]
   double* cam_pre;         // [F][Nmax][CAM_PRE] per-stage derived camera quantities (k_cam_prepare)
   unsigned long long* phys_used;   // [F] bit mask of physical slots in use
+  int* obs_N;              // [F] camera-state count after this frame's augmentation (k_cam_slot), what k_observe sees
+  int* obs_phys;           // [F] physical observation slot of the camera state being added (-1: window full)
   double* P;               // [F][ld*ld] row-major, logical layout, n = 21+6*ncam
   // ---- landmark store (map_server)
   long long* f_id;         // [F][Fcap]

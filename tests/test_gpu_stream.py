@@ -294,6 +294,57 @@ def test_two_frames_in_flight_equal_sequential():
         assert np.array_equal(outs['blocking'][1][k], outs['pipelined'][1][k])
 
 
+def test_euroc_replay_through_publishers_vs_oracle(tmp_path):
+    """a sequence on disk in the EuRoC layout, replayed by two DataPublisher threads into queues and consumed
+    the way vio.py does (IMU thread -> imu_callback, image thread -> feature_callback), drives the CUDA drop-in; the oracle
+    fed with the same messages in the same order agrees (1e-9, ids exact) and the ATE against the ground-truth file is small."""
+    from queue import Queue
+    import time
+    from msckf_b200 import dataset
+    stream = synth.make_stream(50, 90, structure_seed=6, noise_seed=12)
+    dataset.write_euroc(stream, str(tmp_path), t0_ns=0)
+    ds = dataset.EuRoCDataset(str(tmp_path))
+    q_imu, q_feat = Queue(), Queue()
+    pubs = [dataset.DataPublisher(ds.imu, q_imu, ratio=50.0), dataset.DataPublisher(ds.features, q_feat, ratio=50.0)]
+    now = time.time()
+    for p in pubs:
+        p.start(now)
+    imu_msgs, feat_msgs = [], []
+    for q, out in ((q_imu, imu_msgs), (q_feat, feat_msgs)):
+        while True:
+            m = q.get(timeout=60)
+            if m is None:
+                break
+            out.append(m)
+    for p in pubs:
+        p.stop()
+    assert len(imu_msgs) == len(stream.imu_ts) and len(feat_msgs) == stream.n_frames
+    dcfg = ConfigEuRoC()
+    dcfg._vio_max_cam_state_size__ = 10
+    ocfg = orc.ConfigEuRoC()
+    ocfg._vio_max_cam_state_size__ = 10
+    df, of = MSCKF(dcfg, feature_capacity=512), orc.MSCKF(ocfg)
+    worst, k = 0.0, 0
+    est_t, est_p = [], []
+    try:
+        for msg in feat_msgs:
+            while k < len(imu_msgs) and imu_msgs[k].vio_timestamp__ <= msg.timestamp:
+                df.imu_callback(imu_msgs[k])
+                of.imu_callback(imu_msgs[k])
+                k += 1
+            rd, ro = df.feature_callback(msg), of.feature_callback(msg)
+            assert (rd is None) == (ro is None)
+            sd, so = snapshot(df), snapshot(of)
+            assert np.array_equal(sd['cam_ids'], so['cam_ids']) and np.array_equal(sd['map_ids'], so['map_ids'])
+            worst = max(worst, rel_err(sd['imu'], so['imu']), rel_err(sd['P'], so['P']), rel_err(sd['cams'], so['cams']))
+            est_t.append(msg.timestamp)
+            est_p.append(sd['imu'][13:16].copy())
+    finally:
+        df.close()
+    assert worst < TOL, worst
+    assert dataset.absolute_trajectory_error(est_t, est_p, ds.groundtruth) < 0.25
+
+
 def test_graph_replay_equals_eager_on_ragged_frames(monkeypatch):
     """The captured frame graph is replayed with new message pointers every frame; its launch dimensions must not depend
     on the message.  Filters of one batch receive different numbers of features and IMU samples per frame (ragged

@@ -70,6 +70,7 @@ def make_structure(n_frames=200, feats_per_frame=300, structure_seed=0, mean_tra
     rng = np.random.default_rng(structure_seed)
     st = Structure()
     st.n_frames = n_frames
+    st.speed = speed
     t_end = T_START + FRAME_DT * (n_frames + 1)
     n_imu = int(round(t_end / IMU_DT)) + 1
     ts = np.arange(n_imu) * IMU_DT

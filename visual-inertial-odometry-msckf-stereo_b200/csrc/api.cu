@@ -349,7 +349,7 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   d.prm = dprm;
   DA(d.imu, F * IMU_STRIDE);
   DA(d.cam_id, F * Nm); DA(d.cam_phys, F * Nm); DA(d.cam, F * Nm * CAM_STRIDE); DA(d.ncam, F); DA(d.phys_used, F); DA(d.obs_N, F); DA(d.obs_phys, F); DA(d.cam_pre, F * Nm * CAM_PRE);
-  DA(d.P, F * (size_t)d.ld * d.ld);
+  DA(d.P, 2 * F * (size_t)d.ld * d.ld); DA(d.Pcur, F); DA(d.p_compacted, F);
   DA(d.f_id, F * Fc); DA(d.f_mask, F * Fc); DA(d.f_flags, F * Fc); DA(d.f_pos, F * Fc * 3); DA(d.f_obs, F * Fc * Nm * 4);
   DA(d.ord, F * Fc); DA(d.ord_tmp, F * Fc); DA(d.nlive, F); DA(d.free_stack, F * Fc); DA(d.nfree, F);
   DA(d.h_key, F * (size_t)d.Hs); DA(d.h_val, F * (size_t)d.Hs);
@@ -536,7 +536,9 @@ int msckf_get_cov(msckf_ctx* ctx, int32_t f, double* P, int32_t n) {
   CK(cudaSetDevice(ctx->device));
   int rc = sync_and_check(ctx);
   if (rc) return rc;
-  CK(cudaMemcpy2D(P, (size_t)n * sizeof(double), d.P + (size_t)f * d.ld * d.ld, (size_t)d.ld * sizeof(double),
+  double* Pf = nullptr;                  // the filter's current covariance buffer
+  CK(cudaMemcpy(&Pf, d.Pcur + f, sizeof Pf, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy2D(P, (size_t)n * sizeof(double), Pf, (size_t)d.ld * sizeof(double),
                   (size_t)n * sizeof(double), n, cudaMemcpyDeviceToHost));
   return MSCKF_OK;
 }
@@ -546,7 +548,9 @@ int msckf_set_cov(msckf_ctx* ctx, int32_t f, const double* P, int32_t n) {
   ARG(f >= 0 && f < d.F && P && n >= NI && n <= d.nmax, "filter index / size");
   CK(cudaSetDevice(ctx->device));
   CK(cudaStreamSynchronize(ctx->st));
-  CK(cudaMemcpy2D(d.P + (size_t)f * d.ld * d.ld, (size_t)d.ld * sizeof(double), P, (size_t)n * sizeof(double),
+  double* Pf = nullptr;
+  CK(cudaMemcpy(&Pf, d.Pcur + f, sizeof Pf, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy2D(Pf, (size_t)d.ld * sizeof(double), P, (size_t)n * sizeof(double),
                   (size_t)n * sizeof(double), n, cudaMemcpyHostToDevice));
   return MSCKF_OK;
 }

@@ -286,7 +286,7 @@ __device__ __forceinline__ void jac_front(const Dev& d, int f, int k, int M, uns
   }
   gsync<NT>(gmask);
   // ---- step 4: PZt = Pcc Z^T  (6M x 3)
-  const double* P = d.P + (size_t)f * d.ld * d.ld;
+  const double* P = cov_of(d, f);
   const int ld = d.ld;
   for (int c = tid; c < C6; c += NT) {
     const double* prow = P + (size_t)(NI + 6 * B.cl[c / 6] + (c % 6)) * ld + NI;
@@ -357,7 +357,7 @@ __device__ void jac_core(const Dev& d, int f, int k, int M, unsigned long long l
   const Params& prm = *d.prm;
   const int R4 = 4 * M, C6 = 6 * M, R = R4 - 3, ldT = C6 + 1;
   jac_front<NT>(d, f, k, M, lmask, B, tid, gmask_in);
-  const double* P = d.P + (size_t)f * d.ld * d.ld;
+  const double* P = cov_of(d, f);
   const int ld = d.ld;
   // ---- step 5: T1 = E Pcc - V PZt^T   (one (block a, column c) 4-vector per thread; P is exactly symmetric)
   for (int e2 = tid; e2 < M * C6; e2 += NT) {
@@ -509,7 +509,7 @@ __global__ void __launch_bounds__(256) k_gate_lu(Dev d) {
     const unsigned long long lmask = d.item_lmask[ik];
     if (d.item_off[ik] + jac_record_doubles(M) > d.pool_cap) continue;
     const double* rec = d.pool + d.item_off[ik];
-    const double* P = d.P + (size_t)f * ld * ld;
+    const double* P = cov_of(d, f);
     double* T1 = d.lu_scratch;                  // [R][C6]
     double* S = T1 + (size_t)R * C6;            // [R][R]
     double* y = S + (size_t)R * R;              // [R]
@@ -796,7 +796,7 @@ __global__ void __launch_bounds__(JB_T, MINB) k_jacobian_gate_big(Dev d, int cls
     }
     __syncthreads();
     for (int i = R + tid; i < Rp; i += JB_T) S[(size_t)i * ldS + i] = 1.0;
-    jb_build_S<GS, MAXR>(d.P + (size_t)f * d.ld * d.ld, d.ld, M, B, S, ldS, sigma2, tid);
+    jb_build_S<GS, MAXR>(cov_of(d, f), d.ld, M, B, S, ldS, sigma2, tid);
     __syncthreads();
     const bool bad = jb_cholesky(S, ldS, nkt, sY, sLinv, &s_bad, tid);
     double gamma = 0.0;
@@ -843,7 +843,7 @@ __global__ void k_export_item_dense(Dev d, int f, double* H, double* r, int n_st
 __global__ void __launch_bounds__(256) k_gate_dense(Dev d, int f, const double* __restrict__ H, const double* __restrict__ r, int m,
                                                      int n, int dof, double* scratch, double* out_gamma, int* out_pass) {
   const int tid = threadIdx.x;
-  const double* P = d.P + (size_t)f * d.ld * d.ld;
+  const double* P = cov_of(d, f);
   double* T1 = scratch;                 // m x n row-major
   double* S = T1 + (size_t)m * n;       // m x m row-major
   double* y = S + (size_t)m * m;

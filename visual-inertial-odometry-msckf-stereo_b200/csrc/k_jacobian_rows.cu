@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(JR_T, jr_ctas_per_sm<M>()) k_jacobian_rows(Dev
     if (f != have_f || lmask != have_lmask) {               // group-uniform
       have_f = f;
       have_lmask = lmask;
-      const double* P = d.P + (size_t)f * ld * ld;
+      const double* P = cov_of(d, f);
       for (int e = r; e < C6 * C6; e += G) {
         const int i = e / C6, c = e - i * C6;
         sP[e] = P[(size_t)(NI + 6 * cl[i / 6] + i % 6) * ld + NI + 6 * cl[c / 6] + c % 6];

@@ -214,7 +214,7 @@ __global__ void __launch_bounds__(PW * 32, 7) k_propagate(Dev d, const int* __re
   double* sx = sSt + (PKC + 1) * PST;
   const Params& prm = *d.prm;
   double* imu = d.imu + (size_t)f * IMU_STRIDE;
-  double* P = d.P + (size_t)f * d.ld * d.ld;
+  double* P = cov_of(d, f);
   const int ld = d.ld;
   const int n = NI + 6 * d.ncam[f];
 
@@ -442,7 +442,7 @@ __global__ void __launch_bounds__(PT) k_augment(Dev d, const long long* __restri
   __shared__ double sJ[6 * 21];
   __shared__ double sB[6 * 21];   // J P[:21,:21]
   const double* imu = d.imu + (size_t)f * IMU_STRIDE;
-  double* P = d.P + (size_t)f * d.ld * d.ld;
+  double* P = cov_of(d, f);
   const int ld = d.ld, n = NI + 6 * N;
   if (tid == 0) {
     double Rwi[9], Rwc[9], tw[3], q[4];
@@ -493,7 +493,7 @@ __global__ void __launch_bounds__(PT) k_augment(Dev d, const long long* __restri
 
 // ------------------------------------------------------------------ reset of P (msckf.py:820-830)
 __device__ void reset_cov(const Dev& d, int f, int tid, int nthreads) {
-  double* P = d.P + (size_t)f * d.ld * d.ld;
+  double* P = cov_of(d, f);
   const Params& prm = *d.prm;
   for (int e = tid; e < 21 * d.ld; e += nthreads) {
     const int i = e / d.ld, j = e - i * d.ld;
@@ -535,7 +535,7 @@ __global__ void __launch_bounds__(PT) k_finish_frame(Dev d, int do_reset_check) 
     const double thr = d.prm->pos_std_thr;
     int r = 0;
     if (thr > 0) {
-      const double* P = d.P + (size_t)f * d.ld * d.ld;
+      const double* P = cov_of(d, f);
       const double sx = sqrt(P[(size_t)12 * d.ld + 12]), sy = sqrt(P[(size_t)13 * d.ld + 13]), sz = sqrt(P[(size_t)14 * d.ld + 14]);
       const double m = fmax(fmax(sx, sy), sz);
       r = !(m < thr);
@@ -554,6 +554,13 @@ __global__ void __launch_bounds__(PT) k_finish_frame(Dev d, int do_reset_check) 
 __global__ void __launch_bounds__(PT) k_reset(Dev d, int only_filter, int reset_imu) {
   const int f = only_filter >= 0 ? only_filter : blockIdx.x;
   const int tid = threadIdx.x;
+  if (only_filter < 0) {                 // creation: every filter starts in its first covariance buffer
+    if (tid == 0) {
+      d.Pcur[f] = d.P + (size_t)f * d.ld * d.ld;
+      d.p_compacted[f] = 0;
+    }
+    __syncthreads();
+  }
   clear_window_and_map(d, f, tid, PT);
   reset_cov(d, f, tid, PT);
   if (reset_imu && tid == 0) {
@@ -579,8 +586,11 @@ __global__ void __launch_bounds__(PT) k_remove_cams(Dev d) {
   if (r0 < 0) return;
   extern __shared__ double srow[];     // [RB][ld]
   const int N = d.ncam[f], n = NI + 6 * N, ld = d.ld;
-  double* P = d.P + (size_t)f * ld * ld;
-  const int n2 = n - 12;
+  double* P = cov_of(d, f);
+  // the pruning update already wrote P without the two camera states (k_upd_dmma, stage 1): only the camera table is left
+  const int n2 = d.p_compacted[f] ? 0 : n - 12;
+  __syncthreads();
+  if (tid == 0) d.p_compacted[f] = 0;
   auto src_of = [&](int i) {   // new index -> old index
     if (i < NI + 6 * r0) return i;
     if (i < NI + 6 * (r1 - 1)) return i + 6;

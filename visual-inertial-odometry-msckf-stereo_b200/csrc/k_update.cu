@@ -171,7 +171,7 @@ void launch_compress_update(const Dev& d, int stage, cudaStream_t st) {
       if (c == 0 && stage == 1 && d.qr_tall_ok) launch_qr_tall(d, s);
       launch_qr_dmma_class(d, c, s);
       if (fk.on && s != sb) cudaStreamWaitEvent(s, fk.L->built, 0);
-      launch_upd_dmma_class(d, c, s);
+      launch_upd_dmma_class(d, c, s, stage);
     }
     // the tiled update only takes stacks k_qr_build compressed when every one-CTA class is available ...
     if (all_ok && stage != 1) launch_update_tiled(d, sb);

@@ -31,7 +31,7 @@ size_t upd_dmma_smem_bytes(int nmax, int KC) {
 }
 
 template <int KC, int DT>
-__global__ void __launch_bounds__(DT, KC > 64 ? 1 : 512 / DT) k_upd_dmma(Dev d, int cls) {
+__global__ void __launch_bounds__(DT, KC > 64 ? 1 : 512 / DT) k_upd_dmma(Dev d, int cls, int stage) {
   constexpr int LDX = KC + 4;
   constexpr int NKT = KC / 8;                  // row tiles at capacity
   constexpr int NW = DT / 32;                  // warps per CTA
@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(DT, KC > 64 ? 1 : 512 / DT) k_upd_dmma(Dev d, 
     const int ntn = (n + 7) >> 3;                // column tiles of the state part
     const int nct = (n + 8) >> 3;                // column tiles including the residual column n
     const double* A = d.A + (size_t)f * d.A_elems;
-    double* P = d.P + (size_t)f * ld * ld;
+    double* P = cov_of(d, f);
     const int* cm = d.colmap + (size_t)f * d.nmax;
 
     // ---- stage H_thin (zero padded), r and the column map
@@ -213,6 +213,13 @@ __global__ void __launch_bounds__(DT, KC > 64 ? 1 : 512 / DT) k_upd_dmma(Dev d, 
     __syncwarp();
 
     // ---- P <- P - W^T W : 16x16 warp tiles over the upper triangle, mirrored store
+    // In the pruning stage the two camera states being removed (msckf.py:803-815) are dropped on the way out: the result is
+    // written compacted into the filter's other covariance buffer, which becomes the current one (k_remove_cams then only
+    // compacts the camera table and P is not streamed a second time).
+    const bool compact = stage == 1 && d.rm_idx[2 * f] >= 0;
+    const int cs0 = compact ? NI + 6 * d.rm_idx[2 * f] : 1 << 30, cs1 = compact ? NI + 6 * d.rm_idx[2 * f + 1] : 1 << 30;
+    double* Pout = compact ? cov_other(d, f) : P;
+    auto cmap = [&](int i) { return i < cs0 ? i : (i < cs0 + 6 ? -1 : (i < cs1 ? i - 6 : (i < cs1 + 6 ? -1 : i - 12))); };
     const int nb = (n + 15) >> 4, nblk = nb * (nb + 1) / 2;
     // the P values of the warp's next tile are requested before this tile's DMMAs and stores (tiles are disjoint, and the
     // mirrored stores only touch the strict lower triangle, which nobody reads)
@@ -261,8 +268,11 @@ __global__ void __launch_bounds__(DT, KC > 64 ? 1 : 512 / DT) k_upd_dmma(Dev d, 
             const int a = a0 + 8 * x + g, b = b0 + 8 * y + 2 * tg + e;
             if (a < n && b < n && b >= a) {
               const double v = pv[x][y][e] - acc[x][y][e];
-              P[(size_t)a * ld + b] = v;
-              P[(size_t)b * ld + a] = v;
+              const int ma = cmap(a), mb = cmap(b);
+              if (ma >= 0 && mb >= 0) {
+                Pout[(size_t)ma * ld + mb] = v;
+                Pout[(size_t)mb * ld + ma] = v;
+              }
             }
           }
         }
@@ -272,11 +282,15 @@ __global__ void __launch_bounds__(DT, KC > 64 ? 1 : 512 / DT) k_upd_dmma(Dev d, 
         for (int y = 0; y < 2; ++y) { pv[x][y][0] = pn[x][y][0]; pv[x][y][1] = pn[x][y][1]; }
     }
     __syncthreads();
+    if (compact && tid == 0) {
+      d.Pcur[f] = Pout;
+      d.p_compacted[f] = 1;
+    }
   }
 }
 
 template <int KC, int DT>
-static void launch_upd_class(const Dev& d, int cls, int kid, cudaStream_t st) {
+static void launch_upd_class(const Dev& d, int cls, int kid, cudaStream_t st, int stage) {
   static DevOnce once;     // function attributes are per device
   once.run([&] {
     cudaFuncSetAttribute(k_upd_dmma<KC, DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
@@ -284,20 +298,20 @@ static void launch_upd_class(const Dev& d, int cls, int kid, cudaStream_t st) {
   const int sms = sm_count();
   const size_t sm = upd_dmma_smem_bytes(d.nmax, KC);
   const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(512 / DT, (224 * 1024) / (sm + 1024)));    // 128 registers per thread
-  KLAUNCH(d, kid, st, (k_upd_dmma<KC, DT><<<std::min(d.F, sms * per_sm), DT, sm, st>>>(d, cls)));
+  KLAUNCH(d, kid, st, (k_upd_dmma<KC, DT><<<std::min(d.F, sms * per_sm), DT, sm, st>>>(d, cls, stage)));
 }
 
 // update class c = compression class c: k, n_a + 1 <= 16 / 32 / 48 / 64 / 80
-void launch_upd_dmma_class(const Dev& d, int cls, cudaStream_t st) {
+void launch_upd_dmma_class(const Dev& d, int cls, cudaStream_t st, int stage) {
   if (!d.upd_dmma_ok[cls]) return;
-  if (cls == 0) launch_upd_class<16, 128>(d, 0, KID_UPD_DMMA16, st);
-  else if (cls == 1) launch_upd_class<32, 128>(d, 1, KID_UPD_DMMA32, st);
-  else if (cls == 2) launch_upd_class<48, 256>(d, 2, KID_UPD_DMMA48, st);
-  else if (cls == 3) launch_upd_class<64, 256>(d, 3, KID_UPD_DMMA64, st);
-  else launch_upd_class<80, 256>(d, 4, KID_UPD_DMMA80, st);       // n_a = 66 .. 78: one filter in a few thousand updates, but the tiled path costs it 0.3 ms
+  if (cls == 0) launch_upd_class<16, 128>(d, 0, KID_UPD_DMMA16, st, stage);
+  else if (cls == 1) launch_upd_class<32, 128>(d, 1, KID_UPD_DMMA32, st, stage);
+  else if (cls == 2) launch_upd_class<48, 256>(d, 2, KID_UPD_DMMA48, st, stage);
+  else if (cls == 3) launch_upd_class<64, 256>(d, 3, KID_UPD_DMMA64, st, stage);
+  else launch_upd_class<80, 256>(d, 4, KID_UPD_DMMA80, st, stage);       // n_a = 66 .. 78: one filter in a few thousand updates, but the tiled path costs it 0.3 ms
 }
 void launch_update_dmma(const Dev& d, Fork& fk) {
-  for (int c = 0; c < UPD_DMMA_CLASSES; ++c) launch_upd_dmma_class(d, c, fk.lane(c == 3 ? 0 : c + 1));
+  for (int c = 0; c < UPD_DMMA_CLASSES; ++c) launch_upd_dmma_class(d, c, fk.lane(c == 3 ? 0 : c + 1), 0);
 }
 
 }  // namespace msckf

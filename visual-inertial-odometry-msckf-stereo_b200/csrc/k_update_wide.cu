@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(WT, 2) k_wupd_T(Dev d) {
     const int na = d.n_act[f], mp = d.m_pad[f], ld = d.ld, tld = Tld(d), sld = d.Sld;
     const bool tri = d.m_rows[f] > na;
     const double* A = d.A + (size_t)f * d.A_elems;
-    const double* P = d.P + (size_t)f * ld * ld;
+    const double* P = cov_of(d, f);
     const int* cm = d.colmap + (size_t)f * d.nmax;
     __syncthreads();                                        // the previous tile's epilogue has read s_inv / s_cm
     if (tid < 64) s_inv[tid] = -1;
@@ -568,7 +568,7 @@ __global__ void __launch_bounds__(WT, 2) k_wupd_downdate(Dev d) {
     wide_gemm(rg, 0, k8,
               [&](int r) { return W + (size_t)r * tld + i0; }, min(64, tld - i0),
               [&](int r) { return W + (size_t)r * tld + j0; }, min(64, tld - j0), acc);
-    double* P = d.P + (size_t)f * ld * ld;
+    double* P = cov_of(d, f);
 #pragma unroll
     for (int mt = 0; mt < 4; ++mt) {
       const int a = i0 + wm * 32 + mt * 8 + g;

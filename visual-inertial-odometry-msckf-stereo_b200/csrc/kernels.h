@@ -135,7 +135,7 @@ void launch_qr_wide(const Dev& d, cudaStream_t st);               // k_qr_wide.c
 int qr_wide_rows_per_chunk(int Nmax);
 void launch_qr_dmma(const Dev& d, Fork& fk);               // k_qr_dmma.cu
 void launch_qr_dmma_class(const Dev& d, int cls, cudaStream_t st);
-void launch_upd_dmma_class(const Dev& d, int cls, cudaStream_t st);   // k_update_dmma.cu
+void launch_upd_dmma_class(const Dev& d, int cls, cudaStream_t st, int stage = 0);   // k_update_dmma.cu (stage 1: compacted output)
 void launch_compress_update(const Dev& d, int stage, cudaStream_t st); // QR + update of every class, each class on its own stream
 void launch_qr_tall(const Dev& d, cudaStream_t st);                    // k_qr_tall.cu
 void launch_qr_dense(const Dev& d, int filter, int mp_dense, cudaStream_t st);

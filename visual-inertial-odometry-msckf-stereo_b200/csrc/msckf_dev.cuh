@@ -83,7 +83,10 @@ struct Dev {
   unsigned long long* phys_used;   // [F] bit mask of physical slots in use
   int* obs_N;              // [F] camera-state count after this frame's augmentation (k_cam_slot), what k_observe sees
   int* obs_phys;           // [F] physical observation slot of the camera state being added (-1: window full)
-  double* P;               // [F][ld*ld] row-major, logical layout, n = 21+6*ncam
+  double* P;               // [2][F][ld*ld] two covariance buffers per filter, row-major, logical layout, n = 21+6*ncam
+  double** Pcur;           // [F] the buffer that holds filter f's covariance now: the pruning update writes its result
+                           // compacted (the two removed camera states dropped) into the other one and flips this pointer
+  unsigned char* p_compacted;      // [F] set by that update: k_remove_cams then only compacts the camera table
   // ---- landmark store (map_server)
   long long* f_id;         // [F][Fcap]
   unsigned long long* f_mask;      // [F][Fcap] bit = physical cam slot
@@ -176,6 +179,12 @@ struct Dev {
 };
 
 __host__ __device__ inline int Tld(const Dev& d) { return d.ld + 8; }
+// covariance of filter f
+__device__ __forceinline__ double* cov_of(const Dev& d, int f) { return d.Pcur[f]; }
+__device__ __forceinline__ double* cov_other(const Dev& d, int f) {
+  double* b0 = d.P + (size_t)f * d.ld * d.ld;
+  return d.Pcur[f] == b0 ? b0 + (size_t)d.F * d.ld * d.ld : b0;
+}
 // Pool record of a landmark that passed the gate: its projected Jacobian rows, row-major [4M-3][6M+1]
 // (six columns per observation in logical camera order, last column = projected residual).
 __host__ __device__ inline long long jac_record_doubles(int M) { return (long long)(4 * M - 3) * (6 * M + 1); }

@@ -345,6 +345,28 @@ def test_euroc_replay_through_publishers_vs_oracle(tmp_path):
     assert dataset.absolute_trajectory_error(est_t, est_p, ds.groundtruth) < 0.25
 
 
+def test_two_devices_in_one_process():
+    """Kernel attributes (dynamic shared-memory opt-in) and the SM count are per device: two contexts on two GPUs in one
+    process must both run the wide kernels.  Needs a box with at least two GPUs."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip('one GPU on this box')
+    n_frames = 24
+    stream = synth.make_stream(n_frames, 100, structure_seed=2, noise_seed=6)
+    outs = []
+    for dev in (1, 0):                      # the second device first: nothing may rely on device 0 having run before
+        cfg = ConfigEuRoC()
+        cfg._vio_max_cam_state_size__ = 16
+        filt = MSCKF(cfg, device=dev, feature_capacity=512)
+        try:
+            synth.drive(filt, stream)
+            outs.append(snapshot(filt))
+        finally:
+            filt.close()
+    assert np.array_equal(outs[0]['imu'], outs[1]['imu']) and np.array_equal(outs[0]['P'], outs[1]['P'])
+    assert np.array_equal(outs[0]['map_ids'], outs[1]['map_ids'])
+
+
 def test_graph_replay_equals_eager_on_ragged_frames(monkeypatch):
     """The captured frame graph is replayed with new message pointers every frame; its launch dimensions must not depend
     on the message.  Filters of one batch receive different numbers of features and IMU samples per frame (ragged

@@ -828,6 +828,7 @@ static int enqueue_frame(msckf_ctx* ctx, const FrameIn& in) {
     return MSCKF_OK;
   }
   k_set_frame_in<<<1, 1, 0, ctx->st>>>(d.frame_in, in);
+  CK(cudaGetLastError());
   if (!ctx->frame_graph) {
     long long before[KID_COUNT];
     memcpy(before, ctx->kt.launches, sizeof before);
@@ -839,10 +840,12 @@ static int enqueue_frame(msckf_ctx* ctx, const FrameIn& in) {
       ctx->graph_launches[i] = ctx->kt.launches[i] - before[i];
       ctx->kt.launches[i] = before[i];
     }
-    if (e != cudaSuccess || !g || cudaGraphInstantiate(&ctx->frame_graph, g, 0) != cudaSuccess) {
+    // a launch the runtime rejected during capture (KLAUNCH notes the first one) invalidates the graph as well
+    if (e != cudaSuccess || !g || ctx->kt.bad_launch >= 0 || cudaGraphInstantiate(&ctx->frame_graph, g, 0) != cudaSuccess) {
       cudaGetLastError();
       if (g) cudaGraphDestroy(g);
       ctx->frame_graph = nullptr;
+      ctx->kt.bad_launch = -1;
       ctx->graph_enabled = false;                   // capture not possible here: stay with plain launches
       enqueue_frame_eager(ctx, in, nullptr);
       return MSCKF_OK;

@@ -106,25 +106,28 @@ __global__ void __launch_bounds__(DT, KC > 64 ? 1 : 512 / DT) k_upd_dmma(Dev d, 
     // ---- S = T[:, act] R^T + sigma^2 I, lower tiles, kept in registers until every read of R is done
     const int nst = nkt * (nkt + 1) / 2;
     double sv0[S_PER_WARP], sv1[S_PER_WARP];
+    int sit, sjt;                                  // tile of this warp: decoded once, then stepped (tri_advance)
+    tri_decode(warp, sit, sjt);
 #pragma unroll
     for (int q = 0; q < S_PER_WARP; ++q) {
       sv0[q] = sv1[q] = 0.0;
       const int t = warp + NW * q;
       if (t < nst) {
-        int it, jt;
-        tri_decode(t, it, jt);
+        const int it = sit, jt = sjt;
+        tri_advance(sit, sjt, NW);
         const double* trow = sT + (8 * it + g) * ldT;
         const double* brow = sX + (8 * jt + g) * LDX + tg;
         for (int ks = tri ? 2 * jt : 0; ks < nks; ++ks) dmma884(sv0[q], sv1[q], trow[scm[4 * ks + tg]], brow[4 * ks]);
       }
     }
     __syncthreads();
+    tri_decode(warp, sit, sjt);
 #pragma unroll
     for (int q = 0; q < S_PER_WARP; ++q) {
       const int t = warp + NW * q;
       if (t < nst) {
-        int it, jt;
-        tri_decode(t, it, jt);
+        const int it = sit, jt = sjt;
+        tri_advance(sit, sjt, NW);
         const int row = 8 * it + g, col = 8 * jt + 2 * tg;
         sX[row * LDX + col] = sv0[q] + (row == col ? sigma2 : 0.0);
         sX[row * LDX + col + 1] = sv1[q] + (row == col + 1 ? sigma2 : 0.0);
@@ -165,6 +168,8 @@ __global__ void __launch_bounds__(DT, KC > 64 ? 1 : 512 / DT) k_upd_dmma(Dev d, 
       __syncthreads();
       // trailing update: T_i -= L_ip W_p ;  S_ij -= L_ip L_jp^T  (p < j <= i)
       const int nT = nbelow * nct, nS = nbelow * (nbelow + 1) / 2;
+      int tib = 0, tjb = 0;
+      bool tdec = false;
       for (int item = warp; item < nT + nS; item += DT / 32) {
         if (item < nT) {
           const int ib = item / nct, jt = item - ib * nct, it = p + 1 + ib;
@@ -179,8 +184,9 @@ __global__ void __launch_bounds__(DT, KC > 64 ? 1 : 512 / DT) k_upd_dmma(Dev d, 
           cp[0] = c0;
           cp[1] = c1;
         } else {
-          int ib, jb;
-          tri_decode(item - nT, ib, jb);
+          if (!tdec) { tri_decode(item - nT, tib, tjb); tdec = true; }
+          const int ib = tib, jb = tjb;
+          tri_advance(tib, tjb, DT / 32);
           const int it = p + 1 + ib, jt = p + 1 + jb;
           const double* lrow = sX + (8 * it + g) * LDX + p0 + tg;
           const double a0 = -lrow[0], a1 = -lrow[4];
@@ -224,9 +230,7 @@ __global__ void __launch_bounds__(DT, KC > 64 ? 1 : 512 / DT) k_upd_dmma(Dev d, 
     // the P values of the warp's next tile are requested before this tile's DMMAs and stores (tiles are disjoint, and the
     // mirrored stores only touch the strict lower triangle, which nobody reads)
     double pv[2][2][2], pn[2][2][2];
-    auto load_tile = [&](int item, double (&o)[2][2][2]) {
-      int bj, bi;
-      tri_decode(item, bj, bi);
+    auto load_tile = [&](int bj, int bi, double (&o)[2][2][2]) {
 #pragma unroll
       for (int x = 0; x < 2; ++x)
 #pragma unroll
@@ -236,12 +240,14 @@ __global__ void __launch_bounds__(DT, KC > 64 ? 1 : 512 / DT) k_upd_dmma(Dev d, 
           o[x][y][1] = (a < n && b + 1 < n) ? P[(size_t)a * ld + b + 1] : 0.0;
         }
     };
-    if (warp < nblk) load_tile(warp, pv);
+    int dbj, dbi;                                  // this warp's tile (bi <= bj), stepped from tile to tile
+    tri_decode(warp, dbj, dbi);
+    if (warp < nblk) load_tile(dbj, dbi, pv);
     for (int item = warp; item < nblk; item += DT / 32) {
-      int bj, bi;
-      tri_decode(item, bj, bi);                  // bi <= bj
+      const int bj = dbj, bi = dbi;
+      tri_advance(dbj, dbi, DT / 32);
       const int a0 = 16 * bi, b0 = 16 * bj;
-      if (item + DT / 32 < nblk) load_tile(item + DT / 32, pn);
+      if (item + DT / 32 < nblk) load_tile(dbj, dbi, pn);
       double acc[2][2][2];
 #pragma unroll
       for (int x = 0; x < 2; ++x)

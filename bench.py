@@ -81,7 +81,7 @@ def parse():
     ap.add_argument('--no-c3', action='store_true')
     ap.add_argument('--no-c5', action='store_true')
     ap.add_argument('--no-strong', action='store_true')
-    ap.add_argument('--c5-filters', type=int, default=32)
+    ap.add_argument('--c5-filters', type=int, default=128)
     ap.add_argument('--only', default='', help='development: comma list of c3,c5 -- run just these legs and print them')
     return ap.parse_args()
 

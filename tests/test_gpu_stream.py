@@ -345,6 +345,40 @@ def test_euroc_replay_through_publishers_vs_oracle(tmp_path):
     assert dataset.absolute_trajectory_error(est_t, est_p, ds.groundtruth) < 0.25
 
 
+def test_batch_of_different_sequences_ragged():
+    """MSCKFBatch.feature_callback_ragged: the filters of one context follow DIFFERENT sequences (own landmark fields, own
+    feature counts and ids per frame); each equals the single-filter drop-in run on its own stream."""
+    F, n_frames, max_cam = 3, 28, 7
+    streams = [synth.make_stream(n_frames, 60 + 25 * k, structure_seed=20 + k, noise_seed=40 + k) for k in range(F)]
+    dcfg = ConfigEuRoC()
+    dcfg._vio_max_cam_state_size__ = max_cam
+    batch = MSCKFBatch(dcfg, F, feature_capacity=512)
+    try:
+        batch.initialize_gravity_and_bias(np.stack([s.gyro[:200] for s in streams]), np.stack([s.acc[:200] for s in streams]))
+        for f in range(n_frames):
+            rng = [s.imu_range_for_frame(f) for s in streams]
+            batch.feature_callback_ragged(float(streams[0].frame_ts[f]), [s.imu_ts[a:b] for s, (a, b) in zip(streams, rng)],
+                                          [s.gyro[a:b] for s, (a, b) in zip(streams, rng)], [s.acc[a:b] for s, (a, b) in zip(streams, rng)],
+                                          [s.frame_ids[f] for s in streams], [s.frame_uv[f] for s in streams])
+        got = [(batch.ctx.get_imu_state(k), batch.ctx.get_cov(k), batch.ctx.get_cam_states(k)[0],
+                batch.ctx.get_features(k, with_obs=False)[0]) for k in range(F)]
+    finally:
+        batch.close()
+    assert len(set(len(g[3]) for g in got)) > 1               # the maps really differ in size
+    for k in range(F):
+        single = MSCKF(dcfg, feature_capacity=512)
+        try:
+            synth.drive(single, streams[k])
+            s1 = snapshot(single)
+        finally:
+            single.close()
+        b = got[k][0]
+        imu = np.concatenate([b[capi.IMU_Q:capi.IMU_Q + 4], b[capi.IMU_BG:capi.IMU_BG + 3], b[capi.IMU_V:capi.IMU_V + 3],
+                              b[capi.IMU_BA:capi.IMU_BA + 3], b[capi.IMU_P:capi.IMU_P + 3]])
+        assert rel_err(imu, s1['imu']) < 1e-12 and rel_err(got[k][1], s1['P']) < 1e-12
+        assert np.array_equal(got[k][2], s1['cam_ids']) and np.array_equal(got[k][3], s1['map_ids'])
+
+
 def test_two_devices_in_one_process():
     """Kernel attributes (dynamic shared-memory opt-in) and the SM count are per device: two contexts on two GPUs in one
     process must both run the wide kernels.  Needs a box with at least two GPUs."""

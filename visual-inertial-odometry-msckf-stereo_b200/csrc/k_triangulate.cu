@@ -125,8 +125,11 @@ __device__ bool lm_solve(const Views& V, int nv, const TriCfg& cfg, const double
     }
     const double r0 = u1 - V.at(12, v), r1 = u2 - V.at(13, v);
     const double e2 = r0 * r0 + r1 * r1;
-    // Huber weight eps / (2 e): e only enters through 1 / e
-    const double w = (e2 <= cfg.eps * cfg.eps) ? 1.0 : 0.5 * cfg.eps * rsqrt(e2);
+    // Huber weight eps / (2 e): e only enters through 1 / e.  The reference branches on e <= eps (feature.py:91-95), e = sqrt(e2):
+    // comparing the squares decides the same way except within rounding of eps^2, where the square root is taken as written.
+    const double t2 = cfg.eps * cfg.eps;
+    const bool inside = (e2 < t2 * (1.0 - 1e-15)) || (e2 <= t2 * (1.0 + 1e-15) && sqrt(e2) <= cfg.eps);
+    const double w = inside ? 1.0 : 0.5 * cfg.eps * rsqrt(e2);
     const double ww = w * w;
     for (int i = 0; i < 3; ++i) {
       const double s0 = ww * J0[i], s1 = ww * J1[i];

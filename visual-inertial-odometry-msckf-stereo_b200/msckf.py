@@ -440,6 +440,41 @@ class MSCKFBatch(object):
         self.ctx.feature_callback_async(imu_off, np.tile(ts, F), gyro, acc, cam_ids, feat_off,
                                         np.tile(np.asarray(ids, dtype=np.int64), F), uv)
 
+    def feature_callback_ragged(self, frame_time, imu_ts, gyro, acc, ids, uv):
+        """One frame with per-filter messages (filters that follow different sequences): ``imu_ts[f]`` [K_f], ``gyro[f]`` /
+        ``acc[f]`` [K_f][3] are filter f's not yet consumed IMU samples up to ``frame_time[f]`` (a scalar serves all),
+        ``ids[f]`` [n_f] / ``uv[f]`` [n_f][4] its feature message.  The message selection of batch_imu_processing
+        (msckf.py:267-281) runs per filter.  Returns (imu blocks [F][48], did_reset [F])."""
+        F = self.F
+        ft = np.broadcast_to(np.asarray(frame_time, dtype=np.float64), (F,))
+        if self.is_first_img:
+            self.is_first_img = False
+            self.imu_time = None
+            self._imu_time_f = ft.copy()
+            blocks = self.ctx.get_imu_states()
+            for f in range(F):
+                blocks[f, IMU_TIME] = ft[f]
+                self.ctx.set_imu_state(f, blocks[f])
+        elif getattr(self, '_imu_time_f', None) is None:
+            self._imu_time_f = np.full(F, self.imu_time, dtype=np.float64)
+        imu_off, feat_off, ts_l, gy_l, ac_l = [0], [0], [], [], []
+        for f in range(F):
+            t = np.asarray(imu_ts[f], dtype=np.float64)
+            take = (t >= self._imu_time_f[f]) & (t <= ft[f])
+            if take.any():
+                self._imu_time_f[f] = float(t[take][-1])
+            ts_l.append(t[take])
+            gy_l.append(np.asarray(gyro[f], dtype=np.float64).reshape(-1, 3)[take])
+            ac_l.append(np.asarray(acc[f], dtype=np.float64).reshape(-1, 3)[take])
+            imu_off.append(imu_off[-1] + int(take.sum()))
+            feat_off.append(feat_off[-1] + len(ids[f]))
+        cam_ids = np.full(F, self.next_imu_id, dtype=np.int64)
+        self.next_imu_id += 1
+        cat = lambda xs, shape: np.concatenate(xs) if len(xs) and sum(len(x) for x in xs) else np.zeros(shape)   # noqa: E731
+        return self.ctx.feature_callback(imu_off, cat(ts_l, (0,)), cat(gy_l, (0, 3)), cat(ac_l, (0, 3)), cam_ids, feat_off,
+                                         np.concatenate([np.asarray(i, dtype=np.int64) for i in ids]),
+                                         np.concatenate([np.asarray(u, dtype=np.float64).reshape(-1, 4) for u in uv]))
+
     def collect(self):
         return self.ctx.collect()
 

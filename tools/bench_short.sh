@@ -1,6 +1,3 @@
-python bench.py --steps 60 --no-latency --no-cpu-baseline 2>/dev/null | python -c "
-import sys,json
-for x in sys.stdin:
-    if x.startswith('{'):
-        j=json.loads(x); print(round(j['value']/1e6,2), round(j['ms_per_step'],4), round(j['e2e']['value']/1e6,2), j['clocks']['sm_mhz']); print({k: round(v['ms']/20,3) for k,v in j['roofline']['families'].items()})
-        print(' '.join('%s=%.0f' % (k.replace('k_',''), v['ms']/20*1e3) for k,v in sorted(j['roofline']['all_kernels'].items(), key=lambda kv:-kv[1]['ms'])))"
+#!/bin/bash
+# headline numbers only (no CPU legs, no configs[2] / configs[4] legs), printed in readable form
+python bench.py --steps 20 --warmup 5 --no-latency --no-cpu-baseline --no-c3 --no-c5 --no-parity-spot > /tmp/bench_short.json && python tools/show_legs.py /tmp/bench_short.json

@@ -1,26 +1,20 @@
 """Scratch: histogram of the measurement-update shapes (m, n_a, k, kernel path) per stage at the headline workload,
 plus per-stage device times.  usage: python tools/update_shapes.py [F]"""
-import os, sys
+import sys
+
 import numpy as np
-REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, REPO)
-import bench
-from msckf_b200 import capi, synth
-from msckf_b200.config import ConfigEuRoC
-from msckf_b200.msckf import MSCKFBatch
+
+from _stream import make_batch, host_copy, KEYS
+
 F = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 NF = 130
-cfg = ConfigEuRoC(); cfg._vio_max_cam_state_size__ = 20
-st = synth.make_structure(NF, 300, structure_seed=0)
-gyro, acc, uvs = bench.build_frames(st, np.random.default_rng(1000), F, NF)
-b = MSCKFBatch(cfg, F, device=0, feature_capacity=1024)
-b.initialize_gravity_and_bias(gyro[:, :200], acc[:, :200])
+b, st, frames = make_batch(F, NF)
 ctx = b.ctx
 hist = {0: [], 1: []}
 for f in range(NF):
-    a = bench.frame_arrays(b, st, gyro, acc, uvs, f)
+    a = dict(zip(KEYS, host_copy(frames[f])))
     if f < 90:
-        ctx.feature_callback(*[a[k] for k in bench.KEYS])
+        ctx.feature_callback(*[a[k] for k in KEYS])
         continue
     ctx.propagate(a['imu_off'], a['ts'], a['gyro'], a['acc'])
     ctx.augment(a['cam_ids'])

@@ -564,7 +564,7 @@ __device__ __forceinline__ unsigned long long logical_mask(const Dev& d, int f, 
 
 // Small tracks: one group of G lanes per landmark, persistent grid over the work list wl_jac_small[0 .. n).
 template <int G>
-__global__ void __launch_bounds__(JAC_WARPS * 32, 8) k_jacobian_gate_small(Dev d, int cls, int per_group_doubles, int write_all) {
+__global__ void __launch_bounds__(JAC_WARPS * 32, G == 32 ? 3 : 8) k_jacobian_gate_small(Dev d, int cls, int per_group_doubles, int write_all) {
   extern __shared__ double smem[];
   constexpr int GPW = 32 / G;                       // groups per warp
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;

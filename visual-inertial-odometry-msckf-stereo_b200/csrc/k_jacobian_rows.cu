@@ -76,7 +76,7 @@ __device__ __forceinline__ void jr_row(const double* __restrict__ pre, const dou
 
 // registers: the projected row (6M), its product with Pcc (6M) and the row of S (4M-3) live in registers per lane
 template <int M>
-constexpr int jr_ctas_per_sm() { return M == 2 ? 6 : (M == 3 ? 4 : 3); }
+constexpr int jr_ctas_per_sm() { return M == 2 ? 5 : (M == 3 ? 4 : 3); }
 
 template <int M, int G>
 __global__ void __launch_bounds__(JR_T, jr_ctas_per_sm<M>()) k_jacobian_rows(Dev d, int cls, int write_all) {
@@ -289,7 +289,7 @@ static void launch_rows(const Dev& d, int cls, int write_all, cudaStream_t st) {
     cudaFuncSetAttribute(k_jacobian_rows<M, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   });
   const int sms = sm_count();
-  int per_sm = (int)std::min<size_t>(2 * jr_ctas_per_sm<M>(), (220 * 1024) / (smem + 1024));
+  int per_sm = (int)std::min<size_t>(jr_ctas_per_sm<M>(), (220 * 1024) / (smem + 1024));   // one resident wave: every group walks a contiguous piece of the list
   per_sm = std::max(per_sm, 1);
   KLAUNCH(d, KID_JACOBIAN_ROWS, st, (k_jacobian_rows<M, G><<<sms * per_sm, JR_T, smem, st>>>(d, cls, write_all)));
 }

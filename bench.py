@@ -82,6 +82,7 @@ def parse():
     ap.add_argument('--no-c5', action='store_true')
     ap.add_argument('--no-strong', action='store_true')
     ap.add_argument('--c5-filters', type=int, default=128)
+    ap.add_argument('--groups', type=int, default=0, help='contexts (streams) a GPU\'s filters are spread over; 0 = the library default (2 from 1024 filters on)')
     ap.add_argument('--only', default='', help='development: comma list of c3,c5 -- run just these legs and print them')
     return ap.parse_args()
 
@@ -644,7 +645,7 @@ def measure_batch(args, torch, dist, world, rank, local, F, seed0, K, W, R, with
     cfg = ConfigEuRoC()
     cfg._vio_max_cam_state_size__ = args.max_cam
     st = get_structure(n_frames, args.feats)
-    batch = MSCKFBatch(cfg, F, device=local, feature_capacity=1024)
+    batch = MSCKFBatch(cfg, F, device=local, feature_capacity=1024, groups=(args.groups or None))
     ctx = batch.ctx
     ds = DeviceStream(st, batch, F, seed0, local, torch)
     g0, a0 = ds.static_samples()
@@ -662,7 +663,7 @@ def measure_batch(args, torch, dist, world, rank, local, F, seed0, K, W, R, with
         if first_e2e <= f < first_prof:
             host_frames[f] = to_pinned(d, torch)      # e2e frames live in page-locked HOST memory
         else:
-            dev_frames[f] = d                         # everything else stays in HBM
+            dev_frames[f] = (d, batch.device_frame_parts(d, KEYS))   # everything else stays in HBM
         if spot and f < first_e2e:
             ts, ids = ds.plan[f]
             gy, ac, uv = d['gyro'][spot].cpu().numpy(), d['acc'][spot].cpu().numpy(), d['uv'][spot].cpu().numpy()
@@ -671,9 +672,8 @@ def measure_batch(args, torch, dist, world, rank, local, F, seed0, K, W, R, with
     traj = torch.zeros((K * R, F, capi.IMU_STRIDE), dtype=torch.float64, device=dev)
     torch.cuda.synchronize()
 
-    def run_dev(f, out_ptr=0):
-        d = dev_frames[f]
-        ctx.feature_callback_dev(*[d[k].data_ptr() for k in KEYS], imu_out=out_ptr)
+    def run_dev(f, out=None):
+        batch.feature_callback_dev(dev_frames[f][1], out)
 
     # ---- lead-in: fills the camera window, then keeps running the job's own frames until the clocks have settled
     sampler = ClockSampler(local)
@@ -691,7 +691,7 @@ def measure_batch(args, torch, dist, world, rank, local, F, seed0, K, W, R, with
         barrier()
         ctx.mark(0)
         for i in range(K):
-            run_dev(first_dev + b * K + i, traj[b * K + i].data_ptr())
+            run_dev(first_dev + b * K + i, traj[b * K + i])
         ctx.mark(1)
         ms = ctx.mark_elapsed_ms()
         ctx.sync()
@@ -748,7 +748,12 @@ def measure_batch(args, torch, dist, world, rank, local, F, seed0, K, W, R, with
         kt0 = ctx.kernel_times()
         c4 = ctx.counters().sum(axis=0)
         for f in range(first_prof, n_frames):
-            run_dev(f)
+            if batch.groups == 1:
+                run_dev(f)
+            else:                                     # per-kernel event times want the GPU to themselves: one context at a time
+                for g, part in enumerate(ctx.parts):
+                    part.feature_callback_dev(*dev_frames[f][1][g])
+                    part.sync()
         ctx.sync()
         kt1 = ctx.kernel_times()
         ctx.set_kernel_timing(False)
@@ -779,7 +784,7 @@ def measure_batch(args, torch, dist, world, rank, local, F, seed0, K, W, R, with
     med = int(np.argsort(tms)[len(tms) // 2])
     emed = int(np.argsort(ets)[len(ets) // 2])
     Ftot = rsum(float(F))
-    res = {'label': label, 'filters_local': F, 'filters_total': int(Ftot), 'seed0': seed0,
+    res = {'label': label, 'filters_local': F, 'filters_total': int(Ftot), 'seed0': seed0, 'contexts_per_gpu': batch.groups,
            'value': float(vals[med]), 'ms_per_step': float(tms[med] / K),
            'blocks': {'n': R, 'steps_per_block': K, 'timed_seconds': float(tms.sum() * 1e-3), 'ms_per_step_min': float(tms.min() / K),
                       'ms_per_step_max': float(tms.max() / K), 'value_min': float(vals.min()), 'value_max': float(vals.max()),
@@ -880,7 +885,7 @@ def run_b200(args):
         spot = res.pop('spot')
         line = {'metric': METRIC, 'value': res['value'], 'unit': UNIT, 'n_gpus': world, 'steps': K, 'warmup': W, 'ms_per_step': res['ms_per_step'],
                 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic (generated on the GPU)',
-                'config': workload_config(args, world), 'blocks': res['blocks'],
+                'config': dict(workload_config(args, world), contexts_per_gpu=res['contexts_per_gpu']), 'blocks': res['blocks'],
                 'filter_frames_per_s': res['filter_frames_per_s'], 'feature_updates_per_step': res['feature_updates_per_step'],
                 'e2e': res['e2e'], 'gpu_launches': res['gpu_launches'], 'clocks': res['clocks'], 'roofline': roofline, 'ate': res['ate'],
                 'online_resets': res['online_resets'], 'gate_not_spd': res['gate_not_spd'],
@@ -891,6 +896,7 @@ def run_b200(args):
             line['strong'] = {'filters_total': strong['filters_total'], 'filters_per_gpu': strong['filters_local'], 'value': strong['value'],
                               'ms_per_step': strong['ms_per_step'], 'e2e': strong['e2e'], 'blocks': strong['blocks'],
                               'filter_frames_per_s': strong['filter_frames_per_s'], 'ate': strong['ate'],
+                              'contexts_per_gpu': strong['contexts_per_gpu'],
                               'config': workload_config(args, world, TOTAL_FILTERS)['workload']}
         elif world == 1 and F == TOTAL_FILTERS:
             line['strong'] = {'filters_total': TOTAL_FILTERS, 'filters_per_gpu': F, 'value': res['value'], 'ms_per_step': res['ms_per_step'],

@@ -314,6 +314,9 @@ int msckf_fp64_peak(int32_t device, double* dfma_tflops, double* dmma_tflops);
  * msckf_mark(ctx, 0) ... msckf_mark(ctx, 1); msckf_mark_elapsed waits for mark 1 and returns the milliseconds. */
 int msckf_mark(msckf_ctx* ctx, int32_t which);
 int msckf_mark_elapsed(msckf_ctx* ctx, float* ms);
+/* The same across two contexts of one device (a batch split over several contexts, each with its own stream):
+ * waits for mark 1 of `last` and returns the milliseconds since mark 0 of `first`. */
+int msckf_mark_elapsed_between(msckf_ctx* first, msckf_ctx* last, float* ms);
 
 /* Library build info, e.g. "msckf_b200 sm_100a cuda 12.9". */
 const char* msckf_version(void);

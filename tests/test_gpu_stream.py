@@ -294,6 +294,79 @@ def test_two_frames_in_flight_equal_sequential():
         assert np.array_equal(outs['blocking'][1][k], outs['pipelined'][1][k])
 
 
+def test_filter_groups_equal_one_context():
+    """A batch spread over two contexts (MSCKFBatch(groups=2), uneven split 3 + 2) returns bit for bit what one context
+    returns: through the blocking host call, through device-resident messages (device_frame_parts) and through the staged
+    calls, with ragged per-filter message lengths."""
+    import torch
+    F, n_frames, max_cam = 5, 26, 6
+    st = synth.make_structure(n_frames, 70, structure_seed=9)
+    streams = [synth.realize(st, noise_seed=300 + k) for k in range(F)]
+    dcfg = ConfigEuRoC()
+    dcfg._vio_max_cam_state_size__ = max_cam
+    s0 = streams[0]
+    keys = ['imu_off', 'ts', 'gyro', 'acc', 'cam_ids', 'feat_off', 'ids', 'uv']
+
+    def frame_args(batch, f):
+        """ragged: filter k drops its last k features of the frame"""
+        a, b = s0.imu_range_for_frame(f)
+        take = batch.select_imu(float(s0.frame_ts[f]), s0.imu_ts[a:b])
+        ts = s0.imu_ts[a:b][take]
+        K = len(ts)
+        cam_id = batch.next_imu_id
+        batch.next_imu_id += 1
+        ns = [max(0, len(s0.frame_ids[f]) - k) for k in range(F)]
+        return [(np.arange(F + 1) * K).astype(np.int32), np.tile(ts, F),
+                np.ascontiguousarray(np.stack([s.gyro[a:b][take] for s in streams])),
+                np.ascontiguousarray(np.stack([s.acc[a:b][take] for s in streams])),
+                np.full(F, cam_id, dtype=np.int64), np.concatenate([[0], np.cumsum(ns)]).astype(np.int32),
+                np.concatenate([s0.frame_ids[f][:n].astype(np.int64) for n in ns]),
+                np.concatenate([s.frame_uv[f][:n].reshape(-1, 4) for s, n in zip(streams, ns)])]
+
+    outs = {}
+    for mode, groups in (('one', 1), ('host', 2), ('device', 2), ('staged', 2)):
+        batch = MSCKFBatch(dcfg, F, feature_capacity=256, groups=groups)
+        try:
+            assert batch.groups == groups and batch.ctx.F == F
+            batch.initialize_gravity_and_bias(np.stack([s.gyro[:200] for s in streams]), np.stack([s.acc[:200] for s in streams]))
+            res = []
+            for f in range(n_frames):
+                args = frame_args(batch, f)
+                if mode in ('one', 'host'):
+                    imu, rst = batch.ctx.feature_callback(*args)
+                elif mode == 'device':
+                    d = dict((k, torch.from_numpy(np.ascontiguousarray(v)).cuda()) for k, v in zip(keys, args))
+                    out = torch.zeros((F, capi.IMU_STRIDE), dtype=torch.float64, device='cuda')
+                    batch.feature_callback_dev(batch.device_frame_parts(d, keys), out)
+                    batch.ctx.sync()
+                    imu, rst = out.cpu().numpy(), np.zeros(F, dtype=bool)
+                else:
+                    c = batch.ctx
+                    c.propagate(*args[:4])
+                    c.augment(args[4])
+                    c.add_observations(*args[5:])
+                    c.remove_lost_features()
+                    c.prune_cam_states()
+                    rst = c.online_reset()
+                    imu = c.get_imu_states()
+                assert not rst.any()
+                res.append(imu)
+            cnt = batch.ctx.counters()
+            assert cnt.shape[0] == F and batch.ctx.update_shapes().shape[0] == F and batch.ctx.kernel_launches() > 0
+            outs[mode] = (np.array(res), [batch.ctx.get_cov(k) for k in range(F)], [batch.ctx.get_cam_states(k)[0] for k in range(F)],
+                          [batch.ctx.get_features(k, with_obs=False)[0] for k in range(F)], cnt[:, capi.CNT_FEATURE_UPDATES])
+        finally:
+            batch.close()
+    assert outs['one'][4].sum() > 100
+    for mode in ('host', 'device', 'staged'):
+        assert np.array_equal(outs['one'][0], outs[mode][0]), mode
+        assert np.array_equal(outs['one'][4], outs[mode][4]), mode
+        for k in range(F):
+            assert np.array_equal(outs['one'][1][k], outs[mode][1][k]), (mode, k)
+            assert np.array_equal(outs['one'][2][k], outs[mode][2][k]), (mode, k)
+            assert np.array_equal(outs['one'][3][k], outs[mode][3][k]), (mode, k)
+
+
 def test_euroc_replay_through_publishers_vs_oracle(tmp_path):
     """a sequence on disk in the EuRoC layout, replayed by two DataPublisher threads into queues and consumed
     the way vio.py does (IMU thread -> imu_callback, image thread -> feature_callback), drives the CUDA drop-in; the oracle

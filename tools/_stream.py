@@ -14,13 +14,13 @@ from msckf_b200.msckf import MSCKFBatch  # noqa: E402
 KEYS = bench.KEYS
 
 
-def make_batch(F, n_frames, structure=None, seed0=0, max_cam=20, feats=300, device=0):
+def make_batch(F, n_frames, structure=None, seed0=0, max_cam=20, feats=300, device=0, groups=1):
     """(batch, structure, device frames): a context of F filters (noise seeds seed0 ..) with gravity initialised and the
     messages of n_frames frames resident in HBM."""
     cfg = ConfigEuRoC()
     cfg._vio_max_cam_state_size__ = max_cam
     st = structure if structure is not None else synth.make_structure(n_frames, feats, structure_seed=0)
-    batch = MSCKFBatch(cfg, F, device=device, feature_capacity=1024)
+    batch = MSCKFBatch(cfg, F, device=device, feature_capacity=1024, groups=groups)
     ds = bench.DeviceStream(st, batch, F, seed0, device, torch)
     g0, a0 = ds.static_samples()
     batch.initialize_gravity_and_bias(g0, a0)

@@ -31,7 +31,7 @@ rt = torch.cuda.cudart()
 def batch_frames(F, max_cam, st, n_lead, n_prof, fcap):
     cfg = ConfigEuRoC()
     cfg._vio_max_cam_state_size__ = max_cam
-    batch = MSCKFBatch(cfg, F, device=0, feature_capacity=fcap)
+    batch = MSCKFBatch(cfg, F, device=0, feature_capacity=fcap, groups=1)
     ds = bench.DeviceStream(st, batch, F, 0, 0, torch)
     g0, a0 = ds.static_samples()
     batch.initialize_gravity_and_bias(g0, a0)

@@ -112,6 +112,7 @@ SIGNATURES = {
     'msckf_fp64_peak': [_I, _P, _P],
     'msckf_mark': [_P, _I],
     'msckf_mark_elapsed': [_P, _P],
+    'msckf_mark_elapsed_between': [_P, _P, _P],
     'msckf_version': [],
     'msckf_undistort_points': [_I, _I, _P, _P, _I, _P, _P, _P, _P],
     'msckf_undistort_stereo': [_I, _I, _P, _P, _P, _I, _P, _P, _I, _P, _P],
@@ -513,6 +514,166 @@ class Context(object):
         ms = np.zeros(5, dtype=np.float32)
         self._ck(self.lib.msckf_last_timing(self.h, _ptr(ms)))
         return ms
+
+
+class ContextGroup(object):
+    """F filters spread over G contexts (each with its own CUDA stream, work lists and frame graph) behind the interface of
+    one ``Context``: per-filter calls go to the context that owns the filter, batch calls are split at the group
+    boundaries (ragged offsets rebased) and enqueued on every group before anything is waited for, so the kernels of the
+    groups interleave on the GPU: the tail of one group's launch (a launch lasts as long as its longest filter) is filled
+    by the other group's CTAs.  Filters are independent, so the results do not depend on the grouping."""
+
+    PER_FILTER = ('set_imu_state', 'get_imu_state', 'get_cam_states', 'set_cam_states', 'n_state', 'get_cov', 'set_cov',
+                  'get_features', 'set_features', 'set_feature_position', 'reset', 'stage_log', 'feature_jacobian',
+                  'measurement_jacobian', 'gating_test', 'measurement_update', 'find_redundant_cam_states')
+
+    def __init__(self, cconfigs):
+        self.parts = []
+        try:
+            for c in cconfigs:
+                self.parts.append(Context(c))
+        except Exception:
+            self.close()
+            raise
+        self.lib = self.parts[0].lib
+        self.bounds = np.concatenate([[0], np.cumsum([p.F for p in self.parts])]).astype(np.int64)
+        self.F = int(self.bounds[-1])
+        self.max_cam = self.parts[0].max_cam
+        self.feature_capacity = self.parts[0].feature_capacity
+        for name in self.PER_FILTER:
+            setattr(self, name, self._route(name))
+
+    def _route(self, name):
+        def call(f=0, *a, **kw):
+            g = int(np.searchsorted(self.bounds, f, side='right')) - 1
+            if not (0 <= f < self.F):
+                raise MsckfCudaError(ERR_ARG, 'filter index %d outside 0..%d' % (f, self.F - 1))
+            return getattr(self.parts[g], name)(int(f - self.bounds[g]), *a, **kw)
+        call.__name__ = name
+        return call
+
+    def ranges(self):
+        return [(int(self.bounds[g]), int(self.bounds[g + 1])) for g in range(len(self.parts))]
+
+    def close(self):
+        for p in self.parts:
+            p.close()
+
+    def sync(self):
+        for p in self.parts:
+            p.sync()
+
+    # ---- splitting of ragged batch arguments
+    def _split_imu(self, imu_off, ts, gyro, acc):
+        ts = np.asarray(ts, dtype=np.float64).reshape(-1)
+        gyro = np.asarray(gyro, dtype=np.float64).reshape(-1, 3)
+        acc = np.asarray(acc, dtype=np.float64).reshape(-1, 3)
+        o = np.asarray(imu_off)
+        out = []
+        for a, b in self.ranges():
+            lo, hi = int(o[a]), int(o[b])
+            out.append(((o[a:b + 1] - lo).astype(np.int32), ts[lo:hi], gyro[lo:hi], acc[lo:hi]))
+        return out
+
+    def _split_feat(self, feat_off, ids, uv):
+        ids = np.asarray(ids, dtype=np.int64).reshape(-1)
+        uv = np.asarray(uv, dtype=np.float64).reshape(-1, 4)
+        o = np.asarray(feat_off)
+        out = []
+        for a, b in self.ranges():
+            lo, hi = int(o[a]), int(o[b])
+            out.append(((o[a:b + 1] - lo).astype(np.int32), ids[lo:hi], uv[lo:hi]))
+        return out
+
+    # ---- stages
+    def propagate(self, imu_off, ts, gyro, acc):
+        for p, a in zip(self.parts, self._split_imu(imu_off, ts, gyro, acc)):
+            p.propagate(*a)
+
+    def augment(self, cam_ids):
+        cam_ids = np.asarray(cam_ids, dtype=np.int64)
+        for p, (a, b) in zip(self.parts, self.ranges()):
+            p.augment(cam_ids[a:b])
+
+    def add_observations(self, feat_off, ids, uv):
+        for p, a in zip(self.parts, self._split_feat(feat_off, ids, uv)):
+            p.add_observations(*a)
+
+    def remove_lost_features(self):
+        for p in self.parts:
+            p.remove_lost_features()
+
+    def prune_cam_states(self):
+        for p in self.parts:
+            p.prune_cam_states()
+
+    def online_reset(self):
+        return np.concatenate([p.online_reset() for p in self.parts])
+
+    def feature_callback(self, imu_off, ts, gyro, acc, cam_ids, feat_off, ids, uv):
+        self.feature_callback_async(imu_off, ts, gyro, acc, cam_ids, feat_off, ids, uv)
+        return self.collect()
+
+    def feature_callback_async(self, imu_off, ts, gyro, acc, cam_ids, feat_off, ids, uv):
+        cam_ids = np.asarray(cam_ids, dtype=np.int64)
+        imu = self._split_imu(imu_off, ts, gyro, acc)
+        feat = self._split_feat(feat_off, ids, uv)
+        for g, (p, (a, b)) in enumerate(zip(self.parts, self.ranges())):
+            p.feature_callback_async(imu[g][0], imu[g][1], imu[g][2], imu[g][3], cam_ids[a:b], feat[g][0], feat[g][1], feat[g][2])
+
+    def collect(self):
+        r = [p.collect() for p in self.parts]
+        return np.concatenate([x[0] for x in r]), np.concatenate([x[1] for x in r])
+
+    def feature_callback_dev(self, *a, **kw):
+        raise MsckfCudaError(ERR_ARG, 'a context group takes one set of device addresses per group: feature_callback_dev_parts')
+
+    def feature_callback_dev_parts(self, args_per_group, imu_out_per_group=None):
+        """``args_per_group[g]`` = the eight device addresses of group g's messages (offsets rebased to the group),
+        ``imu_out_per_group[g]`` = where its IMU blocks go (0: nowhere)."""
+        for g, p in enumerate(self.parts):
+            p.feature_callback_dev(*args_per_group[g], imu_out=(imu_out_per_group[g] if imu_out_per_group else 0))
+
+    # ---- read-backs over all filters
+    def get_imu_states(self):
+        return np.concatenate([p.get_imu_states() for p in self.parts])
+
+    def counters(self):
+        return np.concatenate([p.counters() for p in self.parts])
+
+    def update_shapes(self):
+        return np.concatenate([p.update_shapes() for p in self.parts])
+
+    def kernel_launches(self):
+        return sum(p.kernel_launches() for p in self.parts)
+
+    def set_kernel_timing(self, on):
+        for p in self.parts:
+            p.set_kernel_timing(on)
+
+    def kernel_times(self):
+        out = {}
+        for p in self.parts:
+            for k, v in p.kernel_times().items():
+                o = out.get(k, (0, 0, 0.0))
+                out[k] = (o[0] + v[0], o[1] + v[1], o[2] + v[2])
+        return out
+
+    # ---- timing marks: the groups are idle when mark 0 is taken (host sync), group 0's mark comes first; the elapsed
+    # time runs from it to the LAST group's mark 1
+    def mark(self, which):
+        if which == 0:
+            self.sync()
+        for p in self.parts:
+            p.mark(which)
+
+    def mark_elapsed_ms(self):
+        worst = 0.0
+        for p in self.parts:
+            ms = C.c_float(0)
+            p._ck(self.lib.msckf_mark_elapsed_between(self.parts[0].h, p.h, C.addressof(ms)))
+            worst = max(worst, ms.value)
+        return worst
 
 
 def fp64_peak(device=0):

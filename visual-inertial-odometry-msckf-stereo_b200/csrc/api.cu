@@ -1091,6 +1091,16 @@ int msckf_mark_elapsed(msckf_ctx* ctx, float* ms) {
   return MSCKF_OK;
 }
 
+int msckf_mark_elapsed_between(msckf_ctx* first, msckf_ctx* last, float* ms) {
+  if (!first || !last || !ms) return MSCKF_ERR_ARG;
+  msckf_ctx* ctx = last;
+  ARG(first->device == last->device, "contexts on different devices");
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaEventSynchronize(last->mark[1]));
+  CK(cudaEventElapsedTime(ms, first->mark[0], last->mark[1]));
+  return MSCKF_OK;
+}
+
 int msckf_kernel_count(void) { return KID_COUNT; }
 const char* msckf_kernel_name(int32_t i) { return (i >= 0 && i < KID_COUNT) ? kKernelNames[i] : ""; }
 

@@ -471,12 +471,21 @@ __global__ void __launch_bounds__(PT) k_augment(Dev d, const long long* __restri
     }
   }
   __syncthreads();
-  // new rows: J P[:21, :n]; mirrored into the new columns
+  // new rows: J P[:21, :n]; mirrored into the new columns.  J (jit_utils.py:141-156) is [R_i_c 0 .. I_3 at 15] over
+  // [skew(t) 0 .. I_3 at 12 .. I_3 at 18]: only the rows 0..2 and one or two more of P enter a new row (the zero
+  // terms of the dense product change nothing, the others are added in the same ascending order)
   for (int e = tid; e < 6 * n; e += PT) {
     const int i = e / n, j = e - i * n;
+    const double* Pj = P + j;
     double s = 0;
 #pragma unroll
-    for (int k = 0; k < 21; ++k) s += sJ[21 * i + k] * P[(size_t)k * ld + j];
+    for (int k = 0; k < 3; ++k) s += sJ[21 * i + k] * Pj[(size_t)k * ld];
+    if (i < 3) {
+      s += Pj[(size_t)(15 + i) * ld];
+    } else {
+      s += Pj[(size_t)(12 + i - 3) * ld];
+      s += Pj[(size_t)(18 + i - 3) * ld];
+    }
     if (j < 21) sB[21 * i + j] = s;
     P[(size_t)(n + i) * ld + j] = s;
     P[(size_t)j * ld + n + i] = s;
@@ -577,40 +586,51 @@ __global__ void __launch_bounds__(PT) k_reset(Dev d, int only_filter, int reset_
 }
 
 // ------------------------------------------------------------------ camera-state removal (msckf.py:803-818)
-// In-place compaction of P, the camera table and the physical-slot mask.  Rows are moved in
-// increasing order in batches staged through shared memory (destination row <= source row).
-constexpr int RB = 24;  // rows per batch
+// Compaction of P, the camera table and the physical-slot mask.  P is copied without the rows / columns of the two camera
+// states into the filter's other covariance buffer, which becomes the current one (no ordering hazards: every thread
+// copies on its own).
 __global__ void __launch_bounds__(PT) k_remove_cams(Dev d) {
   const int f = blockIdx.x, tid = threadIdx.x;
   const int r0 = d.rm_idx[2 * f], r1 = d.rm_idx[2 * f + 1];
   if (r0 < 0) return;
-  extern __shared__ double srow[];     // [RB][ld]
   const int N = d.ncam[f], n = NI + 6 * N, ld = d.ld;
-  double* P = cov_of(d, f);
   // the pruning update already wrote P without the two camera states (k_upd_dmma, stage 1): only the camera table is left
-  const int n2 = d.p_compacted[f] ? 0 : n - 12;
+  const bool compacted = d.p_compacted[f] != 0;
   __syncthreads();
-  if (tid == 0) d.p_compacted[f] = 0;
-  auto src_of = [&](int i) {   // new index -> old index
-    if (i < NI + 6 * r0) return i;
-    if (i < NI + 6 * (r1 - 1)) return i + 6;
-    return i + 12;
-  };
-  // rows above the first removed camera state keep their place: only their columns right of it move (in-row shift)
-  const int first = NI + 6 * r0;
-  for (int base = 0; base < n2; base += RB) {
-    const int nb = min(RB, n2 - base);
-    const int j0 = (base + nb <= first) ? first : 0;
-    for (int i = tid >> 5; i < nb; i += PT / 32) {                         // a warp owns a row, lanes run along it
-      const double* src = P + (size_t)src_of(base + i) * ld;
-      for (int j = j0 + (tid & 31); j < n2; j += 32) srow[i * ld + j] = src[src_of(j)];
+  if (!compacted) {
+    const double* P = cov_of(d, f);
+    double* Pout = cov_other(d, f);
+    const int n2 = n - 12;
+    auto src_of = [&](int i) {   // new index -> old index
+      if (i < NI + 6 * r0) return i;
+      if (i < NI + 6 * (r1 - 1)) return i + 6;
+      return i + 12;
+    };
+    // 16 loads in flight per thread before the first store: the copy of one filter is a handful of memory round trips
+    constexpr int UB = 16;
+    const int tot = n2 * n2;
+    for (int e0 = tid; e0 < tot; e0 += PT * UB) {
+      double v[UB];
+#pragma unroll
+      for (int u = 0; u < UB; ++u) {
+        const int e = e0 + u * PT;
+        if (e < tot) {
+          const int i = e / n2, j = e - i * n2;
+          v[u] = P[(size_t)src_of(i) * ld + src_of(j)];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UB; ++u) {
+        const int e = e0 + u * PT;
+        if (e < tot) {
+          const int i = e / n2, j = e - i * n2;
+          Pout[(size_t)i * ld + j] = v[u];
+        }
+      }
     }
-    __syncthreads();
-    for (int i = tid >> 5; i < nb; i += PT / 32) {
-      double* dst = P + (size_t)(base + i) * ld;
-      for (int j = j0 + (tid & 31); j < n2; j += 32) dst[j] = srow[i * ld + j];
-    }
-    __syncthreads();
+    if (tid == 0) d.Pcur[f] = Pout;
+  } else if (tid == 0) {
+    d.p_compacted[f] = 0;
   }
   // camera table: stage every surviving entry, then write
   __shared__ double scam[64 * CAM_STRIDE];
@@ -656,11 +676,7 @@ void launch_reset(const Dev& d, int only_filter, int reset_imu, cudaStream_t st)
   KLAUNCH(d, KID_RESET, st, (k_reset<<<only_filter >= 0 ? 1 : d.F, PT, 0, st>>>(d, only_filter, reset_imu)));
 }
 void launch_remove_cams(const Dev& d, cudaStream_t st) {
-  static DevOnce once;     // function attributes are per device
-  once.run([&] {
-    cudaFuncSetAttribute(k_remove_cams, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-  });
-  KLAUNCH(d, KID_REMOVE_CAMS, st, (k_remove_cams<<<d.F, PT, (size_t)RB * d.ld * sizeof(double), st>>>(d)));
+  KLAUNCH(d, KID_REMOVE_CAMS, st, (k_remove_cams<<<d.F, PT, 0, st>>>(d)));
 }
 
 }  // namespace msckf

@@ -251,6 +251,20 @@ int msckf_measurement_jacobian(msckf_ctx* ctx, int32_t filter, int64_t cam_id, i
 int msckf_gating_test(msckf_ctx* ctx, int32_t filter, const double* H, const double* r, int32_t m,
                       int32_t n_state, int32_t dof, double* gamma, int32_t* pass);
 
+/* The gating test for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.
+ * Same kernel and arithmetic as msckf_gating_test, but H_dev [m][n_state], r_dev [m], gamma_dev [1] and pass_dev [1] are
+ * DEVICE pointers, the kernel is enqueued on the context's stream (results are valid after msckf_sync or any later
+ * blocking call) and its scratch (m n_state + m m + m doubles) lives in a static device array of
+ * MSCKF_GATE_NOALLOC_MAX_DOUBLES doubles (534 KiB, held by every GPU that loads the library until the process exits);
+ * the call performs no cudaMalloc / cudaFree.  Larger shapes return MSCKF_ERR_CAPACITY (text in msckf_last_error).
+ * All calls on a device share the array: calls of different contexts (streams) that overlap on the GPU race; calls on one
+ * context are ordered by its stream.  The array keeps the previous call's contents; the kernel overwrites every entry
+ * it reads. */
+#define MSCKF_GATE_NOALLOC_MAX_DOUBLES (128 * 405 + 128 * 128 + 128)   /* e.g. m = 128 rows at n_state = 405 */
+int msckf_gating_test_noalloc(msckf_ctx* ctx, int32_t filter, const double* H_dev, const double* r_dev, int32_t m,
+                              int32_t n_state, int32_t dof, double* gamma_dev, int32_t* pass_dev);
+
 /* measurement_update (msckf.py:543-604) with a caller-supplied dense H [m][n_state], r [m]. */
 int msckf_measurement_update(msckf_ctx* ctx, int32_t filter, const double* H, const double* r, int32_t m,
                              int32_t n_state);

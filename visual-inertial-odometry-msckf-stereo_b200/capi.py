@@ -26,6 +26,7 @@ N_COUNTERS = 16
 FEAT_FEW_OBS, FEAT_TRI_FAILED, FEAT_GATE_PASS, FEAT_GATE_FAIL, FEAT_AFTER_CAP = 1, 2, 3, 4, 5
 
 ERR_ARG, ERR_CUDA, ERR_CAPACITY, ERR_NUMERIC = -1, -2, -3, -4
+GATE_NOALLOC_MAX_DOUBLES = 128 * 405 + 128 * 128 + 128     # include/msckf_b200.h MSCKF_GATE_NOALLOC_MAX_DOUBLES
 
 
 class MsckfCudaError(RuntimeError):
@@ -100,6 +101,7 @@ SIGNATURES = {
     'msckf_feature_jacobian': [_P, _I, _L, _I, _P, _P, _P, _P, _I],
     'msckf_measurement_jacobian': [_P, _I, _L, _L, _P, _P, _P],
     'msckf_gating_test': [_P, _I, _P, _P, _I, _I, _I, _P, _P],
+    'msckf_gating_test_noalloc': [_P, _I, _P, _P, _I, _I, _I, _P, _P],
     'msckf_measurement_update': [_P, _I, _P, _P, _I, _I],
     'msckf_find_redundant_cam_states': [_P, _I, _P],
     'msckf_last_timing': [_P, _P],
@@ -495,6 +497,11 @@ class Context(object):
         self._ck(self.lib.msckf_gating_test(self.h, f, _ptr(H), _ptr(r), H.shape[0], H.shape[1], int(dof), C.addressof(g),
                                             C.addressof(p)))
         return g.value, bool(p.value)
+
+    def gating_test_noalloc(self, f, H_dev, r_dev, m, n_state, dof, gamma_dev, pass_dev):
+        """msckf_gating_test_noalloc: all pointers are raw DEVICE addresses (ints); enqueued on the context's stream, no
+        allocation.  Results are valid after sync()."""
+        self._ck(self.lib.msckf_gating_test_noalloc(self.h, int(f), H_dev, r_dev, int(m), int(n_state), int(dof), gamma_dev, pass_dev))
 
     def measurement_update(self, f, H, r):
         H, r = _f64(H), _f64(r)

@@ -1244,6 +1244,46 @@ int msckf_gating_test(msckf_ctx* ctx, int32_t f, const double* H, const double* 
   return rc;
 }
 
+// ------------------------------------------------------------------ gating test without any allocation
+// The scratch of k_gate_dense (T1 = H P: m x n, S: m x m, y: m doubles) in a file-scope device array instead of a
+// cudaMalloc per call.  Every GPU that loads the library holds the array until the process exits.
+static __device__ __align__(256) double g_gate_scratch[MSCKF_GATE_NOALLOC_MAX_DOUBLES];
+static double* g_gate_scratch_ptr[64];      // device address of the array, per device (the name above is a host-side stand-in)
+static int g_gate_scratch_rc[64];
+static DevOnce g_gate_scratch_once;
+
+int msckf_gating_test_noalloc(msckf_ctx* ctx, int32_t f, const double* H_dev, const double* r_dev, int32_t m, int32_t n_state,
+                              int32_t dof, double* gamma_dev, int32_t* pass_dev) {
+  if (!ctx) return MSCKF_ERR_ARG;
+  const Dev& d = ctx->d;
+  ARG(f >= 0 && f < d.F && H_dev && r_dev && gamma_dev && pass_dev && m > 0 && dof >= 1 && dof <= 99 && n_state >= NI && n_state <= d.nmax,
+      "filter / pointers / sizes / dof");
+  const unsigned long long need = (unsigned long long)m * n_state + (unsigned long long)m * m + (unsigned long long)m;
+  if (need > (unsigned long long)MSCKF_GATE_NOALLOC_MAX_DOUBLES) {
+    ctx->err = "msckf_gating_test_noalloc: m = " + std::to_string(m) + ", n_state = " + std::to_string(n_state) + " need " +
+               std::to_string(need) + " doubles of scratch (m n_state + m m + m), the static array holds " +
+               std::to_string((long long)MSCKF_GATE_NOALLOC_MAX_DOUBLES) + "; use msckf_gating_test";
+    return MSCKF_ERR_CAPACITY;
+  }
+  ARG(ctx->device >= 0 && ctx->device < 64, "device index");
+  CK(cudaSetDevice(ctx->device));
+  g_gate_scratch_once.run([&] {          // once per device, with that device current
+    double* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_gate_scratch);
+    g_gate_scratch_ptr[ctx->device] = (e == cudaSuccess) ? p : nullptr;
+    g_gate_scratch_rc[ctx->device] = (int)e;
+  });
+  double* scratch = g_gate_scratch_ptr[ctx->device];
+  if (!scratch) {
+    ctx->err = std::string("cudaGetSymbolAddress(g_gate_scratch): ") + cudaGetErrorString((cudaError_t)g_gate_scratch_rc[ctx->device]);
+    return MSCKF_ERR_CUDA;
+  }
+  // the kernel writes T1, S and y in full before it reads them: nothing in the array has to start at zero
+  launch_gate_dense(d, f, H_dev, r_dev, m, n_state, dof, scratch, gamma_dev, pass_dev, ctx->st);
+  CK(cudaGetLastError());
+  return MSCKF_OK;
+}
+
 int msckf_measurement_update(msckf_ctx* ctx, int32_t f, const double* H, const double* r, int32_t m, int32_t n_state) {
   if (!ctx) return MSCKF_ERR_ARG;
   const Dev& d = ctx->d;

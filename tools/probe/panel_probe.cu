@@ -3,6 +3,7 @@
 //   nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -I visual-inertial-odometry-msckf-stereo_b200/csrc \
 //        tools/probe/panel_probe.cu -o /tmp/panel_probe && /tmp/panel_probe
 #include <cstdio>
+#include <cmath>
 #include <cuda_runtime.h>
 #include "qr_panel.cuh"
 
@@ -126,7 +127,56 @@ static void run(const char* name, int warps) {
   cudaFree(d);
 }
 
+// one panel with T on known data, checked on the host: (I - U T U^T)^T [R; C] must equal [R_new; 0] in the panel columns
+__global__ void check_kernel(double* out) {
+  extern __shared__ double sm[];
+  const int ldr = 52, lane = threadIdx.x;
+  double* sR = sm;
+  double* sC = sR + 8 * ldr;
+  double* sTm = sC + 128 * ldr;
+  for (int e = lane; e < 128 * ldr; e += 32) sC[e] = 0.001 * ((e * 37) % 101) - 0.05;
+  for (int e = lane; e < 8 * ldr; e += 32) { const int i = e / ldr, c = e % ldr; sR[e] = (c < i) ? 0.0 : ((c == i) ? 2.0 + i : 0.01 * ((e * 13) % 7)); }
+  __syncwarp();
+  for (int e = lane; e < 8 * 8; e += 32) out[e] = sR[(e / 8) * ldr + e % 8];
+  for (int e = lane; e < 128 * 8; e += 32) out[64 + e] = sC[(e / 8) * ldr + e % 8];
+  __syncwarp();
+  qr_panel<4, true>(sR, ldr, sR, ldr, sC, ldr, sTm, 12, 8, true, lane);
+  __syncwarp();
+  double* o2 = out + 64 + 1024;
+  for (int e = lane; e < 8 * 8; e += 32) o2[e] = sR[(e / 8) * ldr + e % 8];
+  for (int e = lane; e < 128 * 8; e += 32) o2[64 + e] = sC[(e / 8) * ldr + e % 8];
+  for (int e = lane; e < 64; e += 32) o2[64 + 1024 + e] = sTm[(e / 8) * 12 + e % 8];
+}
+static void check() {
+  double* d;
+  const int n = 2 * (64 + 1024) + 64;
+  cudaMalloc(&d, n * sizeof(double));
+  cudaFuncSetAttribute(check_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  check_kernel<<<1, 32, (8 * 52 + 128 * 52 + 96) * 8>>>(d);
+  cudaDeviceSynchronize();
+  static double h[2 * (64 + 1024) + 64];
+  cudaMemcpy(h, d, sizeof h, cudaMemcpyDeviceToHost);
+  const double *R0 = h, *C0 = h + 64, *R1 = h + 1088, *V = h + 1088 + 64, *T = h + 1088 + 64 + 1024;
+  // A = [R0; C0] (136 x 8), U = [I; V];  B = A - U T^T (U^T A)
+  static double A[136][8], U[136][8], W[8][8], Y[8][8];
+  for (int i = 0; i < 8; ++i) for (int c = 0; c < 8; ++c) { A[i][c] = R0[i * 8 + c]; U[i][c] = (i == c) ? 1.0 : 0.0; }
+  for (int i = 0; i < 128; ++i) for (int c = 0; c < 8; ++c) { A[8 + i][c] = C0[i * 8 + c]; U[8 + i][c] = V[i * 8 + c]; }
+  for (int a = 0; a < 8; ++a) for (int c = 0; c < 8; ++c) { double s = 0; for (int i = 0; i < 136; ++i) s += U[i][a] * A[i][c]; W[a][c] = s; }
+  for (int a = 0; a < 8; ++a) for (int c = 0; c < 8; ++c) { double s = 0; for (int l = 0; l < 8; ++l) s += T[l * 8 + a] * W[l][c]; Y[a][c] = s; }
+  double eR = 0, eZ = 0, tmax = 0;
+  for (int i = 0; i < 136; ++i) for (int c = 0; c < 8; ++c) {
+    double b = A[i][c];
+    for (int a = 0; a < 8; ++a) b -= U[i][a] * Y[a][c];
+    if (i < 8) { const double e = fabs(b - (c >= i ? R1[i * 8 + c] : 0.0)); if (e > eR) eR = e; }
+    else if (fabs(b) > eZ) eZ = fabs(b);
+  }
+  for (int e = 0; e < 64; ++e) if (fabs(T[e]) > tmax) tmax = fabs(T[e]);
+  printf("panel check: |Q^T A - R| top %.3e, below %.3e, max |T| %.3e  (%s)\n", eR, eZ, tmax, cudaGetErrorString(cudaGetLastError()));
+  cudaFree(d);
+}
+
 int main() {
+  check();
   for (int warps : {1, 3}) {
     run<0>("full panel, folded reductions, T", warps);
     run<1>("no T, no V write-back", warps);

@@ -606,26 +606,27 @@ __global__ void __launch_bounds__(PT) k_remove_cams(Dev d) {
       if (i < NI + 6 * (r1 - 1)) return i + 6;
       return i + 12;
     };
-    // 16 loads in flight per thread before the first store: the copy of one filter is a handful of memory round trips
-    constexpr int UB = 16;
-    const int tot = n2 * n2;
-    for (int e0 = tid; e0 < tot; e0 += PT * UB) {
-      double v[UB];
+    // a warp takes four rows at a time, lanes run along them: 16 loads in flight per thread before the first store, no
+    // index arithmetic beyond the two jumps over the removed blocks
+    const int lane = tid & 31, warp = tid >> 5;
+    for (int i0 = 4 * warp; i0 < n2; i0 += 4 * (PT / 32)) {
+      const double* src[4];
 #pragma unroll
-      for (int u = 0; u < UB; ++u) {
-        const int e = e0 + u * PT;
-        if (e < tot) {
-          const int i = e / n2, j = e - i * n2;
-          v[u] = P[(size_t)src_of(i) * ld + src_of(j)];
-        }
-      }
+      for (int u = 0; u < 4; ++u) src[u] = P + (size_t)src_of(min(i0 + u, n2 - 1)) * ld;
+      for (int j0 = lane; j0 < n2; j0 += 128) {
+        double v[4][4];
+        int sj[4];
 #pragma unroll
-      for (int u = 0; u < UB; ++u) {
-        const int e = e0 + u * PT;
-        if (e < tot) {
-          const int i = e / n2, j = e - i * n2;
-          Pout[(size_t)i * ld + j] = v[u];
-        }
+        for (int w = 0; w < 4; ++w) sj[w] = src_of(min(j0 + 32 * w, n2 - 1));
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+          for (int w = 0; w < 4; ++w) v[u][w] = src[u][sj[w]];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+          for (int w = 0; w < 4; ++w)
+            if (i0 + u < n2 && j0 + 32 * w < n2) Pout[(size_t)(i0 + u) * ld + j0 + 32 * w] = v[u][w];
       }
     }
     if (tid == 0) d.Pcur[f] = Pout;

@@ -107,3 +107,67 @@ def test_gather_world_size_2_gloo():
     assert full.shape == (total, 5, 7)
     assert np.array_equal(full[:, 0, 0], np.arange(total, dtype=np.float64))
     assert tmax == 2.0 and tsum == float(total)
+
+
+def test_context_group_splits_ragged_batches():
+    """capi.ContextGroup (a batch spread over several contexts): ragged batch arguments are cut at the group boundaries with
+    rebased offsets, per-filter calls reach the owning context with the local index, read-backs are concatenated in filter
+    order.  Host logic only: the contexts are stand-ins that record what they receive."""
+    from msckf_b200 import capi
+
+    class Part(object):
+        def __init__(self, F, tag):
+            self.F, self.tag, self.calls = F, tag, []
+
+        def feature_callback_async(self, *a):
+            self.calls.append(('frame',) + tuple(np.array(x, copy=True) for x in a))
+
+        def collect(self):
+            return np.full((self.F, capi.IMU_STRIDE), float(self.tag)), np.zeros(self.F, dtype=bool)
+
+        def get_cov(self, f, n=None):
+            return (self.tag, f)
+
+        def counters(self):
+            return np.full((self.F, capi.N_COUNTERS), self.tag, dtype=np.int64)
+
+        def kernel_launches(self):
+            return 10 * (self.tag + 1)
+
+        def close(self):
+            pass
+
+    g = object.__new__(capi.ContextGroup)
+    g.parts = [Part(3, 0), Part(2, 1)]
+    g.bounds = np.array([0, 3, 5], dtype=np.int64)
+    g.F = 5
+    for name in capi.ContextGroup.PER_FILTER:
+        if hasattr(Part, name):
+            setattr(g, name, g._route(name))
+    assert g.ranges() == [(0, 3), (3, 5)]
+    # ragged: filter k has k + 1 IMU samples and 2 k features
+    imu_n, feat_n = [1, 2, 3, 4, 5], [0, 2, 4, 6, 8]
+    imu_off = np.concatenate([[0], np.cumsum(imu_n)]).astype(np.int32)
+    feat_off = np.concatenate([[0], np.cumsum(feat_n)]).astype(np.int32)
+    ts = np.arange(imu_off[-1], dtype=np.float64)
+    gyro = np.arange(3 * imu_off[-1], dtype=np.float64).reshape(-1, 3)
+    acc = -gyro
+    ids = np.arange(feat_off[-1], dtype=np.int64) + 100
+    uv = np.arange(4 * feat_off[-1], dtype=np.float64).reshape(-1, 4)
+    cam_ids = np.array([7, 7, 7, 8, 8], dtype=np.int64)
+    g.feature_callback_async(imu_off, ts, gyro, acc, cam_ids, feat_off, ids, uv)
+    a, b = g.parts[0].calls[0], g.parts[1].calls[0]
+    assert a[1].tolist() == [0, 1, 3, 6] and b[1].tolist() == [0, 4, 9]                 # rebased IMU offsets
+    assert np.array_equal(a[2], ts[:6]) and np.array_equal(b[2], ts[6:])
+    assert np.array_equal(a[3], gyro[:6]) and np.array_equal(b[4], acc[6:])
+    assert a[5].tolist() == [7, 7, 7] and b[5].tolist() == [8, 8]
+    assert a[6].tolist() == [0, 0, 2, 6] and b[6].tolist() == [0, 6, 14]                # rebased feature offsets
+    assert np.array_equal(a[7], ids[:6]) and np.array_equal(b[7], ids[6:])
+    assert np.array_equal(a[8], uv[:6]) and np.array_equal(b[8], uv[6:])
+    imu, rst = g.collect()
+    assert imu.shape == (5, capi.IMU_STRIDE) and imu[:3].max() == 0.0 and imu[3:].min() == 1.0 and rst.shape == (5,)
+    assert g.get_cov(0) == (0, 0) and g.get_cov(2) == (0, 2) and g.get_cov(3) == (1, 0) and g.get_cov(4) == (1, 1)
+    with pytest.raises(capi.MsckfCudaError):
+        g.get_cov(5)
+    assert g.counters()[:, 0].tolist() == [0, 0, 0, 1, 1]
+    assert g.kernel_launches() == 30

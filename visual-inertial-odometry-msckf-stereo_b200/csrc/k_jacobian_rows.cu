@@ -289,7 +289,10 @@ static void launch_rows(const Dev& d, int cls, int write_all, cudaStream_t st) {
     cudaFuncSetAttribute(k_jacobian_rows<M, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   });
   const int sms = sm_count();
-  int per_sm = (int)std::min<size_t>(jr_ctas_per_sm<M>(), (220 * 1024) / (smem + 1024));   // one resident wave: every group walks a contiguous piece of the list
+  // One wave of resident CTAs, every group walking a contiguous piece of the list -- but two CTAs per SM fewer than the
+  // register file holds: a full wave owns every register of every SM for the whole launch (50-100 us) and whatever else
+  // is ready (the other classes on their lanes, the other half-batch) has to wait; leaving room is worth 2-3 % of a frame.
+  int per_sm = (int)std::min<size_t>(jr_ctas_per_sm<M>() - 2, (220 * 1024) / (smem + 1024));
   per_sm = std::max(per_sm, 1);
   KLAUNCH(d, KID_JACOBIAN_ROWS, st, (k_jacobian_rows<M, G><<<sms * per_sm, JR_T, smem, st>>>(d, cls, write_all)));
 }

@@ -264,6 +264,18 @@ __global__ void __launch_bounds__(DT, KC > 64 ? 1 : 512 / DT) k_upd_dmma(Dev d, 
         wa += 4 * ldT;
         wb += 4 * ldT;
       }
+      // destination indices of this thread's two rows and four columns of the tile, once per tile (-1: outside / removed)
+      int ma[2], mb[2][2];
+#pragma unroll
+      for (int x = 0; x < 2; ++x) {
+        const int a = a0 + 8 * x + g;
+        ma[x] = (a < n) ? (compact ? cmap(a) : a) : -1;
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int b = b0 + 8 * x + 2 * tg + e;
+          mb[x][e] = (b < n) ? (compact ? cmap(b) : b) : -1;
+        }
+      }
 #pragma unroll
       for (int x = 0; x < 2; ++x)
 #pragma unroll
@@ -272,13 +284,10 @@ __global__ void __launch_bounds__(DT, KC > 64 ? 1 : 512 / DT) k_upd_dmma(Dev d, 
 #pragma unroll
           for (int e = 0; e < 2; ++e) {
             const int a = a0 + 8 * x + g, b = b0 + 8 * y + 2 * tg + e;
-            if (a < n && b < n && b >= a) {
+            if (b >= a && ma[x] >= 0 && mb[y][e] >= 0) {
               const double v = pv[x][y][e] - acc[x][y][e];
-              const int ma = cmap(a), mb = cmap(b);
-              if (ma >= 0 && mb >= 0) {
-                Pout[(size_t)ma * ld + mb] = v;
-                Pout[(size_t)mb * ld + ma] = v;
-              }
+              Pout[(size_t)ma[x] * ld + mb[y][e]] = v;
+              Pout[(size_t)mb[y][e] * ld + ma[x]] = v;
             }
           }
         }

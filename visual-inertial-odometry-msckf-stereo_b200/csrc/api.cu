@@ -357,7 +357,7 @@ int msckf_create(const msckf_config* cfg, msckf_ctx** out) {
   DA(d.item_cand, F * Fc); DA(d.item_mask, F * Fc); DA(d.item_rows, F * Fc); DA(d.item_off, F * Fc); DA(d.item_rowoff, F * Fc);
   DA(d.item_dof, F * Fc); DA(d.item_gamma, F * Fc); DA(d.item_pass, F * Fc); DA(d.nitem, F);
   DA(d.rm_mask, F); DA(d.rm_idx, F * 2);
-  DA(d.pool, (size_t)d.pool_cap); DA(d.stage_ctr, SC_COUNT); DA(d.item_lmask, F * Fc);
+  DA(d.pool, (size_t)d.pool_cap); DA(d.stage_ctr, SC_COUNT); DA(d.item_lmask, F * Fc); DA(d.item_slot, F * Fc);
   DA(d.wl_tri, F * Fc); DA(d.wl_jac_small, JAC_CLASSES * F * Fc); DA(d.wl_jac_big, F * Fc); DA(d.wl_jac_big2, F * Fc); DA(d.wl_lu, F * Fc);
   { const size_t Rm = 4 * Nm - 3; DA(d.lu_scratch, Rm * 6 * Nm + Rm * Rm + 3 * Rm + 8); }
   DA(d.jac_scratch, (size_t)d.jac_big_grid * d.jac_scratch_stride);
@@ -1156,6 +1156,10 @@ int msckf_feature_jacobian(msckf_ctx* ctx, int32_t f, int64_t feature_id, int32_
   CK(cudaMemcpyAsync(d.cand + b, &slot, sizeof(int), cudaMemcpyHostToDevice, ctx->st));
   CK(cudaMemcpyAsync(d.item_cand + b, &zero, sizeof(int), cudaMemcpyHostToDevice, ctx->st));
   CK(cudaMemcpyAsync(d.item_mask + b, &im, sizeof(im), cudaMemcpyHostToDevice, ctx->st));
+  unsigned long long lm = 0;                 // the same mask in logical camera order, and the slot (k_plan_items' part)
+  for (int c = 0; c < s.ncam; ++c) lm |= ((im >> s.phys[c]) & 1ull) << c;
+  CK(cudaMemcpyAsync(d.item_lmask + b, &lm, sizeof(lm), cudaMemcpyHostToDevice, ctx->st));
+  CK(cudaMemcpyAsync(d.item_slot + b, &slot, sizeof(int), cudaMemcpyHostToDevice, ctx->st));
   CK(cudaMemcpyAsync(d.item_rows + b, &rows, sizeof(int), cudaMemcpyHostToDevice, ctx->st));
   CK(cudaMemcpyAsync(d.item_dof + b, &dof, sizeof(int), cudaMemcpyHostToDevice, ctx->st));
   CK(cudaMemcpyAsync(d.item_off + b, &off0, sizeof(off0), cudaMemcpyHostToDevice, ctx->st));

@@ -111,18 +111,8 @@ __global__ void __launch_bounds__(JR_T, jr_ctas_per_sm<M>()) k_jacobian_rows(Dev
     const size_t ik = (size_t)f * d.Fcap + k;
     const int N = d.ncam[f], ld = d.ld;
     const int* phys = d.cam_phys + (size_t)f * d.Nmax;
-    // ---- observation mask in logical camera order, cameras of the M observations
-    unsigned long long lmask = 0;
-    {
-      const unsigned long long mask = d.item_mask[ik];
-      for (int c0 = 0; c0 < d.Nmax; c0 += G) {
-        const int c = c0 + r;
-        const int bit = (c < N) ? (int)((mask >> phys[c]) & 1ull) : 0;
-        unsigned b = __ballot_sync(JFULL, bit) >> gbase;
-        if (G < 32) b &= (1u << G) - 1u;
-        lmask |= (unsigned long long)b << c0;
-      }
-    }
+    // ---- observation mask in logical camera order (k_plan_items), cameras of the M observations
+    const unsigned long long lmask = d.item_lmask[ik];
     if (r < M) {
       unsigned long long mm = lmask;
       for (int x = 0; x < r; ++x) mm &= mm - 1;
@@ -130,7 +120,7 @@ __global__ void __launch_bounds__(JR_T, jr_ctas_per_sm<M>()) k_jacobian_rows(Dev
     }
     __syncwarp();
     // ---- step 1: this lane's row of H_x, H_f, r
-    const int slot = d.cand[(size_t)f * d.Fcap + d.item_cand[ik]];
+    const int slot = d.item_slot[ik];
     const size_t fs = (size_t)f * d.Fcap + slot;
     double Hx[6], v[3], res;
     {
@@ -270,7 +260,6 @@ __global__ void __launch_bounds__(JR_T, jr_ctas_per_sm<M>()) k_jacobian_rows(Dev
       }
       d.item_gamma[ik] = gamma;
       d.item_pass[ik] = pass;
-      d.item_lmask[ik] = lmask;
     }
     // ---- record for the stacking / QR kernel: the projected rows and residual, row-major [R][6M+1]
     if (active && (pass || write_all || !spd) && d.item_off[ik] + jac_record_doubles(M) <= d.pool_cap) {

@@ -344,6 +344,10 @@ __global__ void __launch_bounds__(ST) k_plan_items(Dev d, int stage) {
   const int* cand = d.cand + (size_t)f * d.Fcap;
   const int* cst = d.cand_status + (size_t)f * d.Fcap;
   const unsigned long long rmm = d.rm_mask[f];
+  __shared__ int s_phys[64];                 // physical observation slot of logical camera c
+  const int N = d.ncam[f];
+  for (int c = tid; c < N; c += ST) s_phys[c] = d.cam_phys[(size_t)f * d.Nmax + c];
+  __syncthreads();
   int ni = 0;
   long long elems_total = 0;
   long long w_obs = 0, w_flops = 0, w_bytes = 0;   // algorithmic work of the Jacobian / gate kernel
@@ -371,6 +375,10 @@ __global__ void __launch_bounds__(ST) k_plan_items(Dev d, int stage) {
       const size_t k = (size_t)f * d.Fcap + ni + r;
       d.item_cand[k] = ci;
       d.item_mask[k] = im;
+      unsigned long long lm = 0;             // the mask in logical camera order: what the Jacobian and QR kernels index by
+      for (int c = 0; c < N; ++c) lm |= ((im >> s_phys[c]) & 1ull) << c;
+      d.item_lmask[k] = lm;
+      d.item_slot[k] = cand[ci];
       d.item_rows[k] = rows;
       d.item_dof[k] = stage == 0 ? M - 1 : M;
       d.item_off[k] = elems_total + eoff;   // relative; rebased below

@@ -115,7 +115,8 @@ struct Dev {
   int* nitem;              // [F]
   unsigned long long* rm_mask;     // [F] physical mask of the camera states being pruned
   int* rm_idx;             // [F][2] logical indices, -1 when not pruning
-  unsigned long long* item_lmask;  // [F][Fcap] the same mask in logical camera order (written by the Jacobian kernel)
+  unsigned long long* item_lmask;  // [F][Fcap] the same mask in logical camera order (k_plan_items)
+  int* item_slot;          // [F][Fcap] map slot of the item's landmark (= cand[item_cand])
   double* pool;            // compact per-landmark Jacobian records (58 M doubles each, bump allocated per stage)
   unsigned long long* stage_ctr;   // [SC_COUNT] pool bump pointer + work-list lengths, zeroed per stage
   long long pool_cap;      // elements

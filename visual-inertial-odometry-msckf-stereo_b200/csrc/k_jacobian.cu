@@ -184,7 +184,7 @@ __device__ __forceinline__ void jac_front(const Dev& d, int f, int k, int M, uns
   const unsigned gmask = NT <= 32 ? gmask_in : 0xffffffffu;
   const int lane = tid;                 // index inside the leader part (only used when tid < LW)
   const size_t ik = (size_t)f * d.Fcap + k;
-  const int slot = d.cand[(size_t)f * d.Fcap + d.item_cand[ik]];
+  const int slot = d.item_slot[ik];
   const size_t fs = (size_t)f * d.Fcap + slot;
   const int N = d.ncam[f];
   const Params& prm = *d.prm;
@@ -323,7 +323,6 @@ __device__ __forceinline__ void jac_finish(const Dev& d, int f, int k, int M, un
     const int pass = (gamma < d.prm->chi2[d.item_dof[ik]]) ? 1 : 0;
     d.item_gamma[ik] = gamma;
     d.item_pass[ik] = pass;
-    d.item_lmask[ik] = lmask;
     B.Tm[8] = (double)(pass || !spd);
   }
   gsync<NT>(gmask);
@@ -547,21 +546,6 @@ __global__ void __launch_bounds__(256) k_gate_lu(Dev d) {
   }
 }
 
-// logical-order observation mask of a landmark, computed by a group of G lanes (gmask, first lane gbase)
-template <int G>
-__device__ __forceinline__ unsigned long long logical_mask(const Dev& d, int f, unsigned long long mask, int tid, unsigned gmask, int gbase) {
-  const int N = d.ncam[f];
-  unsigned long long lmask = 0;
-  for (int c0 = 0; c0 < N; c0 += G) {
-    const int c = c0 + tid;
-    const int bit = (c < N) ? (int)((mask >> d.cam_phys[(size_t)f * d.Nmax + c]) & 1ull) : 0;
-    unsigned b = __ballot_sync(gmask, bit) >> gbase;
-    if (G < 32) b &= (1u << G) - 1u;
-    lmask |= (unsigned long long)b << c0;
-  }
-  return lmask;
-}
-
 // Small tracks: one group of G lanes per landmark, persistent grid over the work list wl_jac_small[0 .. n).
 template <int G>
 __global__ void __launch_bounds__(JAC_WARPS * 32, G == 32 ? 3 : 8) k_jacobian_gate_small(Dev d, int cls, int per_group_doubles, int write_all) {
@@ -577,7 +561,7 @@ __global__ void __launch_bounds__(JAC_WARPS * 32, G == 32 ? 3 : 8) k_jacobian_ga
   for (int w = (blockIdx.x * JAC_WARPS + warp) * GPW + grp; w < n; w += stride) {
     const int2 it = wl[w];
     const size_t ik = (size_t)it.x * d.Fcap + it.y;
-    const unsigned long long lmask = logical_mask<G>(d, it.x, d.item_mask[ik], tid, gmask, gbase);
+    const unsigned long long lmask = d.item_lmask[ik];          // logical camera order (k_plan_items)
     const int M = __popcll(lmask);
     JacBuf B;
     jac_carve(B, base, M, nullptr);
@@ -775,7 +759,7 @@ __global__ void __launch_bounds__(JB_T, MINB) k_jacobian_gate_big(Dev d, int cls
     const int2 it = wl[w];
     const int f = it.x, k = it.y;
     const size_t ik = (size_t)f * d.Fcap + k;
-    const unsigned long long lmask = logical_mask<32>(d, f, d.item_mask[ik], lane, 0xffffffffu, 0);
+    const unsigned long long lmask = d.item_lmask[ik];          // logical camera order (k_plan_items)
     const int M = __popcll(lmask);
     const int R = 4 * M - 3, Rp = jb_rp(M), nkt = Rp >> 3;
     JacBuf B;

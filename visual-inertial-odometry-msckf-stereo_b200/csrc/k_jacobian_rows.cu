@@ -74,12 +74,16 @@ __device__ __forceinline__ void jr_row(const double* __restrict__ pre, const dou
 }
 
 
-// registers: the projected row (6M), its product with Pcc (6M) and the row of S (4M-3) live in registers per lane
+// registers: the projected row (6M), its product with Pcc (6M) and the row of S (4M-3) live in registers per lane.
+// Register budget (launch bounds): 128 / 128 / 168 registers, no spills.  CTAs per SM actually launched: fewer than that
+// budget would hold, see launch_rows.
 template <int M>
-constexpr int jr_ctas_per_sm() { return M == 2 ? 5 : (M == 3 ? 4 : 3); }
+constexpr int jr_min_blocks() { return M == 4 ? 3 : 4; }
+template <int M>
+constexpr int jr_ctas_per_sm() { return M == 2 ? 3 : (M == 3 ? 2 : 1); }
 
 template <int M, int G>
-__global__ void __launch_bounds__(JR_T, jr_ctas_per_sm<M>()) k_jacobian_rows(Dev d, int cls, int write_all) {
+__global__ void __launch_bounds__(JR_T, jr_min_blocks<M>()) k_jacobian_rows(Dev d, int cls, int write_all) {
   constexpr int R4 = 4 * M, C6 = 6 * M, R = R4 - 3, LDR = C6 + 1, GPW = 32 / G, GD = jr_group_doubles<M>();
   static_assert(R4 <= G, "one lane per row");
   extern __shared__ __align__(16) double jsm[];
@@ -278,10 +282,11 @@ static void launch_rows(const Dev& d, int cls, int write_all, cudaStream_t st) {
     cudaFuncSetAttribute(k_jacobian_rows<M, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   });
   const int sms = sm_count();
-  // One wave of resident CTAs, every group walking a contiguous piece of the list -- but two CTAs per SM fewer than the
-  // register file holds: a full wave owns every register of every SM for the whole launch (50-100 us) and whatever else
-  // is ready (the other classes on their lanes, the other half-batch) has to wait; leaving room is worth 2-3 % of a frame.
-  int per_sm = (int)std::min<size_t>(jr_ctas_per_sm<M>() - 2, (220 * 1024) / (smem + 1024));
+  // One wave of resident CTAs, every group walking a contiguous piece of the list -- but well below what the register file
+  // holds (3 / 2 / 1 CTAs per SM, it would hold 4 / 4 / 3): a full wave owns every register of every SM for the whole launch
+  // (50-100 us) and whatever else is ready (the other classes on their lanes, the other half-batch) has to wait; leaving
+  // room is worth 2-3 % of a frame although the kernel alone gets 30 % slower.
+  int per_sm = (int)std::min<size_t>(jr_ctas_per_sm<M>(), (220 * 1024) / (smem + 1024));
   per_sm = std::max(per_sm, 1);
   KLAUNCH(d, KID_JACOBIAN_ROWS, st, (k_jacobian_rows<M, G><<<sms * per_sm, JR_T, smem, st>>>(d, cls, write_all)));
 }

@@ -171,3 +171,39 @@ def test_context_group_splits_ragged_batches():
         g.get_cov(5)
     assert g.counters()[:, 0].tolist() == [0, 0, 0, 1, 1]
     assert g.kernel_launches() == 30
+
+
+def test_device_frame_parts_addresses():
+    """MSCKFBatch.device_frame_parts: the per-group addresses of a frame resident in (here: host) tensors are the slices of the
+    ragged arrays at the group boundaries, with the offsets rebased per group."""
+    import torch
+    from msckf_b200.msckf import MSCKFBatch
+
+    class Ctx(object):
+        def ranges(self):
+            return [(0, 2), (2, 5)]
+
+    b = object.__new__(MSCKFBatch)
+    b.groups, b.ctx, b.F = 2, Ctx(), 5
+    keys = ['imu_off', 'ts', 'gyro', 'acc', 'cam_ids', 'feat_off', 'ids', 'uv']
+    imu_off = torch.tensor([0, 2, 4, 7, 7, 9], dtype=torch.int32)
+    feat_off = torch.tensor([0, 3, 3, 5, 9, 10], dtype=torch.int32)
+    frame = {'imu_off': imu_off, 'feat_off': feat_off, 'ts': torch.arange(9, dtype=torch.float64),
+             'gyro': torch.zeros((9, 3), dtype=torch.float64), 'acc': torch.ones((9, 3), dtype=torch.float64),
+             'cam_ids': torch.arange(5, dtype=torch.int64), 'ids': torch.arange(10, dtype=torch.int64),
+             'uv': torch.zeros((10, 4), dtype=torch.float64)}
+    parts = b.device_frame_parts(frame, keys)
+    assert len(parts) == 2
+    g0, g1 = [dict(zip(keys, p)) for p in parts]
+    assert g0['ts'] == frame['ts'].data_ptr() and g1['ts'] == frame['ts'].data_ptr() + 4 * 8
+    assert g1['gyro'] == frame['gyro'].data_ptr() + 4 * 3 * 8 and g1['acc'] == frame['acc'].data_ptr() + 4 * 3 * 8
+    assert g1['cam_ids'] == frame['cam_ids'].data_ptr() + 2 * 8
+    assert g0['ids'] == frame['ids'].data_ptr() and g1['ids'] == frame['ids'].data_ptr() + 3 * 8
+    assert g1['uv'] == frame['uv'].data_ptr() + 3 * 4 * 8
+    (o0, f0), (o1, f1) = frame['_group_offsets']
+    assert o0.tolist() == [0, 2, 4] and o1.tolist() == [0, 3, 3, 5]
+    assert f0.tolist() == [0, 3, 3] and f1.tolist() == [0, 2, 6, 7]
+    assert g0['imu_off'] == o0.data_ptr() and g1['feat_off'] == f1.data_ptr()
+    # one group: the frame's own addresses
+    b.groups = 1
+    assert b.device_frame_parts(frame, keys) == [tuple(frame[k].data_ptr() for k in keys)]

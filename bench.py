@@ -82,7 +82,7 @@ def parse():
     ap.add_argument('--no-c5', action='store_true')
     ap.add_argument('--no-strong', action='store_true')
     ap.add_argument('--c5-filters', type=int, default=128)
-    ap.add_argument('--groups', type=int, default=0, help='contexts (streams) a GPU\'s filters are spread over; 0 = the library default (2 from 1024 filters on)')
+    ap.add_argument('--groups', type=int, default=0, help='contexts (streams) a GPU\'s filters are spread over; 0 = the library default (2 from 512 filters on)')
     ap.add_argument('--only', default='', help='development: comma list of c3,c5 -- run just these legs and print them')
     return ap.parse_args()
 

@@ -366,14 +366,13 @@ class MSCKFBatch(object):
     stage is one launch over the batch (grid.y / blockIdx = filter).  Filters may receive
     different numbers of IMU samples and features per frame (ragged offsets)."""
 
-    GROUP_MIN_FILTERS = 1024    # from this batch size on the filters are spread over two contexts (see __init__)
+    GROUP_MIN_FILTERS = 512     # from this batch size on the filters are spread over two contexts (see __init__)
 
     def __init__(self, config, n_filters, device=0, feature_capacity=1024, max_rows=0, jacobian_pool_bytes=0, groups=None):
         """``groups``: number of contexts (CUDA streams) the filters are spread over.  A launch over a batch lasts as long as
-        its longest filter; with two half-batches in flight one half's CTAs fill the other's tails (measured on B200 at
-        1024 filters: 1.09 -> 1.02 ms per frame, end to end 92.8 -> 101.5 M feature-updates/s; three or four groups, or two
-        groups of a 512-filter batch, gain nothing).  None = 2 from
-        GROUP_MIN_FILTERS filters on, else 1."""
+        its longest filter; with two half-batches in flight one half's CTAs fill the other's tails (measured on B200: 1.10 ->
+        0.97 ms per frame at 1024 filters, 0.65 -> 0.62 at 512; 0.48 -> 0.50 at 256, and three or four groups gain nothing).
+        None = 2 from GROUP_MIN_FILTERS filters on, else 1."""
         self.config = config
         self.F = int(n_filters)
         if groups is None:

@@ -822,7 +822,9 @@ def parity_spot(args, res):
         else:
             worst, ids_equal = float('inf'), False
     return {'filters': [int(s + res['seed0']) for s in spot], 'frames': len(frames[spot[0]]), 'worst_rel': worst, 'ids_equal': bool(ids_equal),
-            'tolerance': 1e-9, 'ok': bool(ids_equal and worst < 1e-9), 'oracle_seconds': time.perf_counter() - t0}
+            'tolerance': 1e-9, 'ok': bool(ids_equal and worst < 1e-9), 'oracle_seconds': time.perf_counter() - t0,
+            'yardstick': 'the oracle against itself with every measurement moved by one ulp: 4.7e-13 median, 2.9e-9 worst over 96 seeds x 100 frames '
+                         '(tools/oracle_sensitivity.py)'}
 
 
 def run_b200(args):
